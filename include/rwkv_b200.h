@@ -1,0 +1,75 @@
+/* rwkv_b200.h -- ADDITIVE entry points of librwkv.so (nothing here replaces a reference
+ * symbol; rwkv.h is the drop-in surface).
+ *
+ * Why they exist: the reference ABI moves the whole recurrent state host<->device on every
+ * call (rwkv_eval.inc:2-22), which on a B200 costs more than the token itself for v5+
+ * models, and it has no notion of many independent streams (the ReservoirRWKV /
+ * chat-session workload loops rwkv_eval per stream, python/rwkv_cpp/reservoir.py:139-203).
+ * These calls keep states resident in HBM and step B streams per launch sequence.
+ * Plain pointers and sizes only.
+ */
+#ifndef RWKV_B200_H
+#define RWKV_B200_H
+
+#include "rwkv.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- environment ---------------------------------------------------------------------- */
+/* Number of CUDA devices visible; 0 when there is no usable GPU. */
+RWKV_API int  rwkv_b200_device_count(void);
+/* Selects the device used by subsequent rwkv_init_from_file calls of this thread (default:
+ * LOCAL_RANK env var if set, else 0). */
+RWKV_API bool rwkv_b200_set_device(int device);
+
+/* ---- batched, state-resident decode ------------------------------------------------------ */
+struct rwkv_b200_batch;   /* opaque: n_streams states in HBM + a captured launch graph */
+
+/* Creates n_streams streams over ctx's weights, each initialised like rwkv_init_state. */
+RWKV_API struct rwkv_b200_batch * rwkv_b200_batch_create(struct rwkv_context * ctx, size_t n_streams);
+RWKV_API void   rwkv_b200_batch_free(struct rwkv_b200_batch * batch);
+RWKV_API size_t rwkv_b200_batch_size(const struct rwkv_b200_batch * batch);
+/* state == NULL resets the stream to the initial state.  Host FP32, rwkv_get_state_len. */
+RWKV_API bool   rwkv_b200_batch_set_state(struct rwkv_b200_batch * batch, size_t stream, const float * state);
+RWKV_API bool   rwkv_b200_batch_get_state(struct rwkv_b200_batch * batch, size_t stream, float * state);
+/* Copies the first n floats of every stream's state to out[n_streams][n] (what a
+ * ReservoirRWKV readout consumes: reservoir.py:176-186). */
+RWKV_API bool   rwkv_b200_batch_get_state_prefix(struct rwkv_b200_batch * batch, size_t n, float * out);
+/* One token per stream.  tokens: host uint32[n_streams].  logits_out: host
+ * float[n_streams][n_vocab] or NULL (head skipped).  Same arithmetic per stream as rwkv_eval. */
+RWKV_API bool   rwkv_b200_batch_eval(struct rwkv_b200_batch * batch, const uint32_t * tokens, float * logits_out);
+/* Runs n_steps steps with tokens[n_steps][n_streams] already uploaded once; returns the
+ * device time of the steps in milliseconds (CUDA events on the engine's stream) in *ms.
+ * with_logits != 0 computes the head every step (logits stay in HBM).  Measurement aid. */
+RWKV_API bool   rwkv_b200_batch_run_timed(struct rwkv_b200_batch * batch, const uint32_t * tokens, size_t n_steps, int with_logits, double * ms);
+
+/* Number of kernel launches one decode step of this batch performs (graph nodes). */
+RWKV_API size_t rwkv_b200_batch_launches_per_step(const struct rwkv_b200_batch * batch, int with_logits);
+
+/* ---- sequence mode, device-timed ----------------------------------------------------------- */
+/* rwkv_eval_sequence over `tokens` from a fresh state with everything resident; returns device ms.
+ * Logits of the last token are computed when with_logits != 0. */
+RWKV_API bool   rwkv_b200_sequence_run_timed(struct rwkv_context * ctx, const uint32_t * tokens, size_t n, int with_logits, int iters, double * ms);
+
+/* ---- codec / mat-vec hooks (parity tests and the roofline microbenchmark) ------------------ */
+/* type ids are the ggmf ones (rwkv_file_format.inc:5-26): 0 F32, 1 F16, 2 Q4_0, 3 Q4_1, 7 Q5_0, 8 Q5_1, 9 Q8_0 */
+/* Uploads n_rows x n_cols weights given as raw ggml rows, repacks them as the loader does and
+ * dequantises on the device: out[n_rows][n_cols] must equal ggml's dequantize_row_* bit for bit. */
+RWKV_API bool   rwkv_b200_dequantize(int type, const void * raw, size_t n_rows, size_t n_cols, float * out);
+
+struct rwkv_b200_matrix;  /* `copies` independent device copies of one matrix (to defeat the L2 when timing) */
+RWKV_API struct rwkv_b200_matrix * rwkv_b200_matrix_create(int type, const void * raw, size_t n_rows, size_t n_cols, size_t copies);
+RWKV_API void   rwkv_b200_matrix_free(struct rwkv_b200_matrix * m);
+/* y[n_vec][n_rows] = W x[n_vec][n_cols] through the decode mat-vec kernel (n_vec >= 1). */
+RWKV_API bool   rwkv_b200_matrix_mul(struct rwkv_b200_matrix * m, const float * x, size_t n_vec, float * y);
+/* Times `iters` launches (n_vec columns) rotating over the copies; returns average device ms per launch. */
+RWKV_API bool   rwkv_b200_matrix_bench(struct rwkv_b200_matrix * m, size_t n_vec, int iters, double * ms_per_launch);
+/* Algorithmic bytes of one copy (the file bytes of the matrix). */
+RWKV_API size_t rwkv_b200_matrix_bytes(const struct rwkv_b200_matrix * m);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RWKV_B200_H */

@@ -1,0 +1,96 @@
+// Shared host-side declarations of the B200 engine: error plumbing, ggmf types,
+// device tensor descriptors.  Nothing here is visible across the C ABI.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include <unordered_map>
+#include <atomic>
+#include <mutex>
+
+#include <cuda_runtime.h>
+
+#include "../../include/rwkv.h"
+
+// ---------------------------------------------------------------------------------------
+// Error words.  Same convention as the reference (rwkv_error_handling.inc:1-54): init /
+// quantize record into a thread-local global word, eval paths into the context's word;
+// messages go to stderr only when printing is enabled.
+// ---------------------------------------------------------------------------------------
+namespace rb {
+
+extern thread_local int  g_last_error;
+extern thread_local bool g_print_errors;
+
+void global_fail(int flags, const char * file, int line, const char * fmt, ...);
+
+#define RB_FAIL(flags, ret, ...) do { rb::global_fail((flags), __FILE__, __LINE__, __VA_ARGS__); return ret; } while (0)
+#define RB_CHECK(cond, flags, ret, ...) do { if (!(cond)) RB_FAIL(flags, ret, __VA_ARGS__); } while (0)
+#define RB_CUDA(expr, flags, ret) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) \
+    RB_FAIL(flags, ret, "CUDA error %s at %s", cudaGetErrorString(e_), #expr); } while (0)
+
+// ---------------------------------------------------------------------------------------
+// ggmf container (rwkv_file_format.inc:5-26 type ids, :102-197 headers).
+// ---------------------------------------------------------------------------------------
+enum FileType : uint32_t {
+    T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3,
+    T_Q4_1_O = 4, T_Q4_2 = 5, T_Q4_3 = 6,     // removed formats: rejected like the reference does
+    T_Q5_0 = 7, T_Q5_1 = 8, T_Q8_0 = 9, T_COUNT = 10
+};
+
+inline bool type_supported(uint32_t t) { return t == T_F32 || t == T_F16 || t == T_Q4_0 || t == T_Q4_1 || t == T_Q5_0 || t == T_Q5_1 || t == T_Q8_0; }
+inline bool type_quantized(uint32_t t) { return t == T_Q4_0 || t == T_Q4_1 || t == T_Q5_0 || t == T_Q5_1 || t == T_Q8_0; }
+// bytes per block of `type_block(t)` elements (ggml-common.h:161-208)
+inline size_t type_block(uint32_t t) { return type_quantized(t) ? 32 : 1; }
+inline size_t type_block_bytes(uint32_t t) {
+    switch (t) { case T_F32: return 4; case T_F16: return 2; case T_Q4_0: return 18; case T_Q4_1: return 20;
+                 case T_Q5_0: return 22; case T_Q5_1: return 24; case T_Q8_0: return 34; default: return 0; }
+}
+const char * type_name(uint32_t t);
+int type_from_name(const char * s);   // -1 when unknown
+
+struct FileTensor {
+    std::string name;
+    uint32_t    type = 0;
+    uint32_t    n_dims = 0;
+    uint64_t    ne[3] = {1, 1, 1};        // ggml order: ne[0] fastest
+    const uint8_t * data = nullptr;       // into the mapping
+    size_t      nbytes = 0;
+    uint64_t    n_elements() const { return ne[0] * ne[1] * ne[2]; }
+};
+
+struct GgmfFile {
+    uint32_t version = 0, n_vocab = 0, n_embed = 0, n_layer = 0, data_type = 0;
+    std::vector<FileTensor> tensors;
+    std::unordered_map<std::string, size_t> index;
+    // mapping
+    void * map_base = nullptr; size_t map_size = 0; int fd = -1;
+    ~GgmfFile();
+    const FileTensor * find(const std::string & name) const {
+        auto it = index.find(name); return it == index.end() ? nullptr : &tensors[it->second];
+    }
+};
+// Returns false (with global error flags set) on any format violation.
+bool ggmf_open(const char * path, GgmfFile & out);
+
+// ---------------------------------------------------------------------------------------
+// Device-side matrix: a ggml (K, M) matrix = M rows of K weights, repacked into planes.
+//   quantised: qs plane  [M][nb] x 16 B (Q8_0: 32 B)   nibble bytes exactly as in the block
+//              qh plane  [M][nb] x u32  (Q5 only)       5th bits, bit-permuted (see repack)
+//              dm plane  [M][nb] x half (_0) | half2 (_1)
+//   F16 / F32: qs plane is the dense row-major matrix.
+// nb = K / 32.  Row r of every plane starts at r * nb * unit.
+// ---------------------------------------------------------------------------------------
+struct DevMat {
+    uint32_t type = T_F32;
+    uint32_t M = 0, K = 0;
+    const void * qs = nullptr;
+    const uint32_t * qh = nullptr;
+    const void * dm = nullptr;
+    size_t bytes = 0;                      // algorithmic bytes of the matrix (file bytes)
+};
+
+} // namespace rb

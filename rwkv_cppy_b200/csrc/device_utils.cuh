@@ -1,0 +1,95 @@
+// Device helpers shared by the kernels: warp/block reductions, the q8 activation
+// quantiser, block-wide layer norm.  Arithmetic that the reference performs as separate
+// ggml ops is written with the non-contracting intrinsics (__fmul_rn/__fadd_rn) so that
+// nvcc cannot fuse what the reference rounds twice.
+#pragma once
+#include <cuda_fp16.h>
+#include <cstdint>
+#include "kernels.h"
+
+namespace rb {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+__device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(FULL, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+
+// Block-wide double sum; `red` is >= 32 doubles of shared memory.  All threads get the result.
+__device__ __forceinline__ double block_sum_d(double v, double * red) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum_d(v);
+    __syncthreads();                 // protect `red` from the previous use
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    double t = 0.0;
+    for (int i = 0; i < nw; i++) t += red[i];      // same order in every thread -> identical result
+    return t;
+}
+
+__device__ __forceinline__ float round_f16(float v) { return __half2float(__float2half_rn(v)); }
+
+// One warp holds one block of 32 consecutive activations (lane = element).  Writes the
+// FP32 value and -- when the row has quantised planes -- the q8 block exactly as ggml's
+// x86 quantize_row_q8_0/q8_1 produce it (ggml-cpu-quants.c:783-850, 1083-1150):
+//   d = amax/127 (stored as fp16), id = 127/amax, q = rint(v*id) (ties to even),
+//   s = fp16(d * sum q) with the unrounded d.
+__device__ __forceinline__ void act_store_block(const Act & a, size_t row, int e, bool valid, float v) {
+    if (valid) a.f[row * a.K + e] = v;
+    if (a.q == nullptr) return;
+    const float amax = warp_max(valid ? fabsf(v) : 0.0f);
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+    const int   q  = valid ? __float2int_rn(__fmul_rn(v, id)) : 0;
+    const int   sum = warp_sum_i(q);
+    if (valid) a.q[row * a.K + e] = (int8_t) q;
+    if ((threadIdx.x & 31) == 0) {
+        const size_t b = row * (size_t) (a.K >> 5) + (e >> 5);
+        a.d[b] = round_f16(d);
+        a.s[b] = round_f16(__fmul_rn(d, (float) sum));
+        a.isum[b] = sum;
+    }
+}
+
+// ggml_compute_forward_norm_f32 (ggml-cpu.c:6880-6930): mean and variance accumulated in
+// double, y = (x-mean) * 1/sqrt(var+eps); then rwkv_layer_norm (rwkv_operators.inc:93):
+// y*w + b as two roundings.  `buf` (shared, D floats) receives the result.
+__device__ __forceinline__ void block_layer_norm(const float * __restrict__ x, int D, const float * __restrict__ w,
+                                                 const float * __restrict__ b, float eps, float * buf, double * red) {
+    double s = 0.0;
+    for (int i = threadIdx.x; i < D; i += blockDim.x) { const float v = x[i]; buf[i] = v; s += (double) v; }
+    s = block_sum_d(s, red);
+    const float mean = (float) (s / D);
+    double s2 = 0.0;
+    for (int i = threadIdx.x; i < D; i += blockDim.x) { const float v = __fsub_rn(buf[i], mean); buf[i] = v; s2 += (double) __fmul_rn(v, v); }
+    s2 = block_sum_d(s2, red);
+    const float var = (float) (s2 / D);
+    const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(var, eps)));
+    for (int i = threadIdx.x; i < D; i += blockDim.x) {
+        const float y = __fmul_rn(buf[i], scale);
+        buf[i] = __fadd_rn(__fmul_rn(y, w[i]), b[i]);
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float sigmoidf_ref(float x) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x))); }
+__device__ __forceinline__ float siluf_ref(float x)    { return __fdiv_rn(x, __fadd_rn(1.0f, expf(-x))); }
+
+} // namespace rb

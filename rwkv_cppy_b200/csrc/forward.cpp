@@ -1,0 +1,233 @@
+// The fixed per-layer launch sequence that replaces the reference's ggml graphs
+// (rwkv_build_serial_graph rwkv_graph.inc:611-720, rwkv_build_sequential_graph :744-870,
+// block builders :84-543).  One function serves single-token decode (R = 1), sequence mode
+// (R = T tokens of one stream) and batched decode (R independent streams): the kernels take
+// the row count and the "rows are streams" flag.
+#include "engine.h"
+
+namespace rb {
+
+Workspace::~Workspace() { for (void * p : allocations) cudaFree(p); }
+
+namespace {
+template <typename T>
+bool dalloc(Workspace & ws, T *& p, size_t n) {
+    void * q = nullptr;
+    if (cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) return false;
+    ws.allocations.push_back(q);
+    p = (T *) q;
+    return true;
+}
+bool act_alloc(Workspace & ws, Act & a, int rows, int K) {
+    a.K = K;
+    if (!dalloc(ws, a.f, (size_t) rows * K)) return false;
+    if (K % 32 == 0) {
+        const size_t nb = (size_t) rows * (K / 32);
+        if (!dalloc(ws, a.q, (size_t) rows * K) || !dalloc(ws, a.d, nb) || !dalloc(ws, a.s, nb) || !dalloc(ws, a.isum, nb)) return false;
+    }
+    return true;
+}
+} // namespace
+
+bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows) {
+    if (rows <= ws.rows && logit_rows <= ws.logit_rows) return true;
+    rows = std::max(rows, ws.rows); logit_rows = std::max(logit_rows, ws.logit_rows);
+    for (void * p : ws.allocations) cudaFree(p);
+    ws.allocations.clear();
+    ws.rows = 0; ws.logit_rows = 0;
+    const size_t D = m.n_embed, n = (size_t) rows * D;
+    bool ok = dalloc(ws, ws.x, n) && dalloc(ws, ws.x0, n) && dalloc(ws, ws.sx, n);
+    for (int i = 0; i < 6 && ok; i++) ok = act_alloc(ws, ws.mix[i], rows, (int) D);
+    ok = ok && act_alloc(ws, ws.y, rows, (int) D) && act_alloc(ws, ws.ffn_k, rows, m.ffn_dim);
+    for (int i = 0; i < 4 && ok; i++) ok = act_alloc(ws, ws.lora[i], rows, std::max(m.max_lora, 32));
+    ok = ok && act_alloc(ws, ws.head_in, logit_rows, (int) D);
+    ok = ok && dalloc(ws, ws.r, n) && dalloc(ws, ws.k, n) && dalloc(ws, ws.v, n) && dalloc(ws, ws.g, n) && dalloc(ws, ws.w, n)
+            && dalloc(ws, ws.a, n) && dalloc(ws, ws.vgate, n) && dalloc(ws, ws.ffn_r, n) && dalloc(ws, ws.v_first, n);
+    if (m.arch_major == 6) ok = ok && dalloc(ws, ws.m5, 5 * n);
+    ok = ok && dalloc(ws, ws.logits, (size_t) logit_rows * m.n_vocab) && dalloc(ws, ws.tokens, (size_t) rows);
+    if (!ok) return false;
+    ws.rows = rows; ws.logit_rows = logit_rows;
+    return true;
+}
+
+namespace {
+
+struct Pass {
+    const Model & m; Workspace & ws; const ForwardArgs & fa; cudaStream_t st;
+    cudaError_t err = cudaSuccess;
+    int R; size_t D;
+    size_t sstride;
+
+    Pass(const Model & m_, Workspace & ws_, const ForwardArgs & fa_, cudaStream_t st_)
+        : m(m_), ws(ws_), fa(fa_), st(st_), R(fa_.R), D(m_.n_embed), sstride(m_.state_len()) {}
+
+    void chk(cudaError_t e) { if (err == cudaSuccess && e != cudaSuccess) err = e; }
+
+    static GemvJob job(const DevMat & W, const Act & x, float * out, int ldo, int epi) {
+        GemvJob j; j.W = W; j.x = x; j.out = out; j.ldo = ldo; j.epi = epi; return j;
+    }
+    // launches the jobs grouped by weight type, R rows each
+    void gemv(std::vector<GemvJob> jobs, int rows) {
+        std::vector<bool> done(jobs.size(), false);
+        for (size_t i = 0; i < jobs.size(); i++) {
+            if (done[i]) continue;
+            GemvBatch b; b.T = rows;
+            for (size_t k = i; k < jobs.size() && b.n_jobs < GEMV_MAX_JOBS; k++)
+                if (!done[k] && jobs[k].W.type == jobs[i].W.type) { b.job[b.n_jobs++] = jobs[k]; done[k] = true; }
+            chk(launch_gemv(b, st));
+        }
+    }
+
+    const float * sin(uint32_t layer, size_t off) const { return fa.state_in + (size_t) layer * m.layer_state_len() + off; }
+    float * sout(uint32_t layer, size_t off) const { return fa.state_out + (size_t) layer * m.layer_state_len() + off; }
+
+    void ln_mix(uint32_t layer, bool att, int kind, int n_out, const float * const * mu, bool want_sx) {
+        const LayerW & l = m.layers[layer];
+        LnMixArgs a;
+        a.x = ws.x; a.ln_w = att ? l.ln1_w : l.ln2_w; a.ln_b = att ? l.ln1_b : l.ln2_b;
+        const size_t slot = att ? D : 0;                       // [ffn_xx, att_xx, ...] (rwkv_graph.inc:545-606)
+        a.state_in = sin(layer, slot); a.state_out = sout(layer, slot);
+        a.state_stride = sstride; a.batch = fa.batch; a.R = R; a.D = (int) D; a.kind = kind; a.n_out = n_out;
+        for (int i = 0; i < n_out; i++) { a.mu[i] = mu[i]; a.out[i] = ws.mix[i]; }
+        if (want_sx) { a.x0 = ws.x0; a.sx = ws.sx; }
+        chk(launch_ln_mix(a, st));
+    }
+
+    WkvArgs wkv_base(uint32_t layer) {
+        WkvArgs a;
+        a.R = R; a.D = (int) D; a.H = m.head_count; a.S = m.head_size; a.batch = fa.batch; a.state_stride = sstride;
+        a.state_in = sin(layer, 2 * D); a.state_out = sout(layer, 2 * D);
+        a.r = ws.r; a.k = ws.k; a.v = ws.v; a.y = ws.y; a.layer = (int) layer;
+        return a;
+    }
+
+    void ffn(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        if (m.arch_major == 7) {
+            ln_mix(layer, false, MIX_SX, 1, l.ffn_mu, false);
+            GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
+            gemv({k}, R);
+            Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
+            gemv({job(l.ffn_value, kin, ws.x, (int) D, EPI_ADD_TO)}, R);
+            return;
+        }
+        ln_mix(layer, false, m.arch_major == 6 ? MIX_SX : MIX_LERP, 2, l.ffn_mu, false);
+        GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
+        gemv({k, job(l.ffn_receptance, ws.mix[1], ws.ffn_r, (int) D, EPI_SIGMOID)}, R);
+        Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
+        GemvJob v = job(l.ffn_value, kin, ws.x, (int) D, EPI_MULADD_TO); v.aux = ws.ffn_r; v.ld_aux = (int) D;
+        gemv({v}, R);
+    }
+
+    void att_v4(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false);
+        gemv({job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
+              job(l.att_receptance, ws.mix[2], ws.r, (int) D, EPI_SIGMOID)}, R);
+        WkvArgs a = wkv_base(layer);
+        a.u = l.time_first; a.decay = l.time_decay;
+        chk(launch_wkv4(a, st));
+        gemv({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
+    }
+
+    void att_v5(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        const bool gate = m.arch_minor >= 2;
+        ln_mix(layer, true, MIX_LERP, gate ? 4 : 3, l.att_mu, false);
+        std::vector<GemvJob> jobs = {job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
+                                     job(l.att_receptance, ws.mix[2], ws.r, (int) D, EPI_STORE)};
+        if (gate) jobs.push_back(job(l.att_gate, ws.mix[3], ws.g, (int) D, EPI_SILU));
+        gemv(jobs, R);
+        WkvArgs a = wkv_base(layer);
+        a.u = l.time_first; a.decay = l.time_decay; a.per_head_scalar = gate ? 0 : 1;
+        a.g = gate ? ws.g : nullptr; a.lnx_w = l.lnx_w; a.lnx_b = l.lnx_b; a.gn_eps = 1e-5f;
+        chk(launch_wkv5(a, st));
+        gemv({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
+    }
+
+    void att_v6(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        ln_mix(layer, true, MIX_SX, 1, l.att_mu, true);                      // xxx = x + sx*maa_x
+        const int E5 = (int) l.maa_w1.M, E = E5 / 5;
+        GemvJob j1 = job(l.maa_w1, ws.mix[0], nullptr, 0, EPI_TANH);
+        j1.out_act = ws.lora[0]; j1.out_act.K = E5;
+        if (E5 % 32 != 0) { j1.out = ws.lora[0].f; j1.ldo = E5; j1.out_act = Act(); }
+        gemv({j1}, R);
+        Act t5 = ws.lora[0]; t5.K = E5; if (E5 % 32 != 0) t5.q = nullptr;
+        std::vector<GemvJob> jobs;
+        for (int n = 0; n < 5; n++) { GemvJob j = job(l.maa_w2[n], t5, ws.m5 + (size_t) n * R * D, (int) D, EPI_STORE); j.x_off = n * E; jobs.push_back(j); }
+        gemv(jobs, R);
+        V6Mix2Args mx; mx.x0 = ws.x0; mx.sx = ws.sx; mx.R = R; mx.D = (int) D;
+        for (int n = 0; n < 5; n++) { mx.m[n] = ws.m5 + (size_t) n * R * D; mx.maa[n] = l.att_mu[1 + n]; mx.out[n] = ws.mix[1 + n]; }
+        chk(launch_v6_mix2(mx, st));                                          // mix[1..5] = xw, xk, xv, xr, xg
+        const int DW = (int) l.decay_w1.M;
+        GemvJob jd = job(l.decay_w1, ws.mix[1], nullptr, 0, EPI_TANH); jd.out_act = ws.lora[1]; jd.out_act.K = DW;
+        if (DW % 32 != 0) { jd.out = ws.lora[1].f; jd.ldo = DW; jd.out_act = Act(); }
+        gemv({job(l.att_key, ws.mix[2], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[3], ws.v, (int) D, EPI_STORE),
+              job(l.att_receptance, ws.mix[4], ws.r, (int) D, EPI_STORE), job(l.att_gate, ws.mix[5], ws.g, (int) D, EPI_SILU), jd}, R);
+        Act td = ws.lora[1]; td.K = DW; if (DW % 32 != 0) td.q = nullptr;
+        GemvJob jw = job(l.decay_w2, td, ws.w, (int) D, EPI_V6_DECAY); jw.vec = l.time_decay;
+        gemv({jw}, R);
+        WkvArgs a = wkv_base(layer);
+        a.u = l.time_first; a.w = ws.w; a.g = ws.g; a.lnx_w = l.lnx_w; a.lnx_b = l.lnx_b; a.gn_eps = 64e-5f;
+        chk(launch_wkv5(a, st));
+        gemv({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
+    }
+
+    void att_v7(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        ln_mix(layer, true, MIX_SX, 6, l.att_mu, false);                     // mix = xr, xw, xk, xv, xa, xg
+        auto lora_in = [&](int slot, const DevMat & W, int epi) {
+            GemvJob j = job(W, ws.mix[slot == 0 ? 1 : slot == 1 ? 4 : slot == 2 ? 5 : 3], nullptr, 0, epi);
+            j.out = ws.lora[slot].f; j.ldo = (int) W.M;                       // low-rank mats are never quantised: FP32 rows suffice
+            return j;
+        };
+        std::vector<GemvJob> jobs = {job(l.att_receptance, ws.mix[0], ws.r, (int) D, EPI_STORE), job(l.att_key, ws.mix[2], ws.k, (int) D, EPI_STORE),
+                                     job(l.att_value, ws.mix[3], ws.v, (int) D, EPI_STORE),
+                                     lora_in(0, l.w1, EPI_TANH), lora_in(1, l.a1, EPI_STORE), lora_in(2, l.g1, EPI_SIGMOID)};
+        if (layer != 0) jobs.push_back(lora_in(3, l.v1, EPI_STORE));
+        gemv(jobs, R);
+        auto lora_out = [&](int slot, const DevMat & W, float * out, int epi, const float * vec) {
+            Act x; x.f = ws.lora[slot].f; x.K = (int) W.K;
+            GemvJob j = job(W, x, out, (int) D, epi); j.vec = vec;
+            return j;
+        };
+        jobs = {lora_out(0, l.w2, ws.w, EPI_V7_DECAY, l.w0), lora_out(1, l.a2, ws.a, EPI_BIAS_SIGMOID, l.a0), lora_out(2, l.g2, ws.g, EPI_STORE, nullptr)};
+        if (layer != 0) jobs.push_back(lora_out(3, l.v2, ws.vgate, EPI_BIAS_SIGMOID, l.v0));
+        gemv(jobs, R);
+        WkvArgs a = wkv_base(layer);
+        a.w = ws.w; a.a = ws.a; a.g = ws.g; a.vgate = ws.vgate; a.v_first = ws.v_first;
+        a.k_k = l.k_k; a.k_a = l.k_a; a.r_k = l.r_k; a.lnx_w = l.lnx_w; a.lnx_b = l.lnx_b; a.gn_eps = 64e-5f;
+        chk(launch_wkv7(a, st));
+        gemv({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
+    }
+
+    void run() {
+        chk(launch_embed_ln0(m.emb, ws.tokens, R, m.ln0_w, m.ln0_b, ws.x, st));
+        for (uint32_t i = 0; i < m.n_layer; i++) {
+            switch (m.arch_major) {
+                case 4: att_v4(i); break;
+                case 5: att_v5(i); break;
+                case 6: att_v6(i); break;
+                default: att_v7(i); break;
+            }
+            ffn(i);
+        }
+        if (fa.logits) {
+            const int rows = fa.batch ? R : 1;
+            const float * x = fa.batch ? ws.x : ws.x + (size_t) (R - 1) * D;
+            chk(launch_ln_act(x, (int) D, rows, (int) D, m.ln_out_w, m.ln_out_b, ws.head_in, st));
+            gemv({job(m.head, ws.head_in, ws.logits, (int) m.n_vocab, EPI_STORE)}, rows);
+        }
+    }
+};
+
+} // namespace
+
+cudaError_t forward(const Model & m, Workspace & ws, const ForwardArgs & fa, cudaStream_t st) {
+    Pass p(m, ws, fa, st);
+    p.run();
+    return p.err;
+}
+
+} // namespace rb

@@ -1,0 +1,296 @@
+// Dequant-fused mat-vec (decode) / thin mat-mat (up to 8 columns per pass) kernel.
+//
+// Replaces ggml_compute_forward_mul_mat + ggml_vec_dot_q*_q8_* / _f16 / _f32
+// (ggml-cpu.c:7377,7287; ggml-cpu-quants.c:1741,2321,2614,2969,3343; ggml-cpu.c:1352,1463)
+// and computes what they compute:
+//   quantised W : activations are q8 blocks (see Act); per block an exact integer dot
+//                 sumi = sum q_w*q_x (dp4a), then acc += (d_w*d_x)*sumi [+ m_w*s_x] in FP32;
+//   F16 W       : activations rounded to FP16 (ggml_fp32_to_fp16_row), products exact, FP32 sum;
+//   F32 W       : FP32 FMA.
+// Only the order of the FP32 block sums differs from the CPU (lane-strided + butterfly
+// instead of 8 AVX lanes + hsum).
+//
+// Work split: one CTA = 32 consecutive rows of one job (8 warps x 4 rows); lanes stride the
+// K/32 blocks of a row, so a warp request for one row is 32 consecutive 16-byte nibble
+// groups = 512 B coalesced (+128 B qh, +64/128 B scales).  The activation block (32 B of
+// int8 + d + s) is loaded once per lane iteration and reused for the 4 rows.  HBM-bound:
+// the roofline is bytes(W)/t against the measured copy bandwidth.
+// A CTA owning 32 consecutive outputs can quantise them for the next mat-vec in its
+// epilogue (one q8 block per column), so chained products need no extra launch.
+#include "device_utils.cuh"
+
+namespace rb {
+
+constexpr int GEMV_WARPS = 8;
+constexpr int GEMV_R     = 4;                       // rows per warp
+constexpr int GEMV_ROWS  = GEMV_WARPS * GEMV_R;     // 32 rows per CTA = one q8 block of outputs
+
+__device__ __forceinline__ int dp4a_(int a, int b, int c) { return __dp4a(a, b, c); }
+
+// ---- per-type inner products -------------------------------------------------------------
+template <int TYPE, int NCOL>
+struct RowAcc {
+    float acc[NCOL];
+    float summ[NCOL];     // m_w * s_x sums (Q4_1 / Q5_1)
+    __device__ __forceinline__ void clear() {
+#pragma unroll
+        for (int c = 0; c < NCOL; c++) { acc[c] = 0.0f; summ[c] = 0.0f; }
+    }
+};
+
+template <int NCOL>
+struct XBlock {             // the q8 activation block of NCOL columns held by one lane
+    int   w[NCOL][8];
+    float d[NCOL];
+    float s[NCOL];          // q8_1: s ; q8_0 offset formats: (float) isum is not needed, keep int below
+    int   isum[NCOL];
+};
+
+template <int TYPE, int NCOL>
+__device__ __forceinline__ void load_xblock(XBlock<NCOL> & xb, const Act & x, int x_off, int col0, int T, int b) {
+#pragma unroll
+    for (int c = 0; c < NCOL; c++) {
+        const int t = min(col0 + c, T - 1);
+        const size_t e0 = (size_t) t * x.K + x_off + (size_t) b * 32;
+        const uint4 lo = *reinterpret_cast<const uint4 *>(x.q + e0);
+        const uint4 hi = *reinterpret_cast<const uint4 *>(x.q + e0 + 16);
+        xb.w[c][0] = lo.x; xb.w[c][1] = lo.y; xb.w[c][2] = lo.z; xb.w[c][3] = lo.w;
+        xb.w[c][4] = hi.x; xb.w[c][5] = hi.y; xb.w[c][6] = hi.z; xb.w[c][7] = hi.w;
+        const size_t bi = (size_t) t * (x.K >> 5) + (x_off >> 5) + b;
+        xb.d[c] = x.d[bi];
+        if (TYPE == T_Q4_1 || TYPE == T_Q5_1) xb.s[c] = x.s[bi];
+        if (TYPE == T_Q4_0 || TYPE == T_Q5_0) xb.isum[c] = x.isum[bi];
+    }
+}
+
+// one row x one block for all columns
+template <int TYPE, int NCOL>
+__device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<NCOL> & xb,
+                                          const uint4 q0, const uint4 q1, const uint32_t qh, const float dw, const float mw) {
+    int wv[8];
+    if (TYPE == T_Q8_0) {
+        wv[0] = q0.x; wv[1] = q0.y; wv[2] = q0.z; wv[3] = q0.w; wv[4] = q1.x; wv[5] = q1.y; wv[6] = q1.z; wv[7] = q1.w;
+    } else {
+        const uint32_t v[4] = {q0.x, q0.y, q0.z, q0.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            uint32_t lo = v[i] & 0x0F0F0F0Fu, hi = (v[i] >> 4) & 0x0F0F0F0Fu;
+            if (TYPE == T_Q5_0 || TYPE == T_Q5_1) {
+                lo |= (qh << (4 - i)) & 0x10101010u;            // plane bit (8*j + i)     -> bit 4 of byte j
+                hi |= (qh >> i) & 0x10101010u;                  // plane bit (8*j + 4 + i) -> bit 4 of byte j
+            }
+            wv[i] = (int) lo; wv[4 + i] = (int) hi;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NCOL; c++) {
+        int dp = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) dp = dp4a_(wv[i], xb.w[c][i], dp);
+        if (TYPE == T_Q4_0) dp -= 8 * xb.isum[c];
+        if (TYPE == T_Q5_0) dp -= 16 * xb.isum[c];
+        ra.acc[c] = __fmaf_rn(__fmul_rn(dw, xb.d[c]), (float) dp, ra.acc[c]);
+        if (TYPE == T_Q4_1 || TYPE == T_Q5_1) ra.summ[c] = __fmaf_rn(mw, xb.s[c], ra.summ[c]);
+    }
+}
+
+__device__ __forceinline__ float apply_epilogue(const GemvJob & J, float y, int t, int m) {
+    switch (J.epi) {
+        case EPI_STORE:        return y;
+        case EPI_SIGMOID:      return sigmoidf_ref(y);
+        case EPI_RELU_SQ:      { const float r = fmaxf(y, 0.0f); return __fmul_rn(r, r); }
+        case EPI_SILU:         return siluf_ref(y);
+        case EPI_TANH:         return tanhf(y);
+        case EPI_ADD_TO:       return __fadd_rn(J.out[(size_t) t * J.ldo + m], y);
+        case EPI_MULADD_TO:    return __fadd_rn(J.out[(size_t) t * J.ldo + m], __fmul_rn(J.aux[(size_t) t * J.ld_aux + m], y));
+        case EPI_BIAS_SIGMOID: return sigmoidf_ref(__fadd_rn(y, J.vec[m]));
+        case EPI_V6_DECAY:     return expf(-expf(__fadd_rn(y, J.vec[m])));
+        case EPI_V7_DECAY:     return expf(__fmul_rn(sigmoidf_ref(__fadd_rn(y, J.vec[m])), -0.606531f));
+        default:               return y;
+    }
+}
+
+template <int TYPE, int NCOL>
+__global__ void __launch_bounds__(GEMV_WARPS * 32)
+gemv_kernel(const __grid_constant__ GemvBatch B) {
+    // which job / row block
+    int j = 0;
+#pragma unroll 1
+    while (j + 1 < B.n_jobs && (int) blockIdx.x >= B.cta_begin[j + 1]) j++;
+    const GemvJob & J = B.job[j];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int M = J.W.M, K = J.W.K, T = B.T;
+    const int row0 = ((int) blockIdx.x - B.cta_begin[j]) * GEMV_ROWS + warp * GEMV_R;
+    const int col0 = blockIdx.y * NCOL;
+
+    float res[GEMV_R][NCOL];
+
+    if constexpr (TYPE == T_F32 || TYPE == T_F16) {
+        constexpr int VEC = (TYPE == T_F32) ? 4 : 8;
+        float acc[GEMV_R][NCOL];
+#pragma unroll
+        for (int r = 0; r < GEMV_R; r++)
+#pragma unroll
+            for (int c = 0; c < NCOL; c++) acc[r][c] = 0.0f;
+        const int nchunk = (K % VEC == 0 && J.x_off % VEC == 0 && J.x.K % 4 == 0) ? K / VEC : 0;   // else rows are not 16-byte aligned
+        for (int ch = lane; ch < nchunk; ch += 32) {
+            float xv[NCOL][VEC];
+#pragma unroll
+            for (int c = 0; c < NCOL; c++) {
+                const int t = min(col0 + c, T - 1);
+                const float * xp = J.x.f + (size_t) t * J.x.K + J.x_off + (size_t) ch * VEC;
+#pragma unroll
+                for (int i = 0; i < VEC; i += 4) {
+                    const float4 f = *reinterpret_cast<const float4 *>(xp + i);
+                    xv[c][i] = f.x; xv[c][i + 1] = f.y; xv[c][i + 2] = f.z; xv[c][i + 3] = f.w;
+                }
+                if (TYPE == T_F16) {
+#pragma unroll
+                    for (int i = 0; i < VEC; i++) xv[c][i] = round_f16(xv[c][i]);
+                }
+            }
+            uint4 wq[GEMV_R];
+#pragma unroll
+            for (int r = 0; r < GEMV_R; r++) {
+                const int row = min(row0 + r, M - 1);
+                if (TYPE == T_F32) wq[r] = *reinterpret_cast<const uint4 *>(reinterpret_cast<const float *>(J.W.qs) + (size_t) row * K + (size_t) ch * 4);
+                else               wq[r] = *reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(J.W.qs) + (size_t) row * K + (size_t) ch * 8);
+            }
+#pragma unroll
+            for (int r = 0; r < GEMV_R; r++) {
+                float wf[VEC];
+                if (TYPE == T_F32) {
+                    wf[0] = __uint_as_float(wq[r].x); wf[1] = __uint_as_float(wq[r].y); wf[2] = __uint_as_float(wq[r].z); wf[3] = __uint_as_float(wq[r].w);
+                } else {
+                    const uint32_t u[4] = {wq[r].x, wq[r].y, wq[r].z, wq[r].w};
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const __half2 h = *reinterpret_cast<const __half2 *>(&u[i]);
+                        wf[2 * i] = __low2float(h); wf[2 * i + 1] = __high2float(h);
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < NCOL; c++)
+#pragma unroll
+                    for (int i = 0; i < VEC; i++) acc[r][c] = __fmaf_rn(wf[i], xv[c][i], acc[r][c]);
+            }
+        }
+        // scalar tail when K is not a multiple of the vector width
+        for (int k = nchunk * VEC + lane; k < K; k += 32) {
+#pragma unroll
+            for (int r = 0; r < GEMV_R; r++) {
+                const int row = min(row0 + r, M - 1);
+                const float wv = (TYPE == T_F32) ? reinterpret_cast<const float *>(J.W.qs)[(size_t) row * K + k]
+                                                 : __half2float(reinterpret_cast<const __half *>(J.W.qs)[(size_t) row * K + k]);
+#pragma unroll
+                for (int c = 0; c < NCOL; c++) {
+                    const int t = min(col0 + c, T - 1);
+                    float xs = J.x.f[(size_t) t * J.x.K + J.x_off + k];
+                    if (TYPE == T_F16) xs = round_f16(xs);
+                    acc[r][c] = __fmaf_rn(wv, xs, acc[r][c]);
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < GEMV_R; r++)
+#pragma unroll
+            for (int c = 0; c < NCOL; c++) res[r][c] = warp_sum(acc[r][c]);
+    } else {
+        RowAcc<TYPE, NCOL> ra[GEMV_R];
+#pragma unroll
+        for (int r = 0; r < GEMV_R; r++) ra[r].clear();
+        const int nb = K >> 5;
+        constexpr bool HAS_M = (TYPE == T_Q4_1 || TYPE == T_Q5_1);
+        constexpr bool HAS_H = (TYPE == T_Q5_0 || TYPE == T_Q5_1);
+        constexpr int  QV    = (TYPE == T_Q8_0) ? 2 : 1;          // uint4 per block
+        const uint4 * qs = reinterpret_cast<const uint4 *>(J.W.qs);
+        for (int b = lane; b < nb; b += 32) {
+            uint4 q0[GEMV_R], q1[GEMV_R]; uint32_t qh[GEMV_R]; float dw[GEMV_R], mw[GEMV_R];
+#pragma unroll
+            for (int r = 0; r < GEMV_R; r++) {
+                const size_t blk = (size_t) min(row0 + r, M - 1) * nb + b;
+                q0[r] = qs[blk * QV];
+                q1[r] = (QV == 2) ? qs[blk * QV + 1] : make_uint4(0, 0, 0, 0);
+                qh[r] = HAS_H ? J.W.qh[blk] : 0u;
+                if (HAS_M) {
+                    const __half2 dm = reinterpret_cast<const __half2 *>(J.W.dm)[blk];
+                    dw[r] = __low2float(dm); mw[r] = __high2float(dm);
+                } else {
+                    dw[r] = __half2float(reinterpret_cast<const __half *>(J.W.dm)[blk]); mw[r] = 0.0f;
+                }
+            }
+            XBlock<NCOL> xb;
+            load_xblock<TYPE, NCOL>(xb, J.x, J.x_off, col0, T, b);
+#pragma unroll
+            for (int r = 0; r < GEMV_R; r++) dot_block<TYPE, NCOL>(ra[r], xb, q0[r], q1[r], qh[r], dw[r], mw[r]);
+        }
+#pragma unroll
+        for (int r = 0; r < GEMV_R; r++)
+#pragma unroll
+            for (int c = 0; c < NCOL; c++) {
+                float v = warp_sum(ra[r].acc[c]);
+                if (HAS_M) v = __fadd_rn(v, warp_sum(ra[r].summ[c]));
+                res[r][c] = v;
+            }
+    }
+
+    // ---- epilogue: lane (r*NCOL + c) finishes output (row0 + r, col0 + c) ------------------
+    __shared__ float tile[NCOL][GEMV_ROWS];
+    float mine = 0.0f;
+#pragma unroll
+    for (int r = 0; r < GEMV_R; r++)
+#pragma unroll
+        for (int c = 0; c < NCOL; c++) if (lane == r * NCOL + c) mine = res[r][c];
+    const bool want_q = (J.out_act.f != nullptr);
+    if (lane < GEMV_R * NCOL) {
+        const int r = lane / NCOL, c = lane % NCOL;
+        const int m = row0 + r, t = col0 + c;
+        float v = 0.0f;
+        if (m < M && t < T) {
+            v = apply_epilogue(J, mine, t, m);
+            if (J.out) J.out[(size_t) t * J.ldo + m] = v;
+        }
+        if (want_q) tile[c][warp * GEMV_R + r] = v;
+    }
+    if (want_q) {                                   // uniform per CTA
+        __syncthreads();
+        if (warp < NCOL && col0 + warp < T) {
+            const int m = ((int) blockIdx.x - B.cta_begin[j]) * GEMV_ROWS + lane;
+            act_store_block(J.out_act, (size_t) (col0 + warp), m, m < M, tile[warp][lane]);
+        }
+    }
+}
+
+template <int TYPE>
+static cudaError_t launch_typed(const GemvBatch & b, int total_ctas, cudaStream_t st) {
+    const dim3 block(GEMV_WARPS * 32);
+    if (b.T == 1)      gemv_kernel<TYPE, 1><<<dim3(total_ctas, 1), block, 0, st>>>(b);
+    else if (b.T == 2) gemv_kernel<TYPE, 2><<<dim3(total_ctas, 1), block, 0, st>>>(b);
+    else if (b.T <= 4) gemv_kernel<TYPE, 4><<<dim3(total_ctas, 1), block, 0, st>>>(b);
+    else               gemv_kernel<TYPE, 8><<<dim3(total_ctas, (b.T + 7) / 8), block, 0, st>>>(b);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gemv(const GemvBatch & b_in, cudaStream_t st) {
+    if (b_in.n_jobs == 0) return cudaSuccess;
+    GemvBatch b = b_in;
+    int total = 0;
+    for (int j = 0; j < b.n_jobs; j++) {
+        b.cta_begin[j] = total;
+        total += (b.job[j].W.M + GEMV_ROWS - 1) / GEMV_ROWS;
+        if (b.job[j].W.type != b.job[0].W.type) return cudaErrorInvalidValue;
+    }
+    b.cta_begin[b.n_jobs] = total;
+    switch (b.job[0].W.type) {
+        case T_F32:  return launch_typed<T_F32>(b, total, st);
+        case T_F16:  return launch_typed<T_F16>(b, total, st);
+        case T_Q4_0: return launch_typed<T_Q4_0>(b, total, st);
+        case T_Q4_1: return launch_typed<T_Q4_1>(b, total, st);
+        case T_Q5_0: return launch_typed<T_Q5_0>(b, total, st);
+        case T_Q5_1: return launch_typed<T_Q5_1>(b, total, st);
+        case T_Q8_0: return launch_typed<T_Q8_0>(b, total, st);
+        default:     return cudaErrorInvalidValue;
+    }
+}
+
+} // namespace rb

@@ -1,0 +1,122 @@
+// Host-callable launchers of the sm_100a kernels + the plain-data descriptors they take.
+// Every launcher enqueues on the given stream and returns cudaGetLastError().
+#pragma once
+#include "common.h"
+
+namespace rb {
+
+// An activation matrix [T][K] in the forms the mat-vec kernels consume:
+//   f    FP32 values (always present)
+//   q    int8 per-32 quantised values  } the q8 activation blocks of ggml's CPU backend
+//   d    fp16-rounded scale per block   } (quantize_row_q8_0 / q8_1 as compiled for x86,
+//   s    fp16-rounded d*sum(q) (q8_1)   }  ggml-cpu-quants.c:783-850,1083-1150), split into
+//   isum sum(q) per block (int)         }  planes.  q == nullptr when K % 32 != 0.
+struct Act {
+    float *  f = nullptr;
+    int8_t * q = nullptr;
+    float *  d = nullptr;
+    float *  s = nullptr;
+    int *    isum = nullptr;
+    int      K = 0;          // row length (row stride of f and q; K/32 for d, s, isum)
+};
+
+enum Epilogue : int {
+    EPI_STORE = 0,       // out = y
+    EPI_SIGMOID,         // out = 1/(1+exp(-y))
+    EPI_RELU_SQ,         // out = max(y,0)^2
+    EPI_SILU,            // out = y/(1+exp(-y))
+    EPI_TANH,            // out = tanh(y)
+    EPI_ADD_TO,          // out = out + y                       (residual)
+    EPI_MULADD_TO,       // out = out + aux[t][m] * y           (ffn: x += r * (Wv k))
+    EPI_BIAS_SIGMOID,    // out = sigmoid(y + vec[m])           (v7 a, v-gate)
+    EPI_V6_DECAY,        // out = exp(-exp(y + vec[m]))         (rwkv_graph.inc:349-356)
+    EPI_V7_DECAY,        // out = exp(-0.606531 * sigmoid(y + vec[m]))   (rwkv_graph.inc:418-426)
+};
+
+struct GemvJob {
+    DevMat        W;
+    Act           x;                  // input rows, T of them (x.K == W.K)
+    int           x_off = 0;          // element offset into each input row (slices of a wider row)
+    float *       out = nullptr;      // [T][ldo]
+    int           ldo = 0;
+    int           epi = EPI_STORE;
+    const float * aux = nullptr;      // [T][ld_aux] (EPI_MULADD_TO)
+    int           ld_aux = 0;
+    const float * vec = nullptr;      // [M] per-row constant (bias / decay base)
+    Act           out_act;            // optional quantised copy of `out` (out_act.q may be null)
+};
+
+constexpr int GEMV_MAX_JOBS = 8;
+struct GemvBatch {
+    GemvJob job[GEMV_MAX_JOBS];
+    int     cta_begin[GEMV_MAX_JOBS + 1];   // prefix sum of CTAs per job (32 rows per CTA)
+    int     n_jobs = 0;
+    int     T = 1;
+};
+
+// All jobs of a batch must have the same weight type.
+cudaError_t launch_gemv(const GemvBatch & b, cudaStream_t st);
+
+// ---- codec -----------------------------------------------------------------------------
+// raw ggml blocks (device copy of the file bytes) -> plane layout
+cudaError_t launch_repack(uint32_t type, const uint8_t * raw, size_t n_blocks, void * qs, uint32_t * qh, void * dm, cudaStream_t st);
+// plane layout -> FP32 [M][K]; bit-exact dequantize_row_* (ggml-quants.c:255-363)
+cudaError_t launch_dequant(const DevMat & W, float * out, cudaStream_t st);
+// plane layout -> FP16 [M][K] (operand of the tensor-core sequence GEMM)
+cudaError_t launch_dequant_f16(const DevMat & W, void * out_half, cudaStream_t st);
+
+// ---- embedding + ln0 --------------------------------------------------------------------
+cudaError_t launch_embed_ln0(const DevMat & emb, const int * tokens, int T, const float * w, const float * b, float * x, cudaStream_t st);
+
+// ---- layer norm + token shift + mixes ---------------------------------------------------
+enum MixKind : int { MIX_LERP = 0 /* v4/v5: x*mu + (xp - xp*mu) */, MIX_SX = 1 /* v6/v7: x + (xp-x)*mu */ };
+constexpr int MIX_MAX_OUT = 6;
+struct LnMixArgs {
+    const float * x = nullptr;       // [R][D] residual stream
+    const float * ln_w = nullptr, * ln_b = nullptr;
+    // token shift source: row r uses state_in[(batch ? r : 0)*state_stride + slot ..] when r == 0 or batch,
+    // else LN(x[r-1]).  The new shift value LN(x[r]) is stored for the last row (sequence) / every row (batch).
+    const float * state_in = nullptr; float * state_out = nullptr;
+    size_t state_stride = 0;         // floats between consecutive streams' states
+    int    batch = 0;                // 0: rows are consecutive tokens of one stream; 1: rows are independent streams
+    int    R = 1, D = 0;
+    int    kind = MIX_LERP, n_out = 0;
+    const float * mu[MIX_MAX_OUT] = {};
+    Act    out[MIX_MAX_OUT];
+    float * x0 = nullptr;            // optional [R][D] copy of LN(x)
+    float * sx = nullptr;            // optional [R][D] xp - LN(x)
+};
+cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st);
+
+// plain LN of selected rows -> Act (ln_out before the head). row_idx == nullptr: rows 0..R-1.
+cudaError_t launch_ln_act(const float * x, int ldx, int R, int D, const float * w, const float * b, Act out, cudaStream_t st);
+
+// v6: x_i = x0 + sx * (maa_i + m_i), i = w,k,v,r,g  (rwkv_graph.inc:312-336)
+struct V6Mix2Args { const float * x0, * sx; const float * m[5]; const float * maa[5]; Act out[5]; int R, D; };
+cudaError_t launch_v6_mix2(const V6Mix2Args & a, cudaStream_t st);
+
+// standalone activation quantiser (when a producer could not fuse it)
+cudaError_t launch_quantize_act(Act a, int R, cudaStream_t st);
+
+// ---- WKV recurrences --------------------------------------------------------------------
+struct WkvArgs {
+    int R = 1, D = 0, H = 0, S = 0, batch = 0;
+    size_t state_stride = 0;
+    const float * state_in = nullptr; float * state_out = nullptr;   // pointers at this layer's att state slot(s)
+    const float * r = nullptr, * k = nullptr, * v = nullptr, * w = nullptr, * g = nullptr, * a = nullptr;   // [R][D]
+    const float * u = nullptr;            // time_first / time_faaaa  ([D] or [H] when per-head scalar)
+    const float * decay = nullptr;        // static decay ([D] or [H]); v6 uses per-token w instead
+    int   per_head_scalar = 0;            // v5.1: u, decay are one value per head
+    const float * lnx_w = nullptr, * lnx_b = nullptr;
+    float gn_eps = 1e-5f;
+    // v7 extras
+    const float * k_k = nullptr, * k_a = nullptr, * r_k = nullptr, * vgate = nullptr;
+    float * v_first = nullptr;            // [R][D]; written when layer == 0, read otherwise
+    int   layer = 0;
+    Act   y;                              // output rows
+};
+cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st);   // state slots: aa, bb, pp at state + {0,1,2}*D
+cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st);   // v5.1 / v5.2 / v6 (w != nullptr => per-token decay)
+cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st);
+
+} // namespace rb

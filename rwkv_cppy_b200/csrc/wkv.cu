@@ -1,0 +1,259 @@
+// WKV state recurrences, fused with what surrounds them in the reference graph
+// (group norm, ln_x affine, gate, v7 key/value preparation and bonus term), producing the
+// activation rows of the att.output mat-vec.
+//
+//   v4      rwkv_att_wkv_v4           rwkv_graph.inc:119-161 (per channel, running-max form)
+//   v5/v6   ggml_rwkv_wkv6            ggml.c:4627 -> ggml-cpu.c:11803-11980
+//           + per-head ggml_norm, ln_x, gate   rwkv_graph.inc:276-290 (v5), :371-384 (v6)
+//   v7      rwkv_wkv_v7_impl          rwkv_operators_wkv_v7.inc:37-121
+//           + l2norm / k,v preparation / bonus  rwkv_graph.inc:428-477, rwkv_operators.inc:40-83
+//
+// Rows are either T consecutive tokens of one stream (the scan runs inside the kernel,
+// state held in registers) or B independent streams (one step each).
+#include "device_utils.cuh"
+
+namespace rb {
+
+// ----------------------------------------------------------------------------------------
+// v4: one thread per channel.
+// ----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvArgs a) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    const int D = a.D;
+    const bool valid = e < D;
+    const int stream = a.batch ? blockIdx.y : 0;
+    const size_t soff = (size_t) stream * a.state_stride;
+    float aa = 0, bb = 0, pp = 0, u = 0, w = 0;
+    if (valid) {
+        aa = a.state_in[soff + e]; bb = a.state_in[soff + D + e]; pp = a.state_in[soff + 2 * D + e];
+        u = a.u[e]; w = a.decay[e];
+    }
+    const int steps = a.batch ? 1 : a.R;
+    for (int s = 0; s < steps; s++) {
+        const size_t row = a.batch ? stream : s;
+        float out = 0.0f;
+        if (valid) {
+            const float k = a.k[row * D + e], v = a.v[row * D + e], r = a.r[row * D + e];
+            float ww = __fadd_rn(u, k);
+            float qq = fmaxf(pp, ww);
+            float e1 = expf(__fsub_rn(pp, qq)), e2 = expf(__fsub_rn(ww, qq));
+            const float num = __fadd_rn(__fmul_rn(e1, aa), __fmul_rn(e2, v));
+            const float den = __fadd_rn(__fmul_rn(e1, bb), e2);
+            ww = __fadd_rn(pp, w);
+            qq = fmaxf(ww, k);
+            e1 = expf(__fsub_rn(ww, qq)); e2 = expf(__fsub_rn(k, qq));
+            aa = __fadd_rn(__fmul_rn(e1, aa), __fmul_rn(e2, v));
+            bb = __fadd_rn(__fmul_rn(e1, bb), e2);
+            pp = qq;
+            out = __fmul_rn(r, __fdiv_rn(num, den));
+        }
+        act_store_block(a.y, row, e, valid, out);
+    }
+    if (valid) { a.state_out[soff + e] = aa; a.state_out[soff + D + e] = bb; a.state_out[soff + 2 * D + e] = pp; }
+}
+
+cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st) {
+    dim3 grid((a.D + 255) / 256, a.batch ? a.R : 1);
+    wkv4_kernel<<<grid, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+// Per-head normalisation of `y` over the S threads of a head (ggml norm: double sums).
+// sy: shared [threads]; returns normalised value for this thread.
+template <int S>
+__device__ __forceinline__ float head_norm(float y, float * sy, int tid, bool active, float eps) {
+    __syncthreads();
+    sy[tid] = y;
+    __syncthreads();
+    const int base = (tid / S) * S;
+    double s = 0.0;
+    if (active) for (int j = 0; j < S; j++) s += (double) sy[base + j];
+    const float mean = (float) (s / S);
+    const float vv = __fsub_rn(y, mean);
+    __syncthreads();
+    sy[tid] = __fmul_rn(vv, vv);
+    __syncthreads();
+    double s2 = 0.0;
+    if (active) for (int j = 0; j < S; j++) s2 += (double) sy[base + j];
+    const float var = (float) (s2 / S);
+    const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(var, eps)));
+    return __fmul_rn(vv, scale);
+}
+
+// ----------------------------------------------------------------------------------------
+// v5.1 / v5.2 / v6.  CTA = HPB heads, thread (hl, j) owns column j (value index) of the
+// head state S[i][j]; state[h*S*S + i*S + j] (i = key index).
+// ----------------------------------------------------------------------------------------
+template <int S>
+__global__ void wkv5_kernel(const __grid_constant__ WkvArgs a) {
+    extern __shared__ float sm[];
+    const int nthr = blockDim.x;
+    float * sr = sm, * sk = sm + nthr, * sw = sm + 2 * nthr, * su = sm + 3 * nthr, * sy = sm + 4 * nthr;
+    const int tid = threadIdx.x;
+    const int hpb = nthr / S > 0 ? nthr / S : 1;
+    const int h = blockIdx.x * hpb + tid / S, j = tid % S;
+    const bool active = (tid < hpb * S) && h < a.H;
+    const int e = h * S + j, D = a.D;
+    const int hb = (tid / S) * S;
+    const int stream = a.batch ? blockIdx.y : 0;
+    const size_t soff = (size_t) stream * a.state_stride;
+
+    float st[S];
+    if (active) {
+#pragma unroll
+        for (int i = 0; i < S; i++) st[i] = a.state_in[soff + (size_t) h * S * S + (size_t) i * S + j];
+        su[tid] = a.per_head_scalar ? a.u[h] : a.u[e];
+        if (a.w == nullptr) sw[tid] = a.per_head_scalar ? a.decay[h] : a.decay[e];
+    }
+    const int steps = a.batch ? 1 : a.R;
+    for (int s = 0; s < steps; s++) {
+        const size_t row = a.batch ? stream : s;
+        __syncthreads();
+        float vj = 0.0f;
+        if (active) {
+            sr[tid] = a.r[row * D + e]; sk[tid] = a.k[row * D + e]; vj = a.v[row * D + e];
+            if (a.w) sw[tid] = a.w[row * D + e];
+        }
+        __syncthreads();
+        float y = 0.0f;
+        if (active) {
+#pragma unroll
+            for (int i = 0; i < S; i++) {
+                const float kv = __fmul_rn(vj, sk[hb + i]);
+                const float tmp = __fmaf_rn(kv, su[hb + i], st[i]);
+                y = __fmaf_rn(tmp, sr[hb + i], y);
+                st[i] = __fmaf_rn(st[i], sw[hb + i], kv);
+            }
+        }
+        float o = head_norm<S>(y, sy, tid, active, a.gn_eps);
+        if (active) {
+            o = __fadd_rn(__fmul_rn(o, a.lnx_w[e]), a.lnx_b[e]);
+            if (a.g) o = __fmul_rn(o, a.g[row * D + e]);
+        }
+        act_store_block(a.y, row, e, active, o);
+    }
+    if (active) {
+#pragma unroll
+        for (int i = 0; i < S; i++) a.state_out[soff + (size_t) h * S * S + (size_t) i * S + j] = st[i];
+    }
+}
+
+template <int S>
+static cudaError_t launch_wkv5_t(const WkvArgs & a, cudaStream_t st) {
+    const int hpb = S >= 32 ? 1 : 32 / S;
+    const int threads = ((hpb * S + 31) / 32) * 32;
+    dim3 grid((a.H + hpb - 1) / hpb, a.batch ? a.R : 1);
+    wkv5_kernel<S><<<grid, threads, 5 * threads * sizeof(float), st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st) {
+    switch (a.S) {
+        case 8:  return launch_wkv5_t<8>(a, st);
+        case 16: return launch_wkv5_t<16>(a, st);
+        case 32: return launch_wkv5_t<32>(a, st);
+        case 64: return launch_wkv5_t<64>(a, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+// ----------------------------------------------------------------------------------------
+// v7.  Thread (hl, i) owns ROW i (value index) of the head state S[i][j]:
+// state[h*S*S + i*S + j] (j = key index).
+// ----------------------------------------------------------------------------------------
+template <int S>
+__global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
+    extern __shared__ float sm[];
+    const int nthr = blockDim.x;
+    float * s_a = sm, * s_b = sm + nthr, * s_k = sm + 2 * nthr, * s_w = sm + 3 * nthr, * s_r = sm + 4 * nthr, * sy = sm + 5 * nthr;
+    const int tid = threadIdx.x;
+    const int hpb = nthr / S > 0 ? nthr / S : 1;
+    const int h = blockIdx.x * hpb + tid / S, i = tid % S;
+    const bool active = (tid < hpb * S) && h < a.H;
+    const int e = h * S + i, D = a.D;
+    const int hb = (tid / S) * S;
+    const int stream = a.batch ? blockIdx.y : 0;
+    const size_t soff = (size_t) stream * a.state_stride;
+
+    float st[S];
+    float kkc = 0, kac = 0, rkc = 0, lw = 0, lb = 0;
+    if (active) {
+        const float4 * p = reinterpret_cast<const float4 *>(a.state_in + soff + (size_t) h * S * S + (size_t) i * S);
+#pragma unroll
+        for (int j = 0; j < S / 4; j++) { const float4 f = p[j]; st[4 * j] = f.x; st[4 * j + 1] = f.y; st[4 * j + 2] = f.z; st[4 * j + 3] = f.w; }
+        kkc = a.k_k[e]; kac = a.k_a[e]; rkc = a.r_k[e]; lw = a.lnx_w[e]; lb = a.lnx_b[e];
+    }
+    const int steps = a.batch ? 1 : a.R;
+    for (int s = 0; s < steps; s++) {
+        const size_t row = a.batch ? stream : s;
+        float k = 0, v = 0, r = 0, w = 0, av = 0, g = 0;
+        if (active) {
+            const size_t x = row * D + e;
+            k = a.k[x]; v = a.v[x]; r = a.r[x]; w = a.w[x]; av = a.a[x]; g = a.g[x];
+            if (a.layer == 0) a.v_first[x] = v;
+            else v = __fadd_rn(v, __fmul_rn(__fsub_rn(a.v_first[x], v), a.vgate[x]));
+        }
+        // kk = l2norm_head(k * k_k)
+        const float kkp = __fmul_rn(k, kkc);
+        __syncthreads();
+        sy[tid] = kkp;
+        __syncthreads();
+        float ss = 0.0f;
+        if (active) for (int j = 0; j < S; j++) ss = __fmaf_rn(sy[hb + j], sy[hb + j], ss);
+        const float kk = __fmul_rn(kkp, __fdiv_rn(1.0f, fmaxf(__fsqrt_rn(ss), 1e-12f)));
+        const float ka = __fmul_rn(k, kac);
+        k = __fadd_rn(k, __fsub_rn(__fmul_rn(av, ka), ka));
+        __syncthreads();
+        s_a[tid] = -kk; s_b[tid] = __fmul_rn(kk, av); s_k[tid] = k; s_w[tid] = w; s_r[tid] = r;
+        sy[tid] = __fmul_rn(__fmul_rn(k, r), rkc);
+        __syncthreads();
+        float y = 0.0f, bonus = 0.0f;
+        if (active) {
+            float sa = 0.0f;
+#pragma unroll
+            for (int j = 0; j < S; j++) sa = __fmaf_rn(s_a[hb + j], st[j], sa);
+#pragma unroll
+            for (int j = 0; j < S; j++) {
+                const float kv = __fmul_rn(v, s_k[hb + j]);
+                st[j] = __fmaf_rn(sa, s_b[hb + j], __fmaf_rn(st[j], s_w[hb + j], kv));
+                y = __fmaf_rn(st[j], s_r[hb + j], y);
+            }
+            double rk = 0.0;
+            for (int j = 0; j < S; j++) rk += (double) sy[hb + j];
+            bonus = __fmul_rn(v, (float) rk);
+        }
+        float o = head_norm<S>(y, sy, tid, active, a.gn_eps);
+        if (active) {
+            o = __fadd_rn(__fmul_rn(o, lw), lb);
+            o = __fadd_rn(o, bonus);
+            o = __fmul_rn(o, g);
+        }
+        act_store_block(a.y, row, e, active, o);
+    }
+    if (active) {
+        float4 * p = reinterpret_cast<float4 *>(a.state_out + soff + (size_t) h * S * S + (size_t) i * S);
+#pragma unroll
+        for (int j = 0; j < S / 4; j++) p[j] = make_float4(st[4 * j], st[4 * j + 1], st[4 * j + 2], st[4 * j + 3]);
+    }
+}
+
+template <int S>
+static cudaError_t launch_wkv7_t(const WkvArgs & a, cudaStream_t st) {
+    const int hpb = S >= 32 ? 1 : 32 / S;
+    const int threads = ((hpb * S + 31) / 32) * 32;
+    dim3 grid((a.H + hpb - 1) / hpb, a.batch ? a.R : 1);
+    wkv7_kernel<S><<<grid, threads, 6 * threads * sizeof(float), st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st) {
+    switch (a.S) {
+        case 8:  return launch_wkv7_t<8>(a, st);
+        case 16: return launch_wkv7_t<16>(a, st);
+        case 32: return launch_wkv7_t<32>(a, st);
+        case 64: return launch_wkv7_t<64>(a, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+} // namespace rb
