@@ -84,6 +84,10 @@ class RwkvLib:
         lib.rwkv_get_print_errors.restype = ctypes.c_bool
         lib.rwkv_get_last_error.argtypes = [ctypes.c_void_p]
         lib.rwkv_get_last_error.restype = ctypes.c_int
+        if hasattr(lib, "rwkv_b200_device_count"):      # the product library also exports the additive API
+            lib.rwkv_b200_device_count.restype = ctypes.c_int
+            lib.rwkv_b200_dequantize.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, P_FLOAT]
+            lib.rwkv_b200_dequantize.restype = ctypes.c_bool
 
     def system_info(self) -> str:
         return self.lib.rwkv_get_system_info_string().decode()

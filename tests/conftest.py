@@ -17,3 +17,24 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture(scope="session")
+def lib_path():
+    """librwkv.so, built in-tree (no-op when the stamp matches)."""
+    from rwkv_cppy_b200.build import build_library
+    return build_library(verbose=False)
+
+
+@pytest.fixture(scope="session")
+def raw_lib(lib_path):
+    """The product library through the plain C-ABI binding (shared with the reference loader)."""
+    from oracle.refload import RwkvLib
+    L = RwkvLib(lib_path)
+    return L
+
+
+@pytest.fixture(scope="session")
+def shared_library(lib_path):
+    from rwkv_cppy_b200 import load_rwkv_shared_library
+    return load_rwkv_shared_library()

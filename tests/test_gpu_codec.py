@@ -1,0 +1,136 @@
+"""GPU parity of the block codecs and the dequant-fused mat-vec kernel against the oracle
+(numpy restatement pinned to ggml) -- through the C ABI hooks of include/rwkv_b200.h."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from oracle import rwkv_oracle as O
+from tests import util
+
+pytestmark = pytest.mark.gpu
+PF = ctypes.POINTER(ctypes.c_float)
+QT = {"q4_0": O.TYPE_Q4_0, "q4_1": O.TYPE_Q4_1, "q5_0": O.TYPE_Q5_0, "q5_1": O.TYPE_Q5_1, "q8_0": O.TYPE_Q8_0}
+
+
+def dev_dequant(lib, t, raw, rows, cols):
+    out = np.empty((rows, cols), np.float32)
+    raw = np.ascontiguousarray(raw)
+    assert lib.rwkv_b200_dequantize(t, raw.ctypes.data, rows, cols, out.ctypes.data_as(PF))
+    return out
+
+
+@pytest.mark.parametrize("name", list(QT))
+def test_device_dequant_bit_exact_on_ggml_vectors(raw_lib, name):
+    """dequantize_row_* (ggml-quants.c:255-363) incl. d=0, max half, subnormal, all-ones qh."""
+    cv = np.load(os.path.join(util.GOLDEN, "codec_vectors.npz"))
+    raw = cv[f"{name}/raw"]                                   # [512 blocks][block bytes]
+    y = dev_dequant(raw_lib.lib, QT[name], raw, 16, 32 * 32)  # 16 rows x 32 blocks
+    assert np.array_equal(y.reshape(-1).view(np.uint32), cv[f"{name}/deq"].view(np.uint32))
+
+
+@pytest.mark.parametrize("fmt", util.SIX)
+def test_device_dequant_bit_exact_on_model_tensors(raw_lib, fmt):
+    """Every quantised tensor of the committed 6v0 files, after upload + repack."""
+    f = O.read_ggmf(os.path.join(util.MODELS, f"tiny-rwkv-6v0-3m-{fmt}.bin"))
+    n = 0
+    for name in f.order:
+        t = f.tensors[name]
+        if t.dtype not in QT.values() or not name.startswith(("blocks.0.", "blocks.7.")):
+            continue
+        K, M = t.shape[0], int(np.prod(t.shape[1:]))
+        y = dev_dequant(raw_lib.lib, t.dtype, t.data, M, K)
+        assert np.array_equal(y.reshape(-1).view(np.uint32), O.dequantize(t.dtype, t.data).view(np.uint32)), name
+        n += 1
+    assert n >= 16
+
+
+def test_device_dequant_passthrough_f16_f32(raw_lib):
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((5, 40)).astype(np.float32)
+    assert np.array_equal(dev_dequant(raw_lib.lib, 0, x.view(np.uint8), 5, 40), x)
+    h = x.astype(np.float16)
+    assert np.array_equal(dev_dequant(raw_lib.lib, 1, h.view(np.uint8), 5, 40), h.astype(np.float32))
+
+
+def make_matrix(rng, t, M, K):
+    w = (rng.standard_normal((M, K)) / np.sqrt(K)).astype(np.float32)
+    if t == O.TYPE_FP32:
+        raw = w.view(np.uint8).reshape(-1)
+    elif t == O.TYPE_FP16:
+        raw = w.astype(np.float16).view(np.uint8).reshape(-1)
+    else:
+        raw = O.quantize_ref(t, w.reshape(-1))
+    return O.Mat(O.GgmfTensor("w", t, (K, M), raw)), raw
+
+
+class DevMatrix:
+    def __init__(self, lib, t, raw, M, K, copies=1):
+        lib.rwkv_b200_matrix_create.restype = ctypes.c_void_p
+        lib.rwkv_b200_matrix_create.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_size_t]
+        lib.rwkv_b200_matrix_mul.argtypes = [ctypes.c_void_p, PF, ctypes.c_size_t, PF]
+        lib.rwkv_b200_matrix_mul.restype = ctypes.c_bool
+        lib.rwkv_b200_matrix_free.argtypes = [ctypes.c_void_p]
+        self.lib, self.M, self.K = lib, M, K
+        raw = np.ascontiguousarray(raw)
+        self.ptr = lib.rwkv_b200_matrix_create(t, raw.ctypes.data, M, K, copies)
+        assert self.ptr
+
+    def mul(self, x):
+        x = np.ascontiguousarray(x, np.float32).reshape(-1, self.K)
+        y = np.empty((x.shape[0], self.M), np.float32)
+        assert self.lib.rwkv_b200_matrix_mul(self.ptr, x.ctypes.data_as(PF), x.shape[0], y.ctypes.data_as(PF))
+        return y
+
+    def free(self):
+        self.lib.rwkv_b200_matrix_free(self.ptr)
+
+
+TYPES = [O.TYPE_FP32, O.TYPE_FP16, O.TYPE_Q4_0, O.TYPE_Q4_1, O.TYPE_Q5_0, O.TYPE_Q5_1, O.TYPE_Q8_0]
+
+
+@pytest.mark.parametrize("t", TYPES, ids=[O.TYPE_NAMES[t] for t in TYPES])
+@pytest.mark.parametrize("M,K", [(96, 256), (1000, 768), (67, 2048), (32, 32)])
+def test_matvec_matches_reference_arithmetic(raw_lib, t, M, K):
+    """y = W x computed as ggml's CPU backend does (q8 activation blocks + integer block dots /
+    fp16-rounded activations): only the order of the FP32 block sums may differ."""
+    rng = np.random.default_rng(M * 7 + K + t)
+    mat, raw = make_matrix(rng, t, M, K)
+    dm = DevMatrix(raw_lib.lib, t, raw, M, K)
+    for n_vec in (1, 2, 3, 8, 11):
+        x = rng.standard_normal((n_vec, K)).astype(np.float32) * rng.choice([0.1, 1.0, 10.0])
+        y = dm.mul(x)
+        ref = np.stack([mat.matvec(x[i], "ref") for i in range(n_vec)])
+        scale = np.abs(ref).max() + 1e-6
+        assert np.abs(y - ref).max() <= 2e-5 * scale * np.sqrt(K / 32), (n_vec, np.abs(y - ref).max(), scale)
+        if n_vec > 1:                       # column results do not depend on how many columns share the pass
+            y1 = dm.mul(x[n_vec - 1])
+            assert np.array_equal(y1[0], y[n_vec - 1])
+    dm.free()
+
+
+@pytest.mark.parametrize("t", [O.TYPE_Q4_0, O.TYPE_Q5_1, O.TYPE_Q8_0, O.TYPE_FP16], ids=["Q4_0", "Q5_1", "Q8_0", "FP16"])
+def test_matvec_at_full_size(raw_lib, t):
+    """BASELINE-size matrix (5120 x 5120): a few dense and one-hot vectors against the oracle, and
+    linearity W(a + b) == W a + W b for FP16 weights with fp16-exact activations."""
+    M = K = 5120
+    rng = np.random.default_rng(5)
+    mat, raw = make_matrix(rng, t, M, K)
+    dm = DevMatrix(raw_lib.lib, t, raw, M, K)
+    x = np.zeros((4, K), np.float32)
+    x[0, 0] = 1.0
+    x[1, K - 1] = -2.0
+    x[2] = rng.standard_normal(K).astype(np.float32)
+    x[3] = np.float32(0.0)
+    y = dm.mul(x)
+    assert np.all(y[3] == 0.0)
+    for i in range(3):
+        ref = mat.matvec(x[i], "ref")
+        assert np.abs(y[i] - ref).max() <= 3e-5 * (np.abs(ref).max() + 1e-6) * np.sqrt(K / 32)
+    if t == O.TYPE_FP16:
+        a = rng.integers(-8, 8, K).astype(np.float32)
+        b = rng.integers(-8, 8, K).astype(np.float32)
+        ya, yb, yab = dm.mul(a)[0], dm.mul(b)[0], dm.mul(a + b)[0]
+        assert np.allclose(yab, ya + yb, rtol=1e-5, atol=1e-4)
+    dm.free()
