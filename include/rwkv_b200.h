@@ -24,6 +24,10 @@ RWKV_API int  rwkv_b200_device_count(void);
  * LOCAL_RANK env var if set, else 0). */
 RWKV_API bool rwkv_b200_set_device(int device);
 
+/* Timed runs (rwkv_b200_batch_run_timed) write `bytes` of scratch before every step so the
+ * step starts with a cold L2, and time each step with its own CUDA event pair; 0 = off. */
+RWKV_API void rwkv_b200_set_l2_flush(size_t bytes);
+
 /* ---- batched, state-resident decode ------------------------------------------------------ */
 struct rwkv_b200_batch;   /* opaque: n_streams states in HBM + a captured launch graph */
 

@@ -32,6 +32,9 @@ struct rwkv_b200_matrix {
 
 namespace {
 
+size_t g_flush_bytes = 0;      // rwkv_b200_set_l2_flush
+void * g_flush_buf = nullptr;
+
 bool upload_matrix(int type, const void * raw, size_t M, size_t K, cudaStream_t st, std::vector<void *> & allocs, DevMat & out) {
     RB_CHECK(type_supported((uint32_t) type), RWKV_ERROR_ARGS | RWKV_ERROR_DATA_TYPE, false, "Unsupported type id %d", type);
     const size_t blk = type_block(type), bb = type_block_bytes(type);
@@ -112,6 +115,11 @@ bool rwkv_b200_set_device(int device) {
     RB_CHECK(device >= 0 && device < n, RWKV_ERROR_ARGS, false, "Device %d out of range (%d devices)", device, n);
     t_device = device;
     return true;
+}
+
+void rwkv_b200_set_l2_flush(size_t bytes) {
+    if (g_flush_buf) { cudaFree(g_flush_buf); g_flush_buf = nullptr; }
+    g_flush_bytes = bytes;
 }
 
 // ---- batch ------------------------------------------------------------------------------------
@@ -217,17 +225,34 @@ bool rwkv_b200_batch_run_timed(struct rwkv_b200_batch * b, const uint32_t * toke
     cudaStreamSynchronize(ctx->stream);
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
-    cudaEventRecord(e0, ctx->stream);
     cudaError_t err = cudaSuccess;
-    for (size_t s = 0; s < n_steps && err == cudaSuccess; s++) {
-        err = cudaMemcpyAsync(b->ws.tokens, d_all + s * b->n, b->n * sizeof(int), cudaMemcpyDeviceToDevice, ctx->stream);
-        if (err == cudaSuccess) err = cudaGraphLaunch(b->graph[b->cur][lg], ctx->stream);
-        b->cur ^= 1;
-    }
-    cudaEventRecord(e1, ctx->stream);
-    if (err == cudaSuccess) err = cudaStreamSynchronize(ctx->stream);
     float t = 0.0f;
-    cudaEventElapsedTime(&t, e0, e1);
+    if (g_flush_bytes == 0) {
+        cudaEventRecord(e0, ctx->stream);
+        for (size_t s = 0; s < n_steps && err == cudaSuccess; s++) {
+            err = cudaMemcpyAsync(b->ws.tokens, d_all + s * b->n, b->n * sizeof(int), cudaMemcpyDeviceToDevice, ctx->stream);
+            if (err == cudaSuccess) err = cudaGraphLaunch(b->graph[b->cur][lg], ctx->stream);
+            b->cur ^= 1;
+        }
+        cudaEventRecord(e1, ctx->stream);
+        if (err == cudaSuccess) err = cudaStreamSynchronize(ctx->stream);
+        cudaEventElapsedTime(&t, e0, e1);
+    } else {
+        // L2 flushed before every step; only the steps are timed (one event pair per step)
+        if (!g_flush_buf) err = cudaMalloc(&g_flush_buf, g_flush_bytes);
+        for (size_t s = 0; s < n_steps && err == cudaSuccess; s++) {
+            cudaMemsetAsync(g_flush_buf, (int) (s & 0xFF), g_flush_bytes, ctx->stream);
+            err = cudaMemcpyAsync(b->ws.tokens, d_all + s * b->n, b->n * sizeof(int), cudaMemcpyDeviceToDevice, ctx->stream);
+            cudaEventRecord(e0, ctx->stream);
+            if (err == cudaSuccess) err = cudaGraphLaunch(b->graph[b->cur][lg], ctx->stream);
+            cudaEventRecord(e1, ctx->stream);
+            b->cur ^= 1;
+            if (err == cudaSuccess) err = cudaStreamSynchronize(ctx->stream);
+            float dt = 0.0f;
+            cudaEventElapsedTime(&dt, e0, e1);
+            t += dt;
+        }
+    }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     cudaFree(d_all);
     CTX_CHECK(ctx, err == cudaSuccess, RWKV_ERROR_GRAPH, false, "timed run failed: %s", cudaGetErrorString(err));

@@ -60,6 +60,7 @@ class RWKVSharedLibrary:
         # additive (include/rwkv_b200.h)
         sig("rwkv_b200_device_count", [], ctypes.c_int)
         sig("rwkv_b200_set_device", [ctypes.c_int], b)
+        sig("rwkv_b200_set_l2_flush", [sz], None)
         sig("rwkv_b200_batch_create", [vp, sz], vp)
         sig("rwkv_b200_batch_free", [vp], None)
         sig("rwkv_b200_batch_size", [vp], sz)
