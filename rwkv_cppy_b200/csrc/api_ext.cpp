@@ -50,19 +50,16 @@ bool upload_matrix(int type, const void * raw, size_t M, size_t K, cudaStream_t 
         out.qs = d;
         return true;
     }
-    const bool has_h = (type == T_Q5_0 || type == T_Q5_1), has_m = (type == T_Q4_1 || type == T_Q5_1);
     void * scratch = nullptr;
     RB_CUDA(cudaMalloc(&scratch, nbytes), RWKV_ERROR_ALLOC, false);
-    void * qs = alloc(n_blocks * (type == T_Q8_0 ? 32 : 16));
-    uint32_t * qh = has_h ? (uint32_t *) alloc(n_blocks * 4) : nullptr;
-    void * dm = alloc(n_blocks * (has_m ? 4 : 2));
-    bool ok = qs && dm && (!has_h || qh);
+    void * tiled = alloc(tiled_bytes(type, M, K));
+    bool ok = tiled != nullptr;
     ok = ok && cudaMemcpyAsync(scratch, raw, nbytes, cudaMemcpyHostToDevice, st) == cudaSuccess;
-    ok = ok && launch_repack(type, (const uint8_t *) scratch, n_blocks, qs, qh, dm, st) == cudaSuccess;
+    ok = ok && launch_repack(type, (const uint8_t *) scratch, M, K, tiled, st) == cudaSuccess;
     ok = ok && cudaStreamSynchronize(st) == cudaSuccess;
     cudaFree(scratch);
     RB_CHECK(ok, RWKV_ERROR_ALLOC, false, "matrix upload failed: %s", cudaGetErrorString(cudaGetLastError()));
-    out.qs = qs; out.qh = qh; out.dm = dm;
+    out.qs = tiled; out.rg_stride = (uint32_t) tiled_rg_stride(type, K);
     return true;
 }
 
@@ -325,7 +322,7 @@ struct rwkv_b200_matrix * rwkv_b200_matrix_create(int type, const void * raw, si
     rwkv_b200_matrix * m = new (std::nothrow) rwkv_b200_matrix();
     RB_CHECK(m != nullptr, RWKV_ERROR_ALLOC, nullptr, "alloc failed");
     m->device = dev;
-    bool ok = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) == cudaSuccess;
+    bool ok = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) == cudaSuccess && gemv_async_init() == cudaSuccess;
     m->copies.resize(copies);
     for (size_t c = 0; c < copies && ok; c++) ok = upload_matrix(type, raw, n_rows, n_cols, m->stream, m->allocations, m->copies[c]);
     if (!ok) { rwkv_b200_matrix_free(m); return nullptr; }

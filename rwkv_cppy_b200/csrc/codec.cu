@@ -3,9 +3,10 @@
 // File layout (ggml-common.h:161-208): block_q4_0 {f16 d; u8 qs[16]}, block_q4_1 {f16 d, m;
 // u8 qs[16]}, block_q5_0 {f16 d; u8 qh[4]; u8 qs[16]}, block_q5_1 {f16 d, m; u8 qh[4];
 // u8 qs[16]}, block_q8_0 {f16 d; i8 qs[32]} -- 18/20/22/24/34-byte records, i.e. no field
-// is 16-byte aligned.  At upload they are split into planes (see DevMat in common.h) so
-// that a warp reading 32 consecutive blocks issues one 512-byte fully coalesced request
-// for the nibbles and one 128-/64-byte request each for qh and the scales.
+// is 16-byte aligned.  At upload they are regrouped into warp tiles (see DevMat in common.h):
+// 4 rows x 32 blocks with nibbles, 5th bits and scales as separate 16-byte aligned planes, so
+// that a warp fetches its next 4 x 1024 weights with ONE contiguous bulk copy and then reads
+// lane-consecutive 16-byte / 4-byte / 2-byte items from shared memory without bank conflicts.
 //
 // Q5 high bits: the file keeps bit e of qh for element e.  The mat-vec kernel handles the
 // block as 8 words of 4 elements (word w = elements 4w..4w+3; words 0-3 are the low
@@ -18,78 +19,90 @@ namespace rb {
 
 __host__ __device__ __forceinline__ uint32_t permute_qh(uint32_t qh) {
     uint32_t out = 0;
-#pragma unroll
     for (int w = 0; w < 8; w++)
-#pragma unroll
         for (int i = 0; i < 4; i++) out |= ((qh >> (4 * w + i)) & 1u) << (8 * i + w);
     return out;
 }
 
-__global__ void repack_kernel(uint32_t type, const uint8_t * __restrict__ raw, size_t n_blocks,
-                              uint8_t * __restrict__ qs, uint32_t * __restrict__ qh, __half * __restrict__ dm) {
-    const size_t blk = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (blk >= n_blocks) return;
-    const int bb = type == T_Q4_0 ? 18 : type == T_Q4_1 ? 20 : type == T_Q5_0 ? 22 : type == T_Q5_1 ? 24 : 34;
-    const uint8_t * p = raw + blk * bb;
-    const bool has_m = (type == T_Q4_1 || type == T_Q5_1);
-    const bool has_h = (type == T_Q5_0 || type == T_Q5_1);
-    uint16_t d16 = (uint16_t) p[0] | ((uint16_t) p[1] << 8);
-    p += 2;
-    if (has_m) {
-        uint16_t m16 = (uint16_t) p[0] | ((uint16_t) p[1] << 8);
-        p += 2;
-        reinterpret_cast<uint16_t *>(dm)[2 * blk] = d16;
-        reinterpret_cast<uint16_t *>(dm)[2 * blk + 1] = m16;
-    } else {
-        reinterpret_cast<uint16_t *>(dm)[blk] = d16;
-    }
-    if (has_h) {
-        uint32_t h = (uint32_t) p[0] | ((uint32_t) p[1] << 8) | ((uint32_t) p[2] << 16) | ((uint32_t) p[3] << 24);
-        p += 4;
-        qh[blk] = permute_qh(h);
-    }
-    const int nq = type == T_Q8_0 ? 32 : 16;
-    uint8_t * o = qs + blk * nq;
-    for (int i = 0; i < nq; i++) o[i] = p[i];
+// Byte offsets of block (row, b) inside the tiled storage.
+struct TilePos { size_t qs, qh, dm; };
+__device__ __forceinline__ TilePos tile_pos(uint32_t type, uint32_t rg_stride, int nb, size_t row, int b) {
+    const uint32_t QB = tile_qb(type), HB = tile_hb(type), DB = tile_db(type);
+    const size_t rg = row / TILE_ROWS; const int r = (int) (row % TILE_ROWS);
+    const int c = b / TILE_BLOCKS, jb = b % TILE_BLOCKS;
+    const int cnt = min(TILE_BLOCKS, nb - c * TILE_BLOCKS);
+    const size_t base = rg * rg_stride + (size_t) TILE_ROWS * TILE_BLOCKS * c * (QB + HB + DB);
+    TilePos p;
+    p.qs = base + (size_t) (r * cnt + jb) * QB;
+    p.qh = base + (size_t) TILE_ROWS * cnt * QB + (size_t) (r * cnt + jb) * HB;
+    p.dm = base + (size_t) TILE_ROWS * cnt * (QB + HB) + (size_t) (r * cnt + jb) * DB;
+    return p;
 }
 
-cudaError_t launch_repack(uint32_t type, const uint8_t * raw, size_t n_blocks, void * qs, uint32_t * qh, void * dm, cudaStream_t st) {
-    if (n_blocks == 0) return cudaSuccess;
+// one thread per (padded row, block)
+__global__ void repack_kernel(uint32_t type, const uint8_t * __restrict__ raw, uint32_t M, uint32_t nb, uint32_t rg_stride,
+                              uint8_t * __restrict__ out) {
+    const size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t rows_padded = ((size_t) M + TILE_ROWS - 1) / TILE_ROWS * TILE_ROWS;
+    if (idx >= rows_padded * nb) return;
+    const size_t row = idx / nb; const int b = (int) (idx % nb);
+    const int bb = type == T_Q4_0 ? 18 : type == T_Q4_1 ? 20 : type == T_Q5_0 ? 22 : type == T_Q5_1 ? 24 : 34;
+    const bool has_m = (type == T_Q4_1 || type == T_Q5_1), has_h = (type == T_Q5_0 || type == T_Q5_1);
+    const TilePos p = tile_pos(type, rg_stride, (int) nb, row, b);
+    const int nq = type == T_Q8_0 ? 32 : 16;
+    if (row >= M) {                                   // padding rows: zero blocks (d = 0)
+        for (int i = 0; i < nq; i++) out[p.qs + i] = 0;
+        if (has_h) *reinterpret_cast<uint32_t *>(out + p.qh) = 0;
+        *reinterpret_cast<uint16_t *>(out + p.dm) = 0;
+        if (has_m) *reinterpret_cast<uint16_t *>(out + p.dm + 2) = 0;
+        return;
+    }
+    const uint8_t * s = raw + (row * nb + b) * bb;
+    *reinterpret_cast<uint16_t *>(out + p.dm) = (uint16_t) s[0] | ((uint16_t) s[1] << 8);
+    s += 2;
+    if (has_m) { *reinterpret_cast<uint16_t *>(out + p.dm + 2) = (uint16_t) s[0] | ((uint16_t) s[1] << 8); s += 2; }
+    if (has_h) {
+        const uint32_t h = (uint32_t) s[0] | ((uint32_t) s[1] << 8) | ((uint32_t) s[2] << 16) | ((uint32_t) s[3] << 24);
+        *reinterpret_cast<uint32_t *>(out + p.qh) = permute_qh(h);
+        s += 4;
+    }
+    for (int i = 0; i < nq; i++) out[p.qs + i] = s[i];
+}
+
+cudaError_t launch_repack(uint32_t type, const uint8_t * raw, size_t M, size_t K, void * out, cudaStream_t st) {
+    const size_t nb = K / 32, rows_padded = (M + TILE_ROWS - 1) / TILE_ROWS * TILE_ROWS;
+    const size_t n = rows_padded * nb;
+    if (n == 0) return cudaSuccess;
     const int threads = 256;
-    const unsigned grid = (unsigned) ((n_blocks + threads - 1) / threads);
-    repack_kernel<<<grid, threads, 0, st>>>(type, raw, n_blocks, (uint8_t *) qs, qh, (__half *) dm);
+    repack_kernel<<<(unsigned) ((n + threads - 1) / threads), threads, 0, st>>>(type, raw, (uint32_t) M, (uint32_t) nb,
+                                                                              (uint32_t) tiled_rg_stride(type, K), (uint8_t *) out);
     return cudaGetLastError();
 }
 
-// Integer value and scales of element j (0..31) of block `blk`, from the planes.
+// Value of weight (row, col) from the tiled storage.
 // y = q*d (+m) with one rounding (q*d is exact in FP32: <= 8 x 11 significant bits), which
 // is what dequantize_row_* computes whether or not the host compiler contracts to an FMA.
-__device__ __forceinline__ float plane_element(const DevMat & W, size_t blk, int j) {
-    switch (W.type) {
-        case T_Q8_0: {
-            const int q = reinterpret_cast<const int8_t *>(W.qs)[blk * 32 + j];
-            return __fmul_rn((float) q, __half2float(reinterpret_cast<const __half *>(W.dm)[blk]));
-        }
-        case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: {
-            const uint8_t byte = reinterpret_cast<const uint8_t *>(W.qs)[blk * 16 + (j & 15)];
-            int q = (j < 16) ? (byte & 0x0F) : (byte >> 4);
-            if (W.type == T_Q5_0 || W.type == T_Q5_1) {
-                const int w = j >> 2, i = j & 3;
-                q |= (int) ((W.qh[blk] >> (8 * i + w)) & 1u) << 4;
-            }
-            if (W.type == T_Q4_0) return __fmul_rn((float) (q - 8), __half2float(reinterpret_cast<const __half *>(W.dm)[blk]));
-            if (W.type == T_Q5_0) return __fmul_rn((float) (q - 16), __half2float(reinterpret_cast<const __half *>(W.dm)[blk]));
-            const __half2 dmv = reinterpret_cast<const __half2 *>(W.dm)[blk];
-            return __fmaf_rn((float) q, __low2float(dmv), __high2float(dmv));
-        }
-        default: return 0.0f;
+__device__ __forceinline__ float tiled_element(const DevMat & W, size_t row, int col) {
+    const uint8_t * base = reinterpret_cast<const uint8_t *>(W.qs);
+    const int j = col & 31;
+    const TilePos p = tile_pos(W.type, W.rg_stride, (int) (W.K >> 5), row, col >> 5);
+    const float d = __half2float(*reinterpret_cast<const __half *>(base + p.dm));
+    if (W.type == T_Q8_0) return __fmul_rn((float) reinterpret_cast<const int8_t *>(base + p.qs)[j], d);
+    const uint8_t byte = base[p.qs + (j & 15)];
+    int q = (j < 16) ? (byte & 0x0F) : (byte >> 4);
+    if (W.type == T_Q5_0 || W.type == T_Q5_1) {
+        const int w = j >> 2, i = j & 3;
+        q |= (int) ((*reinterpret_cast<const uint32_t *>(base + p.qh) >> (8 * i + w)) & 1u) << 4;
     }
+    if (W.type == T_Q4_0) return __fmul_rn((float) (q - 8), d);
+    if (W.type == T_Q5_0) return __fmul_rn((float) (q - 16), d);
+    return __fmaf_rn((float) q, d, __half2float(*reinterpret_cast<const __half *>(base + p.dm + 2)));
 }
 
 __device__ __forceinline__ float mat_element(const DevMat & W, size_t row, int col) {
     if (W.type == T_F32) return reinterpret_cast<const float *>(W.qs)[row * W.K + col];
     if (W.type == T_F16) return __half2float(reinterpret_cast<const __half *>(W.qs)[row * W.K + col]);
-    return plane_element(W, row * (size_t) (W.K >> 5) + (col >> 5), col & 31);
+    return tiled_element(W, row, col);
 }
 
 template <typename OutT>

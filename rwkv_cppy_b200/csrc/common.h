@@ -77,20 +77,38 @@ struct GgmfFile {
 bool ggmf_open(const char * path, GgmfFile & out);
 
 // ---------------------------------------------------------------------------------------
-// Device-side matrix: a ggml (K, M) matrix = M rows of K weights, repacked into planes.
-//   quantised: qs plane  [M][nb] x 16 B (Q8_0: 32 B)   nibble bytes exactly as in the block
-//              qh plane  [M][nb] x u32  (Q5 only)       5th bits, bit-permuted (see repack)
-//              dm plane  [M][nb] x half (_0) | half2 (_1)
-//   F16 / F32: qs plane is the dense row-major matrix.
-// nb = K / 32.  Row r of every plane starts at r * nb * unit.
+// Device-side matrix: a ggml (K, M) matrix = M rows of K weights.
+//   F16 / F32: `qs` is the dense row-major matrix.
+//   quantised: `qs` is the WARP-TILE layout the mat-vec kernel streams with one bulk copy per
+//     tile.  A tile = 4 consecutive rows (a row group) x one chunk of up to 32 blocks
+//     (1024 weights) and stores three planes back to back:
+//        nibbles  [4][cnt] x 16 B (Q8_0: 32 B)   bytes exactly as in the ggml block
+//        qh       [4][cnt] x u32  (Q5 only)       5th bits, bit-permuted (see codec.cu)
+//        scales   [4][cnt] x half (_0) | half2 d,m (_1)
+//     cnt = 32 except for the last chunk of a row (nb % 32).  Tiles of a row group are
+//     consecutive (chunk 0, 1, ...); row groups are `rg_stride` bytes apart (4*nb*block
+//     bytes rounded up to 16).  Rows M..4*ceil(M/4)-1 are zero blocks.  Same bytes per
+//     weight as the file format.
 // ---------------------------------------------------------------------------------------
+constexpr int TILE_ROWS = 4, TILE_BLOCKS = 32;
+
 struct DevMat {
     uint32_t type = T_F32;
     uint32_t M = 0, K = 0;
     const void * qs = nullptr;
-    const uint32_t * qh = nullptr;
-    const void * dm = nullptr;
+    uint32_t rg_stride = 0;                // bytes between row groups (quantised only)
     size_t bytes = 0;                      // algorithmic bytes of the matrix (file bytes)
 };
+
+#if defined(__CUDACC__)
+#define RB_HD __host__ __device__
+#else
+#define RB_HD
+#endif
+RB_HD inline uint32_t tile_qb(uint32_t t) { return t == T_Q8_0 ? 32u : 16u; }
+RB_HD inline uint32_t tile_hb(uint32_t t) { return (t == T_Q5_0 || t == T_Q5_1) ? 4u : 0u; }
+RB_HD inline uint32_t tile_db(uint32_t t) { return (t == T_Q4_1 || t == T_Q5_1) ? 4u : 2u; }
+inline size_t tiled_rg_stride(uint32_t t, size_t K) { return ((size_t) TILE_ROWS * (K / 32) * type_block_bytes(t) + 15) & ~(size_t) 15; }
+inline size_t tiled_bytes(uint32_t t, size_t M, size_t K) { return ((M + TILE_ROWS - 1) / TILE_ROWS) * tiled_rg_stride(t, K) + 16; }
 
 } // namespace rb

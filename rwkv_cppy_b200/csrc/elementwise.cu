@@ -11,45 +11,144 @@
 
 namespace rb {
 
-__global__ void __launch_bounds__(256) ln_mix_kernel(const __grid_constant__ LnMixArgs a) {
-    extern __shared__ float smem[];
-    __shared__ double red[32];
-    const int r = blockIdx.x, D = a.D;
-    float * s_x0 = smem, * s_xp = smem + D;
-    block_layer_norm(a.x + (size_t) r * D, D, a.ln_w, a.ln_b, 1e-5f, s_x0, red);
-    const size_t soff = a.batch ? (size_t) r * a.state_stride : 0;
-    if (a.batch || r == 0) {
-        for (int i = threadIdx.x; i < D; i += blockDim.x) s_xp[i] = a.state_in[soff + i];
-        __syncthreads();
-    } else {
-        block_layer_norm(a.x + (size_t) (r - 1) * D, D, a.ln_w, a.ln_b, 1e-5f, s_xp, red);
-    }
-    if (a.batch || r == a.R - 1)
-        for (int i = threadIdx.x; i < D; i += blockDim.x) a.state_out[soff + i] = s_x0[i];
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    for (int e0 = warp * 32; e0 < D; e0 += nw * 32) {
-        const int e = e0 + lane;
-        const bool valid = e < D;
-        const float x0 = valid ? s_x0[e] : 0.0f, xp = valid ? s_xp[e] : 0.0f;
-        const float sx = __fsub_rn(xp, x0);
-        if (valid && a.x0) a.x0[(size_t) r * D + e] = x0;
-        if (valid && a.sx) a.sx[(size_t) r * D + e] = sx;
+// N activation blocks at once (one per output), shuffle chains interleaved for ILP.
+template <int N>
+__device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, int e, bool valid, const float (&v)[N]) {
+    float amax[N]; int q[N], sum[N];
 #pragma unroll
-        for (int o = 0; o < MIX_MAX_OUT; o++) {
-            if (o >= a.n_out) break;
-            const float mu = valid ? a.mu[o][e] : 0.0f;
-            float v;
-            if (a.kind == MIX_LERP) v = __fadd_rn(__fmul_rn(x0, mu), __fsub_rn(xp, __fmul_rn(xp, mu)));
-            else                    v = __fadd_rn(__fmul_rn(sx, mu), x0);
-            act_store_block(a.out[o], (size_t) r, e, valid, v);
+    for (int o = 0; o < N; o++) amax[o] = valid ? fabsf(v[o]) : 0.0f;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+        for (int o = 0; o < N; o++) amax[o] = fmaxf(amax[o], __shfl_xor_sync(FULL, amax[o], off));
+#pragma unroll
+    for (int o = 0; o < N; o++) {
+        const float id = amax[o] != 0.0f ? __fdiv_rn(127.0f, amax[o]) : 0.0f;
+        q[o] = valid ? __float2int_rn(__fmul_rn(v[o], id)) : 0;
+        sum[o] = q[o];
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+        for (int o = 0; o < N; o++) sum[o] += __shfl_xor_sync(FULL, sum[o], off);
+#pragma unroll
+    for (int o = 0; o < N; o++) {
+        const Act & a = outs[o];
+        if (valid) a.f[row * a.K + e] = v[o];
+        if (a.q == nullptr) continue;
+        if (valid) a.q[row * a.K + e] = (int8_t) q[o];
+        if ((threadIdx.x & 31) == 0) {
+            const float d = __fdiv_rn(amax[o], 127.0f);
+            const size_t b = row * (size_t) (a.K >> 5) + (e >> 5);
+            a.d[b] = round_f16(d);
+            a.s[b] = round_f16(__fmul_rn(d, (float) sum[o]));
+            a.isum[b] = sum[o];
         }
     }
 }
 
-cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
-    ln_mix_kernel<<<a.R, 256, 2 * a.D * sizeof(float), st>>>(a);
+// One CTA per row, thread t owns elements t, t + blockDim, ... (ITEMS of them), so every
+// global load of the kernel is issued up front (one round trip) and each warp quantises
+// aligned 32-element blocks.  LN(x[r]) and -- in sequence mode -- LN(x[r-1]) (the token-shift
+// source, recomputed instead of waiting for the neighbouring CTA) run through the same
+// reductions; both use identical arithmetic, so the recomputed row is bit-identical.
+template <int ITEMS, int NOUT>
+__global__ void __launch_bounds__(1024) ln_mix_kernel(const __grid_constant__ LnMixArgs a) {
+    __shared__ double red[4][32];
+    const int r = blockIdx.x, D = a.D, nt = blockDim.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = nt >> 5;
+    const bool from_state = a.batch || r == 0;
+    const size_t soff = a.batch ? (size_t) r * a.state_stride : 0;
+
+    float x[2][ITEMS], xs[ITEMS], w[ITEMS], bia[ITEMS], mu[NOUT][ITEMS];
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * nt + threadIdx.x;
+        const bool valid = e < D;
+        x[0][it] = valid ? a.x[(size_t) r * D + e] : 0.0f;
+        x[1][it] = !valid ? 0.0f : from_state ? a.state_in[soff + e] : a.x[(size_t) (r - 1) * D + e];
+        xs[it] = x[1][it];                                   // untouched copy: the shift value when it comes from the state
+        w[it] = valid ? a.ln_w[e] : 0.0f; bia[it] = valid ? a.ln_b[e] : 0.0f;
+#pragma unroll
+        for (int o = 0; o < NOUT; o++) mu[o][it] = valid ? a.mu[o][e] : 0.0f;
+    }
+    const int nrow = from_state ? 1 : 2;                     // rows to normalise (uniform per CTA)
+    // ---- mean (double accumulation as ggml_compute_forward_norm_f32) ----
+    double s[2] = {0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < 2; k++)
+#pragma unroll
+        for (int it = 0; it < ITEMS; it++) s[k] += (double) x[k][it];
+#pragma unroll
+    for (int k = 0; k < 2; k++) { s[k] = warp_sum_d(s[k]); if (lane == 0) red[k][warp] = s[k]; }
+    __syncthreads();
+    float mean[2];
+#pragma unroll
+    for (int k = 0; k < 2; k++) { const double t = warp_sum_d(lane < nw ? red[k][lane] : 0.0); mean[k] = (float) (t / D); }
+    // ---- variance ----
+    double s2[2] = {0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < 2; k++)
+#pragma unroll
+        for (int it = 0; it < ITEMS; it++) {
+            const bool valid = it * nt + (int) threadIdx.x < D;
+            const float v = valid ? __fsub_rn(x[k][it], mean[k]) : 0.0f;
+            x[k][it] = v; s2[k] += (double) __fmul_rn(v, v);
+        }
+#pragma unroll
+    for (int k = 0; k < 2; k++) { s2[k] = warp_sum_d(s2[k]); if (lane == 0) red[2 + k][warp] = s2[k]; }
+    __syncthreads();
+    float scale[2];
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const double t = warp_sum_d(lane < nw ? red[2 + k][lane] : 0.0);
+        scale[k] = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn((float) (t / D), 1e-5f)));
+    }
+    // ---- affine, shift state, mixes ----
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * nt + threadIdx.x;
+        const bool valid = e < D;
+        const float x0 = __fadd_rn(__fmul_rn(__fmul_rn(x[0][it], scale[0]), w[it]), bia[it]);
+        float xp = xs[it];                                   // state value ...
+        if (nrow == 2) xp = __fadd_rn(__fmul_rn(__fmul_rn(x[1][it], scale[1]), w[it]), bia[it]);   // ... or LN(x[r-1])
+        const float sx = __fsub_rn(xp, x0);
+        if (valid && (a.batch || r == a.R - 1)) a.state_out[soff + e] = x0;
+        if (valid && a.x0) a.x0[(size_t) r * D + e] = x0;
+        if (valid && a.sx) a.sx[(size_t) r * D + e] = sx;
+        float v[NOUT];
+#pragma unroll
+        for (int o = 0; o < NOUT; o++) {
+            if (a.kind == MIX_LERP) v[o] = __fadd_rn(__fmul_rn(x0, mu[o][it]), __fsub_rn(xp, __fmul_rn(xp, mu[o][it])));
+            else                    v[o] = __fadd_rn(__fmul_rn(sx, mu[o][it]), x0);
+        }
+        act_store_blocks<NOUT>(a.out, (size_t) r, e, valid, v);
+    }
+}
+
+template <int ITEMS>
+static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_t st) {
+    switch (a.n_out) {
+        case 1: ln_mix_kernel<ITEMS, 1><<<a.R, threads, 0, st>>>(a); break;
+        case 2: ln_mix_kernel<ITEMS, 2><<<a.R, threads, 0, st>>>(a); break;
+        case 3: ln_mix_kernel<ITEMS, 3><<<a.R, threads, 0, st>>>(a); break;
+        case 4: ln_mix_kernel<ITEMS, 4><<<a.R, threads, 0, st>>>(a); break;
+        case 6: ln_mix_kernel<ITEMS, 6><<<a.R, threads, 0, st>>>(a); break;
+        default: return cudaErrorInvalidValue;
+    }
     return cudaGetLastError();
+}
+
+cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
+    const int items = a.D <= 1024 ? 1 : a.D <= 2048 ? 2 : a.D <= 4096 ? 4 : 8;
+    if (a.D > 8192) return cudaErrorInvalidValue;
+    const int threads = (((a.D + items - 1) / items) + 31) / 32 * 32;
+    switch (items) {
+        case 1: return launch_ln_mix_i<1>(a, threads, st);
+        case 2: return launch_ln_mix_i<2>(a, threads, st);
+        case 4: return launch_ln_mix_i<4>(a, threads, st);
+        default: return launch_ln_mix_i<8>(a, threads, st);
+    }
 }
 
 __global__ void __launch_bounds__(256) ln_act_kernel(const float * __restrict__ x, int ldx, int D, const float * __restrict__ w,

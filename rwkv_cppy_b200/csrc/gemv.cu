@@ -17,98 +17,15 @@
 // the roofline is bytes(W)/t against the measured copy bandwidth.
 // A CTA owning 32 consecutive outputs can quantise them for the next mat-vec in its
 // epilogue (one q8 block per column), so chained products need no extra launch.
-#include "device_utils.cuh"
+#include "gemv_common.cuh"
 
 namespace rb {
+
+cudaError_t launch_gemv_async(const GemvBatch & b, int total_ctas, cudaStream_t st);
 
 constexpr int GEMV_WARPS = 8;
 constexpr int GEMV_R     = 4;                       // rows per warp
 constexpr int GEMV_ROWS  = GEMV_WARPS * GEMV_R;     // 32 rows per CTA = one q8 block of outputs
-
-__device__ __forceinline__ int dp4a_(int a, int b, int c) { return __dp4a(a, b, c); }
-
-// ---- per-type inner products -------------------------------------------------------------
-template <int TYPE, int NCOL>
-struct RowAcc {
-    float acc[NCOL];
-    float summ[NCOL];     // m_w * s_x sums (Q4_1 / Q5_1)
-    __device__ __forceinline__ void clear() {
-#pragma unroll
-        for (int c = 0; c < NCOL; c++) { acc[c] = 0.0f; summ[c] = 0.0f; }
-    }
-};
-
-template <int NCOL>
-struct XBlock {             // the q8 activation block of NCOL columns held by one lane
-    int   w[NCOL][8];
-    float d[NCOL];
-    float s[NCOL];          // q8_1: s ; q8_0 offset formats: (float) isum is not needed, keep int below
-    int   isum[NCOL];
-};
-
-template <int TYPE, int NCOL>
-__device__ __forceinline__ void load_xblock(XBlock<NCOL> & xb, const Act & x, int x_off, int col0, int T, int b) {
-#pragma unroll
-    for (int c = 0; c < NCOL; c++) {
-        const int t = min(col0 + c, T - 1);
-        const size_t e0 = (size_t) t * x.K + x_off + (size_t) b * 32;
-        const uint4 lo = *reinterpret_cast<const uint4 *>(x.q + e0);
-        const uint4 hi = *reinterpret_cast<const uint4 *>(x.q + e0 + 16);
-        xb.w[c][0] = lo.x; xb.w[c][1] = lo.y; xb.w[c][2] = lo.z; xb.w[c][3] = lo.w;
-        xb.w[c][4] = hi.x; xb.w[c][5] = hi.y; xb.w[c][6] = hi.z; xb.w[c][7] = hi.w;
-        const size_t bi = (size_t) t * (x.K >> 5) + (x_off >> 5) + b;
-        xb.d[c] = x.d[bi];
-        if (TYPE == T_Q4_1 || TYPE == T_Q5_1) xb.s[c] = x.s[bi];
-        if (TYPE == T_Q4_0 || TYPE == T_Q5_0) xb.isum[c] = x.isum[bi];
-    }
-}
-
-// one row x one block for all columns
-template <int TYPE, int NCOL>
-__device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<NCOL> & xb,
-                                          const uint4 q0, const uint4 q1, const uint32_t qh, const float dw, const float mw) {
-    int wv[8];
-    if (TYPE == T_Q8_0) {
-        wv[0] = q0.x; wv[1] = q0.y; wv[2] = q0.z; wv[3] = q0.w; wv[4] = q1.x; wv[5] = q1.y; wv[6] = q1.z; wv[7] = q1.w;
-    } else {
-        const uint32_t v[4] = {q0.x, q0.y, q0.z, q0.w};
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            uint32_t lo = v[i] & 0x0F0F0F0Fu, hi = (v[i] >> 4) & 0x0F0F0F0Fu;
-            if (TYPE == T_Q5_0 || TYPE == T_Q5_1) {
-                lo |= (qh << (4 - i)) & 0x10101010u;            // plane bit (8*j + i)     -> bit 4 of byte j
-                hi |= (qh >> i) & 0x10101010u;                  // plane bit (8*j + 4 + i) -> bit 4 of byte j
-            }
-            wv[i] = (int) lo; wv[4 + i] = (int) hi;
-        }
-    }
-#pragma unroll
-    for (int c = 0; c < NCOL; c++) {
-        int dp = 0;
-#pragma unroll
-        for (int i = 0; i < 8; i++) dp = dp4a_(wv[i], xb.w[c][i], dp);
-        if (TYPE == T_Q4_0) dp -= 8 * xb.isum[c];
-        if (TYPE == T_Q5_0) dp -= 16 * xb.isum[c];
-        ra.acc[c] = __fmaf_rn(__fmul_rn(dw, xb.d[c]), (float) dp, ra.acc[c]);
-        if (TYPE == T_Q4_1 || TYPE == T_Q5_1) ra.summ[c] = __fmaf_rn(mw, xb.s[c], ra.summ[c]);
-    }
-}
-
-__device__ __forceinline__ float apply_epilogue(const GemvJob & J, float y, int t, int m) {
-    switch (J.epi) {
-        case EPI_STORE:        return y;
-        case EPI_SIGMOID:      return sigmoidf_ref(y);
-        case EPI_RELU_SQ:      { const float r = fmaxf(y, 0.0f); return __fmul_rn(r, r); }
-        case EPI_SILU:         return siluf_ref(y);
-        case EPI_TANH:         return tanhf(y);
-        case EPI_ADD_TO:       return __fadd_rn(J.out[(size_t) t * J.ldo + m], y);
-        case EPI_MULADD_TO:    return __fadd_rn(J.out[(size_t) t * J.ldo + m], __fmul_rn(J.aux[(size_t) t * J.ld_aux + m], y));
-        case EPI_BIAS_SIGMOID: return sigmoidf_ref(__fadd_rn(y, J.vec[m]));
-        case EPI_V6_DECAY:     return expf(-expf(__fadd_rn(y, J.vec[m])));
-        case EPI_V7_DECAY:     return expf(__fmul_rn(sigmoidf_ref(__fadd_rn(y, J.vec[m])), -0.606531f));
-        default:               return y;
-    }
-}
 
 template <int TYPE, int NCOL>
 __global__ void __launch_bounds__(GEMV_WARPS * 32)
@@ -125,7 +42,8 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
 
     float res[GEMV_R][NCOL];
 
-    if constexpr (TYPE == T_F32 || TYPE == T_F16) {
+    {
+        static_assert(TYPE == T_F32 || TYPE == T_F16, "quantised types use gemv_async.cu");
         constexpr int VEC = (TYPE == T_F32) ? 4 : 8;
         float acc[GEMV_R][NCOL];
 #pragma unroll
@@ -195,43 +113,6 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
         for (int r = 0; r < GEMV_R; r++)
 #pragma unroll
             for (int c = 0; c < NCOL; c++) res[r][c] = warp_sum(acc[r][c]);
-    } else {
-        RowAcc<TYPE, NCOL> ra[GEMV_R];
-#pragma unroll
-        for (int r = 0; r < GEMV_R; r++) ra[r].clear();
-        const int nb = K >> 5;
-        constexpr bool HAS_M = (TYPE == T_Q4_1 || TYPE == T_Q5_1);
-        constexpr bool HAS_H = (TYPE == T_Q5_0 || TYPE == T_Q5_1);
-        constexpr int  QV    = (TYPE == T_Q8_0) ? 2 : 1;          // uint4 per block
-        const uint4 * qs = reinterpret_cast<const uint4 *>(J.W.qs);
-        for (int b = lane; b < nb; b += 32) {
-            uint4 q0[GEMV_R], q1[GEMV_R]; uint32_t qh[GEMV_R]; float dw[GEMV_R], mw[GEMV_R];
-#pragma unroll
-            for (int r = 0; r < GEMV_R; r++) {
-                const size_t blk = (size_t) min(row0 + r, M - 1) * nb + b;
-                q0[r] = qs[blk * QV];
-                q1[r] = (QV == 2) ? qs[blk * QV + 1] : make_uint4(0, 0, 0, 0);
-                qh[r] = HAS_H ? J.W.qh[blk] : 0u;
-                if (HAS_M) {
-                    const __half2 dm = reinterpret_cast<const __half2 *>(J.W.dm)[blk];
-                    dw[r] = __low2float(dm); mw[r] = __high2float(dm);
-                } else {
-                    dw[r] = __half2float(reinterpret_cast<const __half *>(J.W.dm)[blk]); mw[r] = 0.0f;
-                }
-            }
-            XBlock<NCOL> xb;
-            load_xblock<TYPE, NCOL>(xb, J.x, J.x_off, col0, T, b);
-#pragma unroll
-            for (int r = 0; r < GEMV_R; r++) dot_block<TYPE, NCOL>(ra[r], xb, q0[r], q1[r], qh[r], dw[r], mw[r]);
-        }
-#pragma unroll
-        for (int r = 0; r < GEMV_R; r++)
-#pragma unroll
-            for (int c = 0; c < NCOL; c++) {
-                float v = warp_sum(ra[r].acc[c]);
-                if (HAS_M) v = __fadd_rn(v, warp_sum(ra[r].summ[c]));
-                res[r][c] = v;
-            }
     }
 
     // ---- epilogue: lane (r*NCOL + c) finishes output (row0 + r, col0 + c) ------------------
@@ -274,23 +155,18 @@ static cudaError_t launch_typed(const GemvBatch & b, int total_ctas, cudaStream_
 cudaError_t launch_gemv(const GemvBatch & b_in, cudaStream_t st) {
     if (b_in.n_jobs == 0) return cudaSuccess;
     GemvBatch b = b_in;
+    const uint32_t type = b.job[0].W.type;
     int total = 0;
     for (int j = 0; j < b.n_jobs; j++) {
+        if (b.job[j].W.type != type) return cudaErrorInvalidValue;
         b.cta_begin[j] = total;
-        total += (b.job[j].W.M + GEMV_ROWS - 1) / GEMV_ROWS;
-        if (b.job[j].W.type != b.job[0].W.type) return cudaErrorInvalidValue;
+        total += ((int) b.job[j].W.M + GEMV_ROWS - 1) / GEMV_ROWS;
     }
     b.cta_begin[b.n_jobs] = total;
-    switch (b.job[0].W.type) {
-        case T_F32:  return launch_typed<T_F32>(b, total, st);
-        case T_F16:  return launch_typed<T_F16>(b, total, st);
-        case T_Q4_0: return launch_typed<T_Q4_0>(b, total, st);
-        case T_Q4_1: return launch_typed<T_Q4_1>(b, total, st);
-        case T_Q5_0: return launch_typed<T_Q5_0>(b, total, st);
-        case T_Q5_1: return launch_typed<T_Q5_1>(b, total, st);
-        case T_Q8_0: return launch_typed<T_Q8_0>(b, total, st);
-        default:     return cudaErrorInvalidValue;
-    }
+    if (type_quantized(type)) return launch_gemv_async(b, total, st);
+    if (type == T_F32) return launch_typed<T_F32>(b, total, st);
+    if (type == T_F16) return launch_typed<T_F16>(b, total, st);
+    return cudaErrorInvalidValue;
 }
 
 } // namespace rb

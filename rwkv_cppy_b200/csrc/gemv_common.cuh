@@ -1,0 +1,94 @@
+// Inner products and epilogues shared by the two mat-vec kernels (gemv.cu: register-staged,
+// any shape / FP16 / FP32; gemv_async.cu: bulk-async staged, quantised).  See gemv.cu for the
+// reference arithmetic these restate.
+#pragma once
+#include "device_utils.cuh"
+
+namespace rb {
+
+__device__ __forceinline__ int dp4a_(int a, int b, int c) { return __dp4a(a, b, c); }
+
+// ---- per-type inner products -------------------------------------------------------------
+template <int TYPE, int NCOL>
+struct RowAcc {
+    float acc[NCOL];
+    float summ[NCOL];     // m_w * s_x sums (Q4_1 / Q5_1)
+    __device__ __forceinline__ void clear() {
+#pragma unroll
+        for (int c = 0; c < NCOL; c++) { acc[c] = 0.0f; summ[c] = 0.0f; }
+    }
+};
+
+template <int NCOL>
+struct XBlock {             // the q8 activation block of NCOL columns held by one lane
+    int   w[NCOL][8];
+    float d[NCOL];
+    float s[NCOL];          // q8_1: s ; q8_0 offset formats: (float) isum is not needed, keep int below
+    int   isum[NCOL];
+};
+
+template <int TYPE, int NCOL>
+__device__ __forceinline__ void load_xblock(XBlock<NCOL> & xb, const Act & x, int x_off, int col0, int T, int b) {
+#pragma unroll
+    for (int c = 0; c < NCOL; c++) {
+        const int t = min(col0 + c, T - 1);
+        const size_t e0 = (size_t) t * x.K + x_off + (size_t) b * 32;
+        const uint4 lo = *reinterpret_cast<const uint4 *>(x.q + e0);
+        const uint4 hi = *reinterpret_cast<const uint4 *>(x.q + e0 + 16);
+        xb.w[c][0] = lo.x; xb.w[c][1] = lo.y; xb.w[c][2] = lo.z; xb.w[c][3] = lo.w;
+        xb.w[c][4] = hi.x; xb.w[c][5] = hi.y; xb.w[c][6] = hi.z; xb.w[c][7] = hi.w;
+        const size_t bi = (size_t) t * (x.K >> 5) + (x_off >> 5) + b;
+        xb.d[c] = x.d[bi];
+        if (TYPE == T_Q4_1 || TYPE == T_Q5_1) xb.s[c] = x.s[bi];
+        if (TYPE == T_Q4_0 || TYPE == T_Q5_0) xb.isum[c] = x.isum[bi];
+    }
+}
+
+// one row x one block for all columns
+template <int TYPE, int NCOL>
+__device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<NCOL> & xb,
+                                          const uint4 q0, const uint4 q1, const uint32_t qh, const float dw, const float mw) {
+    int wv[8];
+    if (TYPE == T_Q8_0) {
+        wv[0] = q0.x; wv[1] = q0.y; wv[2] = q0.z; wv[3] = q0.w; wv[4] = q1.x; wv[5] = q1.y; wv[6] = q1.z; wv[7] = q1.w;
+    } else {
+        const uint32_t v[4] = {q0.x, q0.y, q0.z, q0.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            uint32_t lo = v[i] & 0x0F0F0F0Fu, hi = (v[i] >> 4) & 0x0F0F0F0Fu;
+            if (TYPE == T_Q5_0 || TYPE == T_Q5_1) {
+                lo |= (qh << (4 - i)) & 0x10101010u;            // plane bit (8*j + i)     -> bit 4 of byte j
+                hi |= (qh >> i) & 0x10101010u;                  // plane bit (8*j + 4 + i) -> bit 4 of byte j
+            }
+            wv[i] = (int) lo; wv[4 + i] = (int) hi;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NCOL; c++) {
+        int dp = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) dp = dp4a_(wv[i], xb.w[c][i], dp);
+        if (TYPE == T_Q4_0) dp -= 8 * xb.isum[c];
+        if (TYPE == T_Q5_0) dp -= 16 * xb.isum[c];
+        ra.acc[c] = __fmaf_rn(__fmul_rn(dw, xb.d[c]), (float) dp, ra.acc[c]);
+        if (TYPE == T_Q4_1 || TYPE == T_Q5_1) ra.summ[c] = __fmaf_rn(mw, xb.s[c], ra.summ[c]);
+    }
+}
+
+__device__ __forceinline__ float apply_epilogue(const GemvJob & J, float y, int t, int m) {
+    switch (J.epi) {
+        case EPI_STORE:        return y;
+        case EPI_SIGMOID:      return sigmoidf_ref(y);
+        case EPI_RELU_SQ:      { const float r = fmaxf(y, 0.0f); return __fmul_rn(r, r); }
+        case EPI_SILU:         return siluf_ref(y);
+        case EPI_TANH:         return tanhf(y);
+        case EPI_ADD_TO:       return __fadd_rn(J.out[(size_t) t * J.ldo + m], y);
+        case EPI_MULADD_TO:    return __fadd_rn(J.out[(size_t) t * J.ldo + m], __fmul_rn(J.aux[(size_t) t * J.ld_aux + m], y));
+        case EPI_BIAS_SIGMOID: return sigmoidf_ref(__fadd_rn(y, J.vec[m]));
+        case EPI_V6_DECAY:     return expf(-expf(__fadd_rn(y, J.vec[m])));
+        case EPI_V7_DECAY:     return expf(__fmul_rn(sigmoidf_ref(__fadd_rn(y, J.vec[m])), -0.606531f));
+        default:               return y;
+    }
+}
+
+} // namespace rb

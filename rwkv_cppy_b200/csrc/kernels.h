@@ -49,20 +49,22 @@ struct GemvJob {
 constexpr int GEMV_MAX_JOBS = 8;
 struct GemvBatch {
     GemvJob job[GEMV_MAX_JOBS];
-    int     cta_begin[GEMV_MAX_JOBS + 1];   // prefix sum of CTAs per job (32 rows per CTA)
+    int     cta_begin[GEMV_MAX_JOBS + 1];   // prefix sum of CTAs per job (filled by launch_gemv)
     int     n_jobs = 0;
     int     T = 1;
 };
 
 // All jobs of a batch must have the same weight type.
 cudaError_t launch_gemv(const GemvBatch & b, cudaStream_t st);
+// once per device, outside stream capture (opts the bulk-async kernel in to > 48 KB shared memory)
+cudaError_t gemv_async_init();
 
 // ---- codec -----------------------------------------------------------------------------
-// raw ggml blocks (device copy of the file bytes) -> plane layout
-cudaError_t launch_repack(uint32_t type, const uint8_t * raw, size_t n_blocks, void * qs, uint32_t * qh, void * dm, cudaStream_t st);
-// plane layout -> FP32 [M][K]; bit-exact dequantize_row_* (ggml-quants.c:255-363)
+// raw ggml rows (device copy of the file bytes, M x K) -> warp-tile layout (tiled_bytes(type, M, K) bytes at `out`)
+cudaError_t launch_repack(uint32_t type, const uint8_t * raw, size_t M, size_t K, void * out, cudaStream_t st);
+// device layout -> FP32 [M][K]; bit-exact dequantize_row_* (ggml-quants.c:255-363)
 cudaError_t launch_dequant(const DevMat & W, float * out, cudaStream_t st);
-// plane layout -> FP16 [M][K] (operand of the tensor-core sequence GEMM)
+// device layout -> FP16 [M][K] (operand of the tensor-core sequence GEMM)
 cudaError_t launch_dequant_f16(const DevMat & W, void * out_half, cudaStream_t st);
 
 // ---- embedding + ln0 --------------------------------------------------------------------

@@ -98,16 +98,13 @@ struct Loader {
             out.qs = d;
             return true;
         }
-        const bool has_h = (t->type == T_Q5_0 || t->type == T_Q5_1), has_m = (t->type == T_Q4_1 || t->type == T_Q5_1);
-        void * qs = bump(n_blocks * (t->type == T_Q8_0 ? 32 : 16));
-        uint32_t * qh = has_h ? (uint32_t *) bump(n_blocks * 4) : nullptr;
-        void * dm = bump(n_blocks * (has_m ? 4 : 2));
-        if (!qs || !dm || (has_h && !qh)) return false;
+        void * tiled = bump(tiled_bytes(t->type, M, K));
+        if (!tiled) return false;
         if (nbytes > scratch_size) { ok = false; return false; }
         if (cudaMemcpyAsync(scratch, src, nbytes, cudaMemcpyHostToDevice, st) != cudaSuccess) { ok = false; return false; }
-        if (launch_repack(t->type, scratch, n_blocks, qs, qh, dm, st) != cudaSuccess) { ok = false; return false; }
+        if (launch_repack(t->type, scratch, M, K, tiled, st) != cudaSuccess) { ok = false; return false; }
         if (cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
-        out.qs = qs; out.qh = qh; out.dm = dm;
+        out.qs = tiled; out.rg_stride = (uint32_t) tiled_rg_stride(t->type, K);
         return true;
     }
 
@@ -165,6 +162,7 @@ Model * model_load(const char * path) {
     for (const FileTensor & t : f.tensors) {
         const size_t as_vec = t.n_elements() * 4;
         arena += std::max(t.nbytes, t.n_dims == 2 ? t.nbytes : as_vec) + 4 * 256;
+        if (type_quantized(t.type)) arena += TILE_ROWS * (t.ne[0] / 32) * type_block_bytes(t.type) + 64;   // row padding of the tiled layout
         if (type_quantized(t.type)) scratch = std::max(scratch, t.nbytes);
     }
     RB_CUDA(cudaMalloc((void **) &L.arena, arena), RWKV_ERROR_MODEL | RWKV_ERROR_ALLOC, nullptr);
@@ -175,6 +173,7 @@ Model * model_load(const char * path) {
         L.scratch_size = scratch;
     }
     RB_CUDA(cudaStreamCreate(&L.st), RWKV_ERROR_MODEL | RWKV_ERROR_ALLOC, nullptr);
+    RB_CUDA(gemv_async_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
 
     const size_t D = m.n_embed, V = m.n_vocab;
     L.mat("emb.weight", D, V, m.emb);
