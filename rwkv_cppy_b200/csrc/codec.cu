@@ -14,6 +14,7 @@
 //     plane bit (8*i + w)  =  file bit (4*w + i)        w = 0..7, i = 0..3
 // and `(qh >> w) & 0x01010101` yields the four 5th bits of word w at byte LSBs.
 #include "device_utils.cuh"
+#include "launch.cuh"
 
 namespace rb {
 
@@ -137,6 +138,8 @@ __global__ void embed_ln0_kernel(DevMat emb, const int * __restrict__ tokens, co
     __shared__ double red[32];
     __shared__ float  tmp_unused;
     (void) tmp_unused;
+    pdl_trigger();
+    pdl_wait();
     const int t = blockIdx.x, D = emb.K;
     const int tok = tokens[t];
     float * raw = smem + D;          // second half: gathered row
@@ -147,6 +150,8 @@ __global__ void embed_ln0_kernel(DevMat emb, const int * __restrict__ tokens, co
 }
 
 cudaError_t launch_embed_ln0(const DevMat & emb, const int * tokens, int T, const float * w, const float * b, float * x, cudaStream_t st) {
+    // Plain stream-ordered launch on purpose: the first kernel of a pass is a full fence, so nothing of
+    // this pass (which may prefetch the input state before its pdl_wait) overlaps the previous pass.
     embed_ln0_kernel<<<T, 256, 2 * emb.K * sizeof(float), st>>>(emb, tokens, w, b, x);
     return cudaGetLastError();
 }

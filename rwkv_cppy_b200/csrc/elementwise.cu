@@ -8,6 +8,7 @@
 //   v6 mixes                   rwkv_graph.inc:301-336         x + (xp-x)*(maa + m)
 //   v7 mixes                   rwkv_graph.inc:395-404         x + (xp-x)*mu
 #include "device_utils.cuh"
+#include "launch.cuh"
 
 namespace rb {
 
@@ -60,17 +61,25 @@ __global__ void __launch_bounds__(1024) ln_mix_kernel(const __grid_constant__ Ln
     const bool from_state = a.batch || r == 0;
     const size_t soff = a.batch ? (size_t) r * a.state_stride : 0;
 
+    pdl_trigger();
     float x[2][ITEMS], xs[ITEMS], w[ITEMS], bia[ITEMS], mu[NOUT][ITEMS];
+    // constants and the (read-only) input state first, then wait for the producer of x
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * nt + threadIdx.x;
+        const bool valid = e < D;
+        xs[it] = (valid && from_state) ? a.state_in[soff + e] : 0.0f;
+        w[it] = valid ? a.ln_w[e] : 0.0f; bia[it] = valid ? a.ln_b[e] : 0.0f;
+#pragma unroll
+        for (int o = 0; o < NOUT; o++) mu[o][it] = valid ? a.mu[o][e] : 0.0f;
+    }
+    pdl_wait();
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
         const int e = it * nt + threadIdx.x;
         const bool valid = e < D;
         x[0][it] = valid ? a.x[(size_t) r * D + e] : 0.0f;
-        x[1][it] = !valid ? 0.0f : from_state ? a.state_in[soff + e] : a.x[(size_t) (r - 1) * D + e];
-        xs[it] = x[1][it];                                   // untouched copy: the shift value when it comes from the state
-        w[it] = valid ? a.ln_w[e] : 0.0f; bia[it] = valid ? a.ln_b[e] : 0.0f;
-#pragma unroll
-        for (int o = 0; o < NOUT; o++) mu[o][it] = valid ? a.mu[o][e] : 0.0f;
+        x[1][it] = (valid && !from_state) ? a.x[(size_t) (r - 1) * D + e] : 0.0f;
     }
     const int nrow = from_state ? 1 : 2;                     // rows to normalise (uniform per CTA)
     // ---- mean (double accumulation as ggml_compute_forward_norm_f32) ----
@@ -129,14 +138,13 @@ __global__ void __launch_bounds__(1024) ln_mix_kernel(const __grid_constant__ Ln
 template <int ITEMS>
 static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_t st) {
     switch (a.n_out) {
-        case 1: ln_mix_kernel<ITEMS, 1><<<a.R, threads, 0, st>>>(a); break;
-        case 2: ln_mix_kernel<ITEMS, 2><<<a.R, threads, 0, st>>>(a); break;
-        case 3: ln_mix_kernel<ITEMS, 3><<<a.R, threads, 0, st>>>(a); break;
-        case 4: ln_mix_kernel<ITEMS, 4><<<a.R, threads, 0, st>>>(a); break;
-        case 6: ln_mix_kernel<ITEMS, 6><<<a.R, threads, 0, st>>>(a); break;
+        case 1: return launch_pdl(ln_mix_kernel<ITEMS, 1>, dim3(a.R), dim3(threads), 0, st, a);
+        case 2: return launch_pdl(ln_mix_kernel<ITEMS, 2>, dim3(a.R), dim3(threads), 0, st, a);
+        case 3: return launch_pdl(ln_mix_kernel<ITEMS, 3>, dim3(a.R), dim3(threads), 0, st, a);
+        case 4: return launch_pdl(ln_mix_kernel<ITEMS, 4>, dim3(a.R), dim3(threads), 0, st, a);
+        case 6: return launch_pdl(ln_mix_kernel<ITEMS, 6>, dim3(a.R), dim3(threads), 0, st, a);
         default: return cudaErrorInvalidValue;
     }
-    return cudaGetLastError();
 }
 
 cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
@@ -156,6 +164,8 @@ __global__ void __launch_bounds__(256) ln_act_kernel(const float * __restrict__ 
     extern __shared__ float smem[];
     __shared__ double red[32];
     const int r = blockIdx.x;
+    pdl_trigger();
+    pdl_wait();
     block_layer_norm(x + (size_t) r * ldx, D, w, b, 1e-5f, smem, red);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     for (int e0 = warp * 32; e0 < D; e0 += nw * 32) {
@@ -165,11 +175,12 @@ __global__ void __launch_bounds__(256) ln_act_kernel(const float * __restrict__ 
 }
 
 cudaError_t launch_ln_act(const float * x, int ldx, int R, int D, const float * w, const float * b, Act out, cudaStream_t st) {
-    ln_act_kernel<<<R, 256, D * sizeof(float), st>>>(x, ldx, D, w, b, out);
-    return cudaGetLastError();
+    return launch_pdl(ln_act_kernel, dim3(R), dim3(256), D * sizeof(float), st, x, ldx, D, w, b, out);
 }
 
 __global__ void __launch_bounds__(256) v6_mix2_kernel(const __grid_constant__ V6Mix2Args a) {
+    pdl_trigger();
+    pdl_wait();
     const int r = blockIdx.x, D = a.D;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     for (int e0 = warp * 32; e0 < D; e0 += nw * 32) {
@@ -187,11 +198,12 @@ __global__ void __launch_bounds__(256) v6_mix2_kernel(const __grid_constant__ V6
 }
 
 cudaError_t launch_v6_mix2(const V6Mix2Args & a, cudaStream_t st) {
-    v6_mix2_kernel<<<a.R, 256, 0, st>>>(a);
-    return cudaGetLastError();
+    return launch_pdl(v6_mix2_kernel, dim3(a.R), dim3(256), 0, st, a);
 }
 
 __global__ void __launch_bounds__(256) quantize_act_kernel(Act a) {
+    pdl_trigger();
+    pdl_wait();
     const int r = blockIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     for (int e0 = warp * 32; e0 < a.K; e0 += nw * 32) {
@@ -203,8 +215,7 @@ __global__ void __launch_bounds__(256) quantize_act_kernel(Act a) {
 
 cudaError_t launch_quantize_act(Act a, int R, cudaStream_t st) {
     if (a.q == nullptr) return cudaSuccess;
-    quantize_act_kernel<<<R, 256, 0, st>>>(a);
-    return cudaGetLastError();
+    return launch_pdl(quantize_act_kernel, dim3(R), dim3(256), 0, st, a);
 }
 
 } // namespace rb

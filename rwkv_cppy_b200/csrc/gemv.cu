@@ -18,6 +18,7 @@
 // A CTA owning 32 consecutive outputs can quantise them for the next mat-vec in its
 // epilogue (one q8 block per column), so chained products need no extra launch.
 #include "gemv_common.cuh"
+#include "launch.cuh"
 
 namespace rb {
 
@@ -30,6 +31,7 @@ constexpr int GEMV_ROWS  = GEMV_WARPS * GEMV_R;     // 32 rows per CTA = one q8 
 template <int TYPE, int NCOL>
 __global__ void __launch_bounds__(GEMV_WARPS * 32)
 gemv_kernel(const __grid_constant__ GemvBatch B) {
+    pdl_trigger();
     // which job / row block
     int j = 0;
 #pragma unroll 1
@@ -41,6 +43,15 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
     const int col0 = blockIdx.y * NCOL;
 
     float res[GEMV_R][NCOL];
+    {   // pull the head of this warp's rows towards L2 while the producer of x is still running
+        const size_t esz = (TYPE == T_F32) ? 4 : 2;
+#pragma unroll
+        for (int r = 0; r < GEMV_R; r++) {
+            const char * p = reinterpret_cast<const char *>(J.W.qs) + (size_t) min(row0 + r, M - 1) * K * esz + (size_t) lane * 128;
+            if ((size_t) lane * 128 < (size_t) K * esz) asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+        }
+    }
+    pdl_wait();
 
     {
         static_assert(TYPE == T_F32 || TYPE == T_F16, "quantised types use gemv_async.cu");
@@ -145,11 +156,10 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
 template <int TYPE>
 static cudaError_t launch_typed(const GemvBatch & b, int total_ctas, cudaStream_t st) {
     const dim3 block(GEMV_WARPS * 32);
-    if (b.T == 1)      gemv_kernel<TYPE, 1><<<dim3(total_ctas, 1), block, 0, st>>>(b);
-    else if (b.T == 2) gemv_kernel<TYPE, 2><<<dim3(total_ctas, 1), block, 0, st>>>(b);
-    else if (b.T <= 4) gemv_kernel<TYPE, 4><<<dim3(total_ctas, 1), block, 0, st>>>(b);
-    else               gemv_kernel<TYPE, 8><<<dim3(total_ctas, (b.T + 7) / 8), block, 0, st>>>(b);
-    return cudaGetLastError();
+    if (b.T == 1)      return launch_pdl(gemv_kernel<TYPE, 1>, dim3(total_ctas, 1), block, 0, st, b);
+    else if (b.T == 2) return launch_pdl(gemv_kernel<TYPE, 2>, dim3(total_ctas, 1), block, 0, st, b);
+    else if (b.T <= 4) return launch_pdl(gemv_kernel<TYPE, 4>, dim3(total_ctas, 1), block, 0, st, b);
+    else               return launch_pdl(gemv_kernel<TYPE, 8>, dim3(total_ctas, (b.T + 7) / 8), block, 0, st, b);
 }
 
 cudaError_t launch_gemv(const GemvBatch & b_in, cudaStream_t st) {

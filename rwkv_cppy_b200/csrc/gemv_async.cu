@@ -16,6 +16,7 @@
 // block of its 32 outputs for a chained mat-vec.  Per output the FP32 summation order is
 // lane-strided over K + butterfly: it depends on K only, never on T or the grid.
 #include "gemv_common.cuh"
+#include "launch.cuh"
 
 namespace rb {
 
@@ -64,6 +65,7 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     extern __shared__ __align__(128) uint8_t ga_smem[];
     __shared__ float tile[NCOL][GA_WARPS * GA_R];
 
+    pdl_trigger();
     int j = 0;
 #pragma unroll 1
     while (j + 1 < B.n_jobs && (int) blockIdx.x >= B.cta_begin[j + 1]) j++;
@@ -95,6 +97,7 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
         }
     }
     __syncwarp();
+    pdl_wait();                                         // activations (and the residual) come from the preceding kernels
 
     RowAcc<TYPE, NCOL> ra[GA_R];
 #pragma unroll
@@ -165,8 +168,7 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
 
 template <int TYPE, int NCOL>
 static cudaError_t launch_async_n(const GemvBatch & b, int total_ctas, int ygrid, cudaStream_t st) {
-    gemv_async_kernel<TYPE, NCOL><<<dim3(total_ctas, ygrid), GA_WARPS * 32, ga_smem_bytes<TYPE>(), st>>>(b);
-    return cudaGetLastError();
+    return launch_pdl(gemv_async_kernel<TYPE, NCOL>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE>(), st, b);
 }
 
 template <int TYPE>

@@ -1,0 +1,41 @@
+// Programmatic dependent launch (PDL) plumbing.
+//
+// Every kernel of the forward pass is launched with the programmatic-stream-serialization
+// attribute and follows one protocol:
+//   pdl_trigger()  first thing: the NEXT kernel in the stream may start its prologue now;
+//   ... prologue that touches only constants (weights, norm vectors) and the read-only
+//       input state: bulk-copy / prefetch them ...
+//   pdl_wait()     before the first access to anything a preceding kernel writes, and before
+//                  the first global write.
+// So a mat-vec streams its first weight tiles while the producer of its activations is
+// still running, and the tail of one kernel overlaps the fill of the next.  pdl_wait()
+// returns when the preceding kernel has completed and flushed; since every kernel waits
+// before it finishes, completion is transitive along the stream.  Captured into the CUDA
+// graphs as programmatic edges.  RWKV_B200_NO_PDL=1 falls back to plain stream order.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdlib>
+#include <utility>
+
+namespace rb {
+
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+    static const bool on = [] { const char * e = getenv("RWKV_B200_NO_PDL"); return !(e && e[0] == '1'); }();
+    return on;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
+} // namespace rb

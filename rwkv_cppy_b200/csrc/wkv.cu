@@ -11,6 +11,7 @@
 // Rows are either T consecutive tokens of one stream (the scan runs inside the kernel,
 // state held in registers) or B independent streams (one step each).
 #include "device_utils.cuh"
+#include "launch.cuh"
 
 namespace rb {
 
@@ -18,6 +19,7 @@ namespace rb {
 // v4: one thread per channel.
 // ----------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvArgs a) {
+    pdl_trigger();
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     const int D = a.D;
     const bool valid = e < D;
@@ -28,6 +30,7 @@ __global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvAr
         aa = a.state_in[soff + e]; bb = a.state_in[soff + D + e]; pp = a.state_in[soff + 2 * D + e];
         u = a.u[e]; w = a.decay[e];
     }
+    pdl_wait();                                 // r, k, v come from the preceding mat-vec; the input state is read-only
     const int steps = a.batch ? 1 : a.R;
     for (int s = 0; s < steps; s++) {
         const size_t row = a.batch ? stream : s;
@@ -54,8 +57,7 @@ __global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvAr
 
 cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st) {
     dim3 grid((a.D + 255) / 256, a.batch ? a.R : 1);
-    wkv4_kernel<<<grid, 256, 0, st>>>(a);
-    return cudaGetLastError();
+    return launch_pdl(wkv4_kernel, grid, dim3(256), 0, st, a);
 }
 
 // Per-head normalisation of `y` over the S threads of a head (ggml norm: double sums).
@@ -87,6 +89,7 @@ __device__ __forceinline__ float head_norm(float y, float * sy, int tid, bool ac
 template <int S>
 __global__ void wkv5_kernel(const __grid_constant__ WkvArgs a) {
     extern __shared__ float sm[];
+    pdl_trigger();
     const int nthr = blockDim.x;
     float * sr = sm, * sk = sm + nthr, * sw = sm + 2 * nthr, * su = sm + 3 * nthr, * sy = sm + 4 * nthr;
     const int tid = threadIdx.x;
@@ -105,6 +108,7 @@ __global__ void wkv5_kernel(const __grid_constant__ WkvArgs a) {
         su[tid] = a.per_head_scalar ? a.u[h] : a.u[e];
         if (a.w == nullptr) sw[tid] = a.per_head_scalar ? a.decay[h] : a.decay[e];
     }
+    pdl_wait();
     const int steps = a.batch ? 1 : a.R;
     for (int s = 0; s < steps; s++) {
         const size_t row = a.batch ? stream : s;
@@ -143,8 +147,7 @@ static cudaError_t launch_wkv5_t(const WkvArgs & a, cudaStream_t st) {
     const int hpb = S >= 32 ? 1 : 32 / S;
     const int threads = ((hpb * S + 31) / 32) * 32;
     dim3 grid((a.H + hpb - 1) / hpb, a.batch ? a.R : 1);
-    wkv5_kernel<S><<<grid, threads, 5 * threads * sizeof(float), st>>>(a);
-    return cudaGetLastError();
+    return launch_pdl(wkv5_kernel<S>, grid, dim3(threads), 5 * threads * sizeof(float), st, a);
 }
 
 cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st) {
@@ -164,6 +167,7 @@ cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st) {
 template <int S>
 __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
     extern __shared__ float sm[];
+    pdl_trigger();
     const int nthr = blockDim.x;
     float * s_a = sm, * s_b = sm + nthr, * s_k = sm + 2 * nthr, * s_w = sm + 3 * nthr, * s_r = sm + 4 * nthr, * sy = sm + 5 * nthr;
     const int tid = threadIdx.x;
@@ -183,6 +187,7 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
         for (int j = 0; j < S / 4; j++) { const float4 f = p[j]; st[4 * j] = f.x; st[4 * j + 1] = f.y; st[4 * j + 2] = f.z; st[4 * j + 3] = f.w; }
         kkc = a.k_k[e]; kac = a.k_a[e]; rkc = a.r_k[e]; lw = a.lnx_w[e]; lb = a.lnx_b[e];
     }
+    pdl_wait();
     const int steps = a.batch ? 1 : a.R;
     for (int s = 0; s < steps; s++) {
         const size_t row = a.batch ? stream : s;
@@ -242,8 +247,7 @@ static cudaError_t launch_wkv7_t(const WkvArgs & a, cudaStream_t st) {
     const int hpb = S >= 32 ? 1 : 32 / S;
     const int threads = ((hpb * S + 31) / 32) * 32;
     dim3 grid((a.H + hpb - 1) / hpb, a.batch ? a.R : 1);
-    wkv7_kernel<S><<<grid, threads, 6 * threads * sizeof(float), st>>>(a);
-    return cudaGetLastError();
+    return launch_pdl(wkv7_kernel<S>, grid, dim3(threads), 6 * threads * sizeof(float), st, a);
 }
 
 cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st) {
