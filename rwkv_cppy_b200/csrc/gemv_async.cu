@@ -17,6 +17,7 @@
 // lane-strided over K + butterfly: it depends on K only, never on T or the grid.
 #include "gemv_common.cuh"
 #include "launch.cuh"
+#include <cstdlib>
 
 namespace rb {
 
@@ -30,7 +31,7 @@ template <> struct QFmt<T_Q5_1> { static constexpr int QB = 16, HB = 4, DB = 4, 
 template <> struct QFmt<T_Q8_0> { static constexpr int QB = 32, HB = 0, DB = 2, STAGES = 3; };
 
 template <int TYPE> __host__ __device__ constexpr int ga_stage_bytes() { return GA_R * GA_KC * (QFmt<TYPE>::QB + QFmt<TYPE>::HB + QFmt<TYPE>::DB); }
-template <int TYPE> __host__ __device__ constexpr int ga_smem_bytes() { return GA_WARPS * QFmt<TYPE>::STAGES * (ga_stage_bytes<TYPE>() + 8); }
+template <int TYPE, int S> __host__ __device__ constexpr int ga_smem_bytes() { return GA_WARPS * S * (ga_stage_bytes<TYPE>() + 8); }
 
 // ---- PTX wrappers ------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -54,14 +55,62 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_
                  :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+// Per-lane cursors into the q8 activation rows (block `lane` of column col0); hoisted out of
+// the chunk loop so an iteration costs one add per pointer.
 template <int TYPE, int NCOL>
-__global__ void __launch_bounds__(GA_WARPS * 32)
+struct XCursor {
+    const int8_t * q; const float * d; const float * s; const int * isum;
+    int K, nbrow, tmax;
+    __device__ __forceinline__ void init(const Act & x, int x_off, int col0, int T, int lane) {
+        K = x.K; nbrow = x.K >> 5; tmax = T - 1 - col0;
+        q = x.q + (size_t) col0 * K + x_off + lane * 32;
+        const size_t b0 = (size_t) col0 * nbrow + (x_off >> 5) + lane;
+        d = x.d + b0; s = x.s + b0; isum = x.isum + b0;
+    }
+    // Fire-and-forget loads of this lane's share of chunks [0, nch): pulls the whole activation
+    // row into L1 in one round trip.  Under a saturated L2 a dependent load per chunk costs a
+    // microsecond each; this way the later load() calls hit L1 (or merge with the miss in flight).
+    __device__ __forceinline__ void warm(int nch, int nb, int lane) const {
+#pragma unroll
+        for (int cc = 0; cc < NCOL; cc++) {
+            const int dt = NCOL == 1 ? 0 : min(cc, tmax);
+#pragma unroll 1
+            for (int c = 0; c < nch; c++) {
+                if (c * GA_KC + lane < nb) {
+                    uint32_t t0, t1;
+                    asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t0) : "l"(q + (size_t) dt * K + c * (GA_KC * 32)));
+                    asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t1) : "l"(d + dt * nbrow + c * GA_KC));
+                    if (TYPE == T_Q4_1 || TYPE == T_Q5_1) asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t1) : "l"(s + dt * nbrow + c * GA_KC));
+                    if (TYPE == T_Q4_0 || TYPE == T_Q5_0) asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t1) : "l"(isum + dt * nbrow + c * GA_KC));
+                }
+            }
+        }
+    }
+    __device__ __forceinline__ void load(XBlock<NCOL> & xb, int c) const {      // block c*32 + lane
+#pragma unroll
+        for (int cc = 0; cc < NCOL; cc++) {
+            const int dt = NCOL == 1 ? 0 : min(cc, tmax);
+            const int8_t * qp = q + (size_t) dt * K + c * (GA_KC * 32);
+            const uint4 lo = *reinterpret_cast<const uint4 *>(qp);
+            const uint4 hi = *reinterpret_cast<const uint4 *>(qp + 16);
+            xb.w[cc][0] = lo.x; xb.w[cc][1] = lo.y; xb.w[cc][2] = lo.z; xb.w[cc][3] = lo.w;
+            xb.w[cc][4] = hi.x; xb.w[cc][5] = hi.y; xb.w[cc][6] = hi.z; xb.w[cc][7] = hi.w;
+            const int bo = dt * nbrow + c * GA_KC;
+            xb.d[cc] = d[bo];
+            if (TYPE == T_Q4_1 || TYPE == T_Q5_1) xb.s[cc] = s[bo];
+            if (TYPE == T_Q4_0 || TYPE == T_Q5_0) xb.isum[cc] = isum[bo];
+        }
+    }
+};
+
+template <int TYPE, int NCOL, int S>
+__global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? (QFmt<TYPE>::QB == 32 ? 2 : 3) : (NCOL == 2 ? 2 : 1))
 gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     using F = QFmt<TYPE>;
-    constexpr int S = F::STAGES;
     constexpr int BB = F::QB + F::HB + F::DB;              // bytes per block
     constexpr int STAGE = ga_stage_bytes<TYPE>();
     constexpr bool HAS_M = (TYPE == T_Q4_1 || TYPE == T_Q5_1);
+    constexpr bool PREFETCH_X = (NCOL == 1);               // next chunk's activations one iteration ahead
     extern __shared__ __align__(128) uint8_t ga_smem[];
     __shared__ float tile[NCOL][GA_WARPS * GA_R];
 
@@ -78,8 +127,10 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     const int nch = row0 < M ? (nb + GA_KC - 1) / GA_KC : 0;     // warps past the last row stay idle
 
     uint8_t * my = ga_smem + (size_t) warp * S * STAGE;
+    const uint32_t my_s = smem_u32(my);
     const uint32_t bars = smem_u32(ga_smem + (size_t) GA_WARPS * S * STAGE) + warp * S * 8;
     const uint8_t * src0 = reinterpret_cast<const uint8_t *>(J.W.qs) + (size_t) (row0 / GA_R) * J.W.rg_stride;
+    const uint32_t last_bytes = (uint32_t) ((GA_R * (nb - (nch - 1) * GA_KC) * BB + 15) & ~15);
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < S; s++) mbar_init(bars + s * 8, 1);
@@ -89,13 +140,14 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
 #pragma unroll
         for (int s = 0; s < S; s++) {
             if (s < nch) {
-                const int cnt = min(GA_KC, nb - s * GA_KC);
-                const uint32_t bytes = (uint32_t) ((GA_R * cnt * BB + 15) & ~15);
+                const uint32_t bytes = (s == nch - 1) ? last_bytes : (uint32_t) STAGE;
                 mbar_expect_tx(bars + s * 8, bytes);
-                bulk_g2s(smem_u32(my + (size_t) s * STAGE), src0 + (size_t) s * GA_R * GA_KC * BB, bytes, bars + s * 8);
+                bulk_g2s(my_s + s * STAGE, src0 + (size_t) s * STAGE, bytes, bars + s * 8);
             }
         }
     }
+    XCursor<TYPE, NCOL> xc;
+    xc.init(J.x, J.x_off, col0, T, lane);
     __syncwarp();
     pdl_wait();                                         // activations (and the residual) come from the preceding kernels
 
@@ -103,37 +155,65 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
 #pragma unroll
     for (int r = 0; r < GA_R; r++) ra[r].clear();
 
+    XBlock<NCOL> xb, xn;
+    if (NCOL <= 2 && nch > 2) xc.warm(nch, nb, lane);
+    if (PREFETCH_X && nch > 0 && lane < min(GA_KC, nb)) xc.load(xb, 0);
+    int s = 0;
+    uint32_t phase = 0;
+#pragma unroll 1
     for (int c = 0; c < nch; c++) {
-        const int s = c % S;
         const int cnt = min(GA_KC, nb - c * GA_KC);
         const bool act = lane < cnt;
-        XBlock<NCOL> xb;
-        if (act) load_xblock<TYPE, NCOL>(xb, J.x, J.x_off, col0, T, c * GA_KC + lane);     // before the wait: independent of the tile
-        mbar_wait(bars + s * 8, (uint32_t) ((c / S) & 1));
+        if (PREFETCH_X) { if (c + 1 < nch && lane < nb - (c + 1) * GA_KC) xc.load(xn, c + 1); }
+        else if (act) xc.load(xb, c);                   // before the wait: independent of the tile
+        mbar_wait(bars + s * 8, phase);
+
+        // the warp's 4 rows x (this lane's block) from the stage into registers, then hand the
+        // stage back to the copy engine before doing the arithmetic
         const uint8_t * st = my + (size_t) s * STAGE;
-        if (act) {
+        uint4 q0[GA_R], q1[GA_R];
+        uint32_t qh[GA_R], dm[GA_R];
+        if (cnt == GA_KC) {
+            const uint8_t * pq = st + lane * F::QB;
+            const uint8_t * ph = st + GA_R * GA_KC * F::QB + lane * 4;
+            const uint8_t * pd = st + GA_R * GA_KC * (F::QB + F::HB) + lane * F::DB;
+#pragma unroll
+            for (int r = 0; r < GA_R; r++) {
+                q0[r] = *reinterpret_cast<const uint4 *>(pq + r * GA_KC * F::QB);
+                if (F::QB == 32) q1[r] = *reinterpret_cast<const uint4 *>(pq + r * GA_KC * F::QB + 16);
+                if (F::HB) qh[r] = *reinterpret_cast<const uint32_t *>(ph + r * GA_KC * 4);
+                if (HAS_M) dm[r] = *reinterpret_cast<const uint32_t *>(pd + r * GA_KC * 4);
+                else       dm[r] = *reinterpret_cast<const uint16_t *>(pd + r * GA_KC * 2);
+            }
+        } else if (act) {
 #pragma unroll
             for (int r = 0; r < GA_R; r++) {
                 const int e = r * cnt + lane;
-                const uint4 * q = reinterpret_cast<const uint4 *>(st + (size_t) e * F::QB);
-                const uint4 q0 = q[0];
-                const uint4 q1 = (F::QB == 32) ? q[1] : make_uint4(0, 0, 0, 0);
-                uint32_t qh = 0;
-                if (F::HB) qh = *reinterpret_cast<const uint32_t *>(st + GA_R * cnt * F::QB + e * 4);
-                float dw, mw = 0.0f;
+                q0[r] = *reinterpret_cast<const uint4 *>(st + (size_t) e * F::QB);
+                if (F::QB == 32) q1[r] = *reinterpret_cast<const uint4 *>(st + (size_t) e * F::QB + 16);
+                if (F::HB) qh[r] = *reinterpret_cast<const uint32_t *>(st + GA_R * cnt * F::QB + e * 4);
                 const uint8_t * dp = st + GA_R * cnt * (F::QB + F::HB) + e * F::DB;
-                if (HAS_M) { const __half2 dm = *reinterpret_cast<const __half2 *>(dp); dw = __low2float(dm); mw = __high2float(dm); }
-                else dw = __half2float(*reinterpret_cast<const __half *>(dp));
-                dot_block<TYPE, NCOL>(ra[r], xb, q0, q1, qh, dw, mw);
+                if (HAS_M) dm[r] = *reinterpret_cast<const uint32_t *>(dp);
+                else       dm[r] = *reinterpret_cast<const uint16_t *>(dp);
             }
         }
-        __syncwarp();                                   // every lane has consumed the stage
+        __syncwarp();                                   // every lane has read the stage
         if (lane == 0 && c + S < nch) {
-            const int cn = c + S, cnt2 = min(GA_KC, nb - cn * GA_KC);
-            const uint32_t bytes = (uint32_t) ((GA_R * cnt2 * BB + 15) & ~15);
+            const uint32_t bytes = (c + S == nch - 1) ? last_bytes : (uint32_t) STAGE;
             mbar_expect_tx(bars + s * 8, bytes);
-            bulk_g2s(smem_u32(my + (size_t) s * STAGE), src0 + (size_t) cn * GA_R * GA_KC * BB, bytes, bars + s * 8);
+            bulk_g2s(my_s + s * STAGE, src0 + (size_t) (c + S) * STAGE, bytes, bars + s * 8);
         }
+        if (act) {
+#pragma unroll
+            for (int r = 0; r < GA_R; r++) {
+                float dw, mw = 0.0f;
+                if (HAS_M) { const __half2 h2 = *reinterpret_cast<const __half2 *>(&dm[r]); dw = __low2float(h2); mw = __high2float(h2); }
+                else dw = __half2float(__ushort_as_half((unsigned short) dm[r]));
+                dot_block<TYPE, NCOL>(ra[r], xb, q0[r], F::QB == 32 ? q1[r] : make_uint4(0, 0, 0, 0), F::HB ? qh[r] : 0u, dw, mw);
+            }
+        }
+        if (PREFETCH_X) xb = xn;
+        if (++s == S) { s = 0; phase ^= 1; }
     }
 
     // ---- warp totals; lane (r*NCOL + c) finishes output (row0 + r, col0 + c) ----------------------
@@ -166,9 +246,21 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     }
 }
 
+static int ga_stage_override() {
+    static const int v = [] { const char * e = getenv("RWKV_B200_GA_STAGES"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
 template <int TYPE, int NCOL>
 static cudaError_t launch_async_n(const GemvBatch & b, int total_ctas, int ygrid, cudaStream_t st) {
-    return launch_pdl(gemv_async_kernel<TYPE, NCOL>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE>(), st, b);
+    // Ring depth: 3 stages let three CTAs share an SM (24 warps hide the unpack latency) and win
+    // once the grid fills them (>= 3 x 148 CTAs); smaller grids run one or two CTAs per SM and
+    // want the deeper ring for bytes in flight.  Q8_0 tiles are 4.25 KB: 3 stages either way.
+    // The depth never changes the arithmetic.
+    int S = (QFmt<TYPE>::QB == 32 || total_ctas * ygrid >= 3 * 148) ? 3 : 4;
+    if (ga_stage_override() == 3 || ga_stage_override() == 4) S = ga_stage_override();
+    if (S == 3) return launch_pdl(gemv_async_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, b);
+    return launch_pdl(gemv_async_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, b);
 }
 
 template <int TYPE>
@@ -191,12 +283,22 @@ cudaError_t launch_gemv_async(const GemvBatch & b, int total_ctas, cudaStream_t 
     }
 }
 
+template <int TYPE, int NCOL, int S>
+static cudaError_t set_smem_one() {
+    return cudaFuncSetAttribute(gemv_async_kernel<TYPE, NCOL, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, S>());
+}
+
 template <int TYPE>
 static cudaError_t set_smem_attr() {
-    cudaError_t e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE>());
+    cudaError_t e = cudaSuccess;
+    if (e == cudaSuccess) e = set_smem_one<TYPE, 1, 3>();
+    if (e == cudaSuccess) e = set_smem_one<TYPE, 2, 3>();
+    if (e == cudaSuccess) e = set_smem_one<TYPE, 4, 3>();
+    if (e == cudaSuccess) e = set_smem_one<TYPE, 8, 3>();
+    if (e == cudaSuccess) e = set_smem_one<TYPE, 1, 4>();
+    if (e == cudaSuccess) e = set_smem_one<TYPE, 2, 4>();
+    if (e == cudaSuccess) e = set_smem_one<TYPE, 4, 4>();
+    if (e == cudaSuccess) e = set_smem_one<TYPE, 8, 4>();
     return e;
 }
 
