@@ -38,6 +38,17 @@ PF = ctypes.POINTER(ctypes.c_float)
 PU = ctypes.POINTER(ctypes.c_uint32)
 
 
+
+def ncu_traffic(key):
+    """DRAM bytes per launch of the roofline kernel, from the committed ncu --set full capture
+    (profiles/traffic.json); None when no capture is recorded for it."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            return json.load(f)[key]["traffic_bytes"]
+    except Exception:
+        return None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -286,7 +297,7 @@ def run_decode(args):
             "e2e": {"value": d.world * K / e2e_s, "unit": "tokens/s", "h2d_bytes_per_step": S * 4 + 4, "d2h_bytes_per_step": S * 4 + V * 4,
                     "api": "rwkv_eval(ctx, token, state_in, state_out, logits_out) with host buffers"},
             "gpu_launches": launches * K,
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": ncu_traffic("head_gemv_f16_50277x768"),
                          "kernel": "gemv_kernel<F16,1> head 50277x768 (77.2 MB), dominant launch of the step",
                          "us_per_launch": kms * 1e3, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)" if which == "measured" else which},
         }
@@ -357,7 +368,7 @@ def run_gemv(args):
     return {"metric": "Q5_1 mat-vec achieved HBM GB/s (best of the 14B / 1.6B shapes)", "value": best, "unit": "GB/s", "n_gpus": 1, "steps": 200, "warmup": 4,
             "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 dp4a blocks + f32 accumulate",
             "data": "synthetic", "config": {"workload": "mat-vec microbenchmark, rotating copies > L2", "rows": rows, "peak_source": which},
-            "roofline": {"bound": "hbm", "achieved": best, "peak": hbm, "unit": "GB/s", "frac": best / hbm, "traffic": None}}
+            "roofline": {"bound": "hbm", "achieved": best, "peak": hbm, "unit": "GB/s", "frac": best / hbm, "traffic": ncu_traffic("gemv_async_q5_1_20480x5120")}}
 
 
 def run_prefill(args):

@@ -70,6 +70,11 @@ RWKV_API void   rwkv_b200_matrix_free(struct rwkv_b200_matrix * m);
 RWKV_API bool   rwkv_b200_matrix_mul(struct rwkv_b200_matrix * m, const float * x, size_t n_vec, float * y);
 /* Times `iters` launches (n_vec columns) rotating over the copies; returns average device ms per launch. */
 RWKV_API bool   rwkv_b200_matrix_bench(struct rwkv_b200_matrix * m, size_t n_vec, int iters, double * ms_per_launch);
+/* Same product through the tensor-core GEMM (tcgen05 / TMEM; FP16 operands, FP32 accumulate):
+ * quantised or FP16 matrices with n_cols >= 64.  This is the kernel rwkv_eval_sequence and wide
+ * batches use for n_vec >= 64 rows (replaces ggml_mul_mat at T > 1, rwkv_graph.inc:744-870). */
+RWKV_API bool   rwkv_b200_matrix_mul_tc(struct rwkv_b200_matrix * m, const float * x, size_t n_vec, float * y);
+RWKV_API bool   rwkv_b200_matrix_bench_tc(struct rwkv_b200_matrix * m, size_t n_vec, int iters, double * ms_per_launch);
 /* Algorithmic bytes of one copy (the file bytes of the matrix). */
 RWKV_API size_t rwkv_b200_matrix_bytes(const struct rwkv_b200_matrix * m);
 

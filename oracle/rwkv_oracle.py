@@ -162,6 +162,28 @@ def dequantize(dtype: int, raw: np.ndarray) -> np.ndarray:
     return y.reshape(-1).astype(F32)
 
 
+def dequantize_fp16(dtype: int, raw: np.ndarray) -> np.ndarray:
+    """Weights as the tensor-core sequence path sees them: fp16(q*d + m) with ONE rounding
+    (float64 holds q*d + m exactly for every fp16 d, m pair of practical range).  This is the
+    dequantise-to-FP16 step of the reference's GPU offload path (ggml-cuda convert + FP16 GEMM),
+    restated; the CPU path never rounds weights to FP16."""
+    if dtype == TYPE_FP16:
+        return raw.view(np.float16).copy()
+    q, d, m = unpack_blocks(dtype, raw)
+    y = q.astype(np.float64) * d[:, None].astype(np.float64)
+    if m is not None:
+        y = y + m[:, None].astype(np.float64)
+    return y.reshape(-1).astype(np.float16)
+
+
+def matmul_fp16(dtype: int, raw: np.ndarray, M: int, K: int, x: np.ndarray) -> np.ndarray:
+    """out[T][M] of the tensor-core path: FP16 weights x FP16-rounded activations, exact products,
+    accumulated here in float64 (the device accumulates in FP32 in an unspecified order)."""
+    w = dequantize_fp16(dtype, raw).reshape(M, K).astype(np.float64)
+    xh = np.asarray(x, F32).astype(np.float16).astype(np.float64)
+    return xh @ w.T
+
+
 def _to_fp16_bytes(x: np.ndarray) -> np.ndarray:
     return x.astype(np.float16).view(np.uint8).reshape(-1, 2)
 

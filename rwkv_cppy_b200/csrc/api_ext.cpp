@@ -56,10 +56,16 @@ bool upload_matrix(int type, const void * raw, size_t M, size_t K, cudaStream_t 
     bool ok = tiled != nullptr;
     ok = ok && cudaMemcpyAsync(scratch, raw, nbytes, cudaMemcpyHostToDevice, st) == cudaSuccess;
     ok = ok && launch_repack(type, (const uint8_t *) scratch, M, K, tiled, st) == cudaSuccess;
+    void * tc = nullptr;
+    if (ok && gemm_tc_enabled() && K >= TC_KB) {
+        tc = alloc(tc_bytes(type, M, K));
+        ok = tc != nullptr && launch_repack_tc(type, (const uint8_t *) scratch, M, K, tc, st) == cudaSuccess;
+    }
     ok = ok && cudaStreamSynchronize(st) == cudaSuccess;
     cudaFree(scratch);
     RB_CHECK(ok, RWKV_ERROR_ALLOC, false, "matrix upload failed: %s", cudaGetErrorString(cudaGetLastError()));
     out.qs = tiled; out.rg_stride = (uint32_t) tiled_rg_stride(type, K);
+    if (tc) { out.tc = tc; out.tc_kblocks = (uint32_t) ((K + TC_KB - 1) / TC_KB); }
     return true;
 }
 
@@ -68,6 +74,7 @@ bool act_dev_alloc(std::vector<void *> & allocs, Act & a, int rows, int K) {
     a.K = K;
     a.f = (float *) alloc((size_t) rows * K * 4);
     if (!a.f) return false;
+    if (gemm_tc_enabled()) { a.h = (uint16_t *) alloc((size_t) rows * K * 2); if (!a.h) return false; }
     if (K % 32 == 0) {
         const size_t nb = (size_t) rows * (K / 32);
         a.q = (int8_t *) alloc((size_t) rows * K); a.d = (float *) alloc(nb * 4); a.s = (float *) alloc(nb * 4); a.isum = (int *) alloc(nb * 4);
@@ -322,7 +329,8 @@ struct rwkv_b200_matrix * rwkv_b200_matrix_create(int type, const void * raw, si
     rwkv_b200_matrix * m = new (std::nothrow) rwkv_b200_matrix();
     RB_CHECK(m != nullptr, RWKV_ERROR_ALLOC, nullptr, "alloc failed");
     m->device = dev;
-    bool ok = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) == cudaSuccess && gemv_async_init() == cudaSuccess;
+    bool ok = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) == cudaSuccess && gemv_async_init() == cudaSuccess
+              && (!gemm_tc_enabled() || gemm_tc_init() == cudaSuccess);
     m->copies.resize(copies);
     for (size_t c = 0; c < copies && ok; c++) ok = upload_matrix(type, raw, n_rows, n_cols, m->stream, m->allocations, m->copies[c]);
     if (!ok) { rwkv_b200_matrix_free(m); return nullptr; }
@@ -368,6 +376,51 @@ bool rwkv_b200_matrix_mul(struct rwkv_b200_matrix * m, const float * x, size_t n
     RB_CUDA(launch_gemv(b, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(cudaMemcpyAsync(y, m->y, n_vec * W.M * sizeof(float), cudaMemcpyDeviceToHost, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(cudaStreamSynchronize(m->stream), RWKV_ERROR_GRAPH, false);
+    return true;
+}
+
+bool rwkv_b200_matrix_mul_tc(struct rwkv_b200_matrix * m, const float * x, size_t n_vec, float * y) {
+    RB_CHECK(m && x && y && n_vec > 0, RWKV_ERROR_ARGS, false, "Bad arguments");
+    RB_CUDA(cudaSetDevice(m->device), RWKV_ERROR_CTX, false);
+    const DevMat & W = m->copies[m->next % m->copies.size()];
+    m->next++;
+    RB_CHECK(gemm_tc_enabled() && (W.type == T_F16 || W.tc != nullptr) && W.K >= 64 && W.K % 8 == 0, RWKV_ERROR_ARGS | RWKV_ERROR_UNSUPPORTED, false,
+             "Matrix not eligible for the tensor-core path");
+    if (!matrix_prepare(m, n_vec)) return false;
+    RB_CUDA(cudaMemcpyAsync(m->x.f, x, n_vec * W.K * sizeof(float), cudaMemcpyHostToDevice, m->stream), RWKV_ERROR_GRAPH, false);
+    RB_CUDA(launch_to_half(m->x.f, m->x.h, n_vec * W.K, m->stream), RWKV_ERROR_GRAPH, false);
+    GemmJob g; g.W = W; g.x16 = m->x.h; g.ldx = (int) W.K; g.out = m->y; g.ldo = (int) W.M; g.epi = EPI_STORE;
+    RB_CUDA(launch_gemm_tc(&g, 1, (int) n_vec, m->stream), RWKV_ERROR_GRAPH, false);
+    RB_CUDA(cudaMemcpyAsync(y, m->y, n_vec * W.M * sizeof(float), cudaMemcpyDeviceToHost, m->stream), RWKV_ERROR_GRAPH, false);
+    RB_CUDA(cudaStreamSynchronize(m->stream), RWKV_ERROR_GRAPH, false);
+    return true;
+}
+
+bool rwkv_b200_matrix_bench_tc(struct rwkv_b200_matrix * m, size_t n_vec, int iters, double * ms_per_launch) {
+    RB_CHECK(m && n_vec > 0 && iters > 0 && ms_per_launch, RWKV_ERROR_ARGS, false, "Bad arguments");
+    RB_CUDA(cudaSetDevice(m->device), RWKV_ERROR_CTX, false);
+    const DevMat & W0 = m->copies[0];
+    RB_CHECK(gemm_tc_enabled() && (W0.type == T_F16 || W0.tc != nullptr) && W0.K >= 64 && W0.K % 8 == 0, RWKV_ERROR_ARGS | RWKV_ERROR_UNSUPPORTED, false,
+             "Matrix not eligible for the tensor-core path");
+    if (!matrix_prepare(m, n_vec)) return false;
+    RB_CUDA(cudaMemsetAsync(m->x.h, 0, n_vec * W0.K * 2, m->stream), RWKV_ERROR_GRAPH, false);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaError_t err = cudaSuccess;
+    auto one = [&](size_t c) {
+        GemmJob g; g.W = m->copies[c % m->copies.size()]; g.x16 = m->x.h; g.ldx = (int) W0.K; g.out = m->y; g.ldo = (int) W0.M; g.epi = EPI_STORE;
+        return launch_gemm_tc(&g, 1, (int) n_vec, m->stream);
+    };
+    for (size_t c = 0; c < m->copies.size() && err == cudaSuccess; c++) err = one(c);
+    cudaEventRecord(e0, m->stream);
+    for (int i = 0; i < iters && err == cudaSuccess; i++) err = one((size_t) i);
+    cudaEventRecord(e1, m->stream);
+    if (err == cudaSuccess) err = cudaStreamSynchronize(m->stream);
+    float t = 0.0f;
+    cudaEventElapsedTime(&t, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    RB_CHECK(err == cudaSuccess, RWKV_ERROR_GRAPH, false, "bench failed: %s", cudaGetErrorString(err));
+    *ms_per_launch = (double) t / iters;
     return true;
 }
 

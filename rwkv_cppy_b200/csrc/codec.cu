@@ -80,6 +80,50 @@ cudaError_t launch_repack(uint32_t type, const uint8_t * raw, size_t M, size_t K
     return cudaGetLastError();
 }
 
+// ---- tensor-core copy (DevMat::tc): one thread per (padded row, padded block) -----------------
+__global__ void repack_tc_kernel(uint32_t type, const uint8_t * __restrict__ raw, uint32_t M, uint32_t nb, uint32_t kblocks,
+                                 uint8_t * __restrict__ out) {
+    const size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t rows_padded = ((size_t) M + TC_ROWS - 1) / TC_ROWS * TC_ROWS, nbp = (size_t) kblocks * 2;
+    if (idx >= rows_padded * nbp) return;
+    const size_t row = idx / nbp; const int b = (int) (idx % nbp);
+    const int bb = type == T_Q4_0 ? 18 : type == T_Q4_1 ? 20 : type == T_Q5_0 ? 22 : type == T_Q5_1 ? 24 : 34;
+    const bool has_m = (type == T_Q4_1 || type == T_Q5_1), has_h = (type == T_Q5_0 || type == T_Q5_1);
+    const uint32_t QB = tile_qb(type), HB = tile_hb(type), DB = tile_db(type);
+    uint8_t * chunk = out + ((row / TC_ROWS) * kblocks + (size_t) (b >> 1)) * (size_t) (2 * TC_ROWS * bb);
+    const int e = (b & 1) * TC_ROWS + (int) (row % TC_ROWS);
+    uint8_t * pq = chunk + (size_t) e * QB;
+    uint8_t * ph = chunk + (size_t) 2 * TC_ROWS * QB + (size_t) e * HB;
+    uint8_t * pd = chunk + (size_t) 2 * TC_ROWS * (QB + HB) + (size_t) e * DB;
+    const int nq = (int) QB;
+    if (row >= M || b >= (int) nb) {                  // padding: zero blocks (d = 0 [, m = 0])
+        for (int i = 0; i < nq; i++) pq[i] = 0;
+        if (has_h) *reinterpret_cast<uint32_t *>(ph) = 0;
+        *reinterpret_cast<uint16_t *>(pd) = 0;
+        if (has_m) *reinterpret_cast<uint16_t *>(pd + 2) = 0;
+        return;
+    }
+    const uint8_t * s = raw + (row * nb + b) * bb;
+    *reinterpret_cast<uint16_t *>(pd) = (uint16_t) s[0] | ((uint16_t) s[1] << 8);
+    s += 2;
+    if (has_m) { *reinterpret_cast<uint16_t *>(pd + 2) = (uint16_t) s[0] | ((uint16_t) s[1] << 8); s += 2; }
+    if (has_h) {
+        const uint32_t h = (uint32_t) s[0] | ((uint32_t) s[1] << 8) | ((uint32_t) s[2] << 16) | ((uint32_t) s[3] << 24);
+        *reinterpret_cast<uint32_t *>(ph) = permute_qh(h);
+        s += 4;
+    }
+    for (int i = 0; i < nq; i++) pq[i] = s[i];
+}
+
+cudaError_t launch_repack_tc(uint32_t type, const uint8_t * raw, size_t M, size_t K, void * out, cudaStream_t st) {
+    const size_t nb = K / 32, kblocks = (K + TC_KB - 1) / TC_KB, rows_padded = (M + TC_ROWS - 1) / TC_ROWS * TC_ROWS;
+    const size_t n = rows_padded * kblocks * 2;
+    if (n == 0) return cudaSuccess;
+    const int threads = 256;
+    repack_tc_kernel<<<(unsigned) ((n + threads - 1) / threads), threads, 0, st>>>(type, raw, (uint32_t) M, (uint32_t) nb, (uint32_t) kblocks, (uint8_t *) out);
+    return cudaGetLastError();
+}
+
 // Value of weight (row, col) from the tiled storage.
 // y = q*d (+m) with one rounding (q*d is exact in FP32: <= 8 x 11 significant bits), which
 // is what dequantize_row_* computes whether or not the host compiler contracts to an FMA.

@@ -98,7 +98,17 @@ struct DevMat {
     const void * qs = nullptr;
     uint32_t rg_stride = 0;                // bytes between row groups (quantised only)
     size_t bytes = 0;                      // algorithmic bytes of the matrix (file bytes)
+    // Second copy for the tensor-core GEMM (quantised only; null when not built): chunks of
+    // 128 rows x 64 weights (2 blocks), chunk (mt, kb) at (mt * tc_kblocks + kb) * 256 * block
+    // bytes.  Inside a chunk, entry e = blk * 128 + row and three planes like the warp tile:
+    // nibbles [256] x 16 B (Q8_0 32 B) | qh [256] x u32 (Q5, permuted) | scales [256] x half or half2.
+    // Rows past M and blocks past K/32 are zero blocks.
+    const void * tc = nullptr;
+    uint32_t tc_kblocks = 0;               // ceil(K / 64)
 };
+constexpr int TC_ROWS = 128, TC_KB = 64;
+inline size_t tc_chunk_bytes(uint32_t t) { return (size_t) 2 * TC_ROWS * type_block_bytes(t); }
+inline size_t tc_bytes(uint32_t t, size_t M, size_t K) { return ((M + TC_ROWS - 1) / TC_ROWS) * ((K + TC_KB - 1) / TC_KB) * tc_chunk_bytes(t); }
 
 #if defined(__CUDACC__)
 #define RB_HD __host__ __device__

@@ -4,6 +4,7 @@
 // (R = T tokens of one stream) and batched decode (R independent streams): the kernels take
 // the row count and the "rows are streams" flag.
 #include "engine.h"
+#include <unordered_map>
 
 namespace rb {
 
@@ -21,6 +22,7 @@ bool dalloc(Workspace & ws, T *& p, size_t n) {
 bool act_alloc(Workspace & ws, Act & a, int rows, int K) {
     a.K = K;
     if (!dalloc(ws, a.f, (size_t) rows * K)) return false;
+    if (gemm_tc_enabled() && rows >= gemm_tc_min_rows() && !dalloc(ws, a.h, (size_t) rows * K)) return false;
     if (K % 32 == 0) {
         const size_t nb = (size_t) rows * (K / 32);
         if (!dalloc(ws, a.q, (size_t) rows * K) || !dalloc(ws, a.d, nb) || !dalloc(ws, a.s, nb) || !dalloc(ws, a.isum, nb)) return false;
@@ -66,16 +68,62 @@ struct Pass {
     static GemvJob job(const DevMat & W, const Act & x, float * out, int ldo, int epi) {
         GemvJob j; j.W = W; j.x = x; j.out = out; j.ldo = ldo; j.epi = epi; return j;
     }
-    // launches the jobs grouped by weight type, R rows each
+    // Acts last written by a tensor-core GEMM: their FP16 copy is current (value true) but their
+    // q8 blocks are stale.  Every other producer writes FP32 + q8.
+    std::unordered_map<const float *, bool> tc_written;
+
+    // launches the jobs grouped by weight type, `rows` rows each; wide row counts go to the
+    // tensor-core GEMM (FP16 operands), everything else to the exact mat-vec kernels
     void gemv(std::vector<GemvJob> jobs, int rows) {
         std::vector<bool> done(jobs.size(), false);
+        // ---- tensor-core path ----
+        for (size_t i = 0; i < jobs.size(); i++) {
+            if (done[i] || !tc_job(jobs[i], rows)) continue;
+            GemmJob g[GEMM_MAX_JOBS]; int n = 0;
+            for (size_t k = i; k < jobs.size() && n < GEMM_MAX_JOBS; k++) {
+                if (done[k] || jobs[k].W.type != jobs[i].W.type || !tc_job(jobs[k], rows)) continue;
+                const GemvJob & j = jobs[k];
+                auto it = tc_written.find(j.x.f);
+                if (it == tc_written.end() || !it->second) {            // FP16 copy of the input rows
+                    chk(launch_to_half(j.x.f, j.x.h, (size_t) rows * j.x.K, st));
+                    tc_written[j.x.f] = true;                           // (q8 state of x is irrelevant from here on within this call)
+                    to_half_marks.push_back(j.x.f);
+                }
+                GemmJob & o = g[n++];
+                o.W = j.W; o.x16 = j.x.h + j.x_off; o.ldx = j.x.K;
+                o.out = j.out; o.ldo = j.ldo; o.epi = j.epi; o.aux = j.aux; o.ld_aux = j.ld_aux; o.vec = j.vec;
+                if (j.out_act.f) {
+                    if (!o.out) { o.out = j.out_act.f; o.ldo = j.out_act.K; }
+                    o.out_h = j.out_act.h; o.ld_h = j.out_act.K;
+                }
+                done[k] = true;
+            }
+            chk(launch_gemm_tc(g, n, rows, st));
+            // inputs converted for this launch keep a valid q8 form: only the marks of GEMM outputs persist
+            for (const float * p : to_half_marks) tc_written.erase(p);
+            to_half_marks.clear();
+            for (size_t k = i; k < jobs.size(); k++)
+                if (done[k] && jobs[k].out_act.f && tc_job(jobs[k], rows) && jobs[k].W.type == jobs[i].W.type) tc_written[jobs[k].out_act.f] = jobs[k].out_act.h != nullptr;
+        }
+        // ---- exact path ----
         for (size_t i = 0; i < jobs.size(); i++) {
             if (done[i]) continue;
             GemvBatch b; b.T = rows;
             for (size_t k = i; k < jobs.size() && b.n_jobs < GEMV_MAX_JOBS; k++)
-                if (!done[k] && jobs[k].W.type == jobs[i].W.type) { b.job[b.n_jobs++] = jobs[k]; done[k] = true; }
+                if (!done[k] && jobs[k].W.type == jobs[i].W.type) {
+                    const GemvJob & j = jobs[k];
+                    if (type_quantized(j.W.type) && tc_written.count(j.x.f)) {   // produced by a GEMM: q8 blocks are stale
+                        Act a = j.x; chk(launch_quantize_act(a, rows, st)); tc_written.erase(j.x.f);
+                    }
+                    if (j.out_act.f) tc_written.erase(j.out_act.f);
+                    b.job[b.n_jobs++] = j; done[k] = true;
+                }
             chk(launch_gemv(b, st));
         }
+    }
+    std::vector<const float *> to_half_marks;
+    bool tc_job(const GemvJob & j, int rows) const {
+        return j.x.h != nullptr && (j.x_off % 8) == 0 && (j.x.K % 8) == 0 && gemm_tc_supported(j.W, rows);
     }
 
     const float * sin(uint32_t layer, size_t off) const { return fa.state_in + (size_t) layer * m.layer_state_len() + off; }

@@ -17,6 +17,7 @@
 // lane-strided over K + butterfly: it depends on K only, never on T or the grid.
 #include "gemv_common.cuh"
 #include "launch.cuh"
+#include "ptx.cuh"
 #include <cstdlib>
 
 namespace rb {
@@ -32,28 +33,6 @@ template <> struct QFmt<T_Q8_0> { static constexpr int QB = 32, HB = 0, DB = 2, 
 
 template <int TYPE> __host__ __device__ constexpr int ga_stage_bytes() { return GA_R * GA_KC * (QFmt<TYPE>::QB + QFmt<TYPE>::HB + QFmt<TYPE>::DB); }
 template <int TYPE, int S> __host__ __device__ constexpr int ga_smem_bytes() { return GA_WARPS * S * (ga_stage_bytes<TYPE>() + 8); }
-
-// ---- PTX wrappers ------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra.uni WAIT_DONE;\n\t"
-        "bra.uni WAIT_LOOP;\n\t"
-        "WAIT_DONE:\n\t}" :: "r"(bar), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
 
 // Per-lane cursors into the q8 activation rows (block `lane` of column col0); hoisted out of
 // the chunk loop so an iteration costs one add per pointer.
@@ -134,8 +113,8 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < S; s++) mbar_init(bars + s * 8, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_init_fence();
+        fence_proxy_async_smem();
         // weights do not depend on the preceding kernel: start streaming at once
 #pragma unroll
         for (int s = 0; s < S; s++) {

@@ -44,11 +44,12 @@ __device__ __forceinline__ void load_xblock(XBlock<NCOL> & xb, const Act & x, in
     }
 }
 
-// one row x one block for all columns
-template <int TYPE, int NCOL>
-__device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<NCOL> & xb,
-                                          const uint4 q0, const uint4 q1, const uint32_t qh, const float dw, const float mw) {
-    int wv[8];
+// The 32 weights of one block as 8 words of 4 byte-sized integers each: word i (< 4) holds
+// elements 4i..4i+3, word 4+i elements 16+4i..16+4i+3 (ggml block order: element j < 16 is the
+// low nibble of byte j, element j+16 its high nibble).  Q4/Q5: unsigned 0..15 / 0..31 (the
+// zero point is applied by the caller); Q8_0: the signed bytes as stored.
+template <int TYPE>
+__device__ __forceinline__ void unpack_block(int (&wv)[8], const uint4 q0, const uint4 q1, const uint32_t qh) {
     if (TYPE == T_Q8_0) {
         wv[0] = q0.x; wv[1] = q0.y; wv[2] = q0.z; wv[3] = q0.w; wv[4] = q1.x; wv[5] = q1.y; wv[6] = q1.z; wv[7] = q1.w;
     } else {
@@ -63,6 +64,14 @@ __device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<
             wv[i] = (int) lo; wv[4 + i] = (int) hi;
         }
     }
+}
+
+// one row x one block for all columns
+template <int TYPE, int NCOL>
+__device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<NCOL> & xb,
+                                          const uint4 q0, const uint4 q1, const uint32_t qh, const float dw, const float mw) {
+    int wv[8];
+    unpack_block<TYPE>(wv, q0, q1, qh);
 #pragma unroll
     for (int c = 0; c < NCOL; c++) {
         int dp = 0;
@@ -75,7 +84,8 @@ __device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<
     }
 }
 
-__device__ __forceinline__ float apply_epilogue(const GemvJob & J, float y, int t, int m) {
+template <typename JobT>
+__device__ __forceinline__ float apply_epilogue(const JobT & J, float y, int t, int m) {
     switch (J.epi) {
         case EPI_STORE:        return y;
         case EPI_SIGMOID:      return sigmoidf_ref(y);

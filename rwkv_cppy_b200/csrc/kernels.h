@@ -11,12 +11,14 @@ namespace rb {
 //   d    fp16-rounded scale per block   } (quantize_row_q8_0 / q8_1 as compiled for x86,
 //   s    fp16-rounded d*sum(q) (q8_1)   }  ggml-cpu-quants.c:783-850,1083-1150), split into
 //   isum sum(q) per block (int)         }  planes.  q == nullptr when K % 32 != 0.
+//   h    FP16 copy [T][K] for the tensor-core GEMM (optional; filled on demand)
 struct Act {
     float *  f = nullptr;
     int8_t * q = nullptr;
     float *  d = nullptr;
     float *  s = nullptr;
     int *    isum = nullptr;
+    uint16_t * h = nullptr;
     int      K = 0;          // row length (row stride of f and q; K/32 for d, s, isum)
 };
 
@@ -59,9 +61,32 @@ cudaError_t launch_gemv(const GemvBatch & b, cudaStream_t st);
 // once per device, outside stream capture (opts the bulk-async kernel in to > 48 KB shared memory)
 cudaError_t gemv_async_init();
 
+// ---- tensor-core GEMM (sequence mode / wide batches; gemm_tc.cu) ----------------------------
+// out[T][M] = epi(X[T][K] * W[M][K]^T) with FP16 operands (quantised weights dequantised to FP16
+// on the fly) and FP32 accumulation on tcgen05 / TMEM.  Same epilogues as the mat-vec jobs.
+constexpr int GEMM_MAX_JOBS = 6;
+struct GemmJob {
+    DevMat           W;                 // quantised (needs W.tc) or T_F16
+    const uint16_t * x16 = nullptr;     // FP16 activations, T rows of W.K values, row stride ldx
+    int              ldx = 0;
+    float *          out = nullptr; int ldo = 0;
+    int              epi = EPI_STORE;
+    const float *    aux = nullptr; int ld_aux = 0;
+    const float *    vec = nullptr;
+    uint16_t *       out_h = nullptr; int ld_h = 0;   // optional FP16 copy of the result (input of a chained GEMM)
+};
+bool gemm_tc_enabled();                                // driver entry point found and RWKV_B200_NO_TC != 1
+int  gemm_tc_min_rows();                               // smallest T that takes the tensor path (default 64)
+bool gemm_tc_supported(const DevMat & W, int T);
+cudaError_t gemm_tc_init();                            // once per device, outside stream capture
+cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t st);   // all jobs share one weight type
+cudaError_t launch_to_half(const float * x, uint16_t * out, size_t n, cudaStream_t st);  // n % 4 == 0
+
 // ---- codec -----------------------------------------------------------------------------
 // raw ggml rows (device copy of the file bytes, M x K) -> warp-tile layout (tiled_bytes(type, M, K) bytes at `out`)
 cudaError_t launch_repack(uint32_t type, const uint8_t * raw, size_t M, size_t K, void * out, cudaStream_t st);
+// raw ggml rows -> the tensor-core chunk layout (DevMat::tc)
+cudaError_t launch_repack_tc(uint32_t type, const uint8_t * raw, size_t M, size_t K, void * out, cudaStream_t st);
 // device layout -> FP32 [M][K]; bit-exact dequantize_row_* (ggml-quants.c:255-363)
 cudaError_t launch_dequant(const DevMat & W, float * out, cudaStream_t st);
 // device layout -> FP16 [M][K] (operand of the tensor-core sequence GEMM)

@@ -105,6 +105,12 @@ struct Loader {
         if (launch_repack(t->type, scratch, M, K, tiled, st) != cudaSuccess) { ok = false; return false; }
         if (cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
         out.qs = tiled; out.rg_stride = (uint32_t) tiled_rg_stride(t->type, K);
+        if (gemm_tc_enabled() && K >= TC_KB) {                 // second copy in the tensor-core chunk layout (scratch still holds the raw rows)
+            void * tc = bump(tc_bytes(t->type, M, K));
+            if (!tc) return false;
+            if (launch_repack_tc(t->type, scratch, M, K, tc, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
+            out.tc = tc; out.tc_kblocks = (uint32_t) ((K + TC_KB - 1) / TC_KB);
+        }
         return true;
     }
 
@@ -163,6 +169,7 @@ Model * model_load(const char * path) {
         const size_t as_vec = t.n_elements() * 4;
         arena += std::max(t.nbytes, t.n_dims == 2 ? t.nbytes : as_vec) + 4 * 256;
         if (type_quantized(t.type)) arena += TILE_ROWS * (t.ne[0] / 32) * type_block_bytes(t.type) + 64;   // row padding of the tiled layout
+        if (type_quantized(t.type) && t.n_dims == 2 && gemm_tc_enabled()) arena += tc_bytes(t.type, t.ne[1] * t.ne[2], t.ne[0]) + 256;
         if (type_quantized(t.type)) scratch = std::max(scratch, t.nbytes);
     }
     RB_CUDA(cudaMalloc((void **) &L.arena, arena), RWKV_ERROR_MODEL | RWKV_ERROR_ALLOC, nullptr);
@@ -174,6 +181,7 @@ Model * model_load(const char * path) {
     }
     RB_CUDA(cudaStreamCreate(&L.st), RWKV_ERROR_MODEL | RWKV_ERROR_ALLOC, nullptr);
     RB_CUDA(gemv_async_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
+    if (gemm_tc_enabled()) RB_CUDA(gemm_tc_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
 
     const size_t D = m.n_embed, V = m.n_vocab;
     L.mat("emb.weight", D, V, m.emb);

@@ -76,6 +76,8 @@ class RWKVSharedLibrary:
         sig("rwkv_b200_matrix_free", [vp], None)
         sig("rwkv_b200_matrix_mul", [vp, P_FLOAT, sz, P_FLOAT], b)
         sig("rwkv_b200_matrix_bench", [vp, sz, ctypes.c_int, ctypes.POINTER(ctypes.c_double)], b)
+        sig("rwkv_b200_matrix_mul_tc", [vp, P_FLOAT, sz, P_FLOAT], b)
+        sig("rwkv_b200_matrix_bench_tc", [vp, sz, ctypes.c_int, ctypes.POINTER(ctypes.c_double)], b)
         sig("rwkv_b200_matrix_bytes", [vp], sz)
         self.nullptr = ctypes.cast(0, P_FLOAT)
 
