@@ -7,16 +7,16 @@
 // GPU offload path (dequantise-to-FP16 + FP16 GEMM), not of its CPU path; FP32 files never
 // take this path.
 //
-// Structure (one persistent CTA per SM, 14 warps, tiles of 128 weight rows x BN tokens):
+// Structure (one persistent CTA per SM, 18 warps, tiles of 128 weight rows x BN tokens):
 //   warp 0      producer: per 64-wide K step one cp.async.bulk of the quantised 128x64 chunk
 //               (DevMat::tc layout, 4.5-8.5 KB) into a ring, and one TMA tensor load of the
 //               BN x 64 FP16 activation box (128-byte swizzle) into the stage;
-//   warps 6-13  dequantisers: thread = (row, block); unpack 32 weights, convert to FP16 and
+//   warps 10-17 dequantisers: thread = (row, block); unpack 32 weights, convert to FP16 and
 //               store them into the stage's A tile in the K-major 128B-swizzled layout;
 //   warp 1      one elected thread issues 4 x tcgen05.mma (M128 x N=BN x K16, kind::f16) per
 //               stage, accumulator in TMEM (double buffered: 2 x BN columns), and commits the
 //               stage / the accumulator to mbarriers;
-//   warps 2-5   epilogue: tcgen05.ld 32 lanes x 32 columns, the same fused epilogues as the
+//   warps 2-9   epilogue: tcgen05.ld 32 lanes x 32 columns, the same fused epilogues as the
 //               mat-vec kernels, coalesced FP32 stores (+ optional FP16 copy for a chained GEMM).
 // FP16 weight matrices (FP16 files, head) skip the dequantisers: the A tile is a second TMA load.
 #include "gemv_common.cuh"
@@ -32,7 +32,8 @@
 namespace rb {
 
 constexpr int GT_BM = TC_ROWS, GT_BK = TC_KB;
-constexpr int GT_WARPS = 14, GT_THREADS = GT_WARPS * 32;
+constexpr int GT_WARPS = 18, GT_THREADS = GT_WARPS * 32;
+constexpr int GT_EPI_WARPS = 8, GT_DQ_WARP0 = 2 + GT_EPI_WARPS;
 constexpr int GT_SQ = 4;                                  // quantised-chunk ring depth
 constexpr int GT_A_BYTES = GT_BM * GT_BK * 2;             // 16 KB
 
@@ -94,6 +95,35 @@ __device__ __forceinline__ void dequant_block_f16(uint4 (&out)[4], const uint4 q
     }
 }
 
+// One warp's share of a finished accumulator tile: lane = weight row m; the warp takes the
+// 16-column (token) chunks `half_id`, `half_id + 2`, ... of the BN columns.  Stores are 128-byte
+// coalesced (32 lanes = 32 consecutive m of one token row).
+template <int EPI, int BN>
+__device__ __forceinline__ void epilogue_tile(const GtJob & J, uint32_t tcol, int m, int t0, int T, int half_id) {
+    const bool row_ok = m < (int) J.M;
+    float * const out = J.out; __half * const out_h = J.out_h;
+    const int ldo = J.ldo, ld_h = J.ld_h;
+#pragma unroll 1
+    for (int c0 = half_id * 16; c0 < BN; c0 += 32) {
+        if (t0 + c0 >= T) break;                                  // warp-uniform
+        uint32_t v[16];
+        tmem_ld_32x16(tcol + c0, v);
+        tmem_ld_wait();
+        const int nv = T - t0 - c0;
+        if (row_ok) {
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                if (i < nv) {
+                    const int t = t0 + c0 + i;
+                    const float y = apply_epilogue_c<EPI>(J, __uint_as_float(v[i]), t, m);
+                    if (out) out[(size_t) t * ldo + m] = y;
+                    if (out_h) out_h[(size_t) t * ld_h + m] = __float2half_rn(y);
+                }
+            }
+        }
+    }
+}
+
 template <int TYPE, int BN>
 __global__ void __launch_bounds__(GT_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ GtBatch B) {
@@ -121,7 +151,7 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < S; s++) { mbar_init(bar_full + 8 * s, QUANT ? 1 + 8 : 1); mbar_init(bar_empty + 8 * s, 1); }
         for (int s = 0; s < GT_SQ; s++) { mbar_init(bar_qfull + 8 * s, 1); mbar_init(bar_qempty + 8 * s, 8); }
-        for (int s = 0; s < 2; s++) { mbar_init(bar_tfull + 8 * s, 1); mbar_init(bar_tempty + 8 * s, 4); }
+        for (int s = 0; s < 2; s++) { mbar_init(bar_tfull + 8 * s, 1); mbar_init(bar_tempty + 8 * s, GT_EPI_WARPS); }
         mbar_init_fence();
         fence_proxy_async_smem();
         for (int j = 0; j < B.n_jobs; j++) { tma_prefetch_desc(&B.job[j].xmap); if (!QUANT) tma_prefetch_desc(&B.job[j].wmap); }
@@ -190,9 +220,9 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
                 __syncwarp();
             }
         }
-    } else if (warp < 6) {
-        // ===== epilogue =====
-        const int q = warp & 3;                                  // TMEM lane quadrant this warp may read
+    } else if (warp < GT_DQ_WARP0) {
+        // ===== epilogue: warp -> TMEM lane quadrant (warp % 4, fixed by the hardware) x column half =====
+        const int q = warp & 3, half_id = (warp - 2) >> 2;
         pdl_wait();
         uint32_t tl = 0;
         for (int tile = blockIdx.x; tile < B.total_tiles; tile += gridDim.x, tl++) {
@@ -201,24 +231,19 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
             const uint32_t buf = tl & 1, bph = (tl >> 1) & 1;
             mbar_wait(bar_tfull + 8 * buf, bph);
             tc_fence_after();
-            const int m = mt * GT_BM + q * 32 + lane;
-            const int t0 = nt * BN;
-#pragma unroll 1
-            for (int c0 = 0; c0 < BN && t0 + c0 < B.T; c0 += 32) {
-                uint32_t v[32];
-                tmem_ld_32x32(tmem_base + ((uint32_t) (q * 32) << 16) + buf * BN + c0, v);
-                tmem_ld_wait();
-                if (m < (int) J.M) {
-#pragma unroll
-                    for (int i = 0; i < 32; i++) {
-                        const int t = t0 + c0 + i;
-                        if (t < B.T) {
-                            const float y = apply_epilogue(J, __uint_as_float(v[i]), t, m);
-                            if (J.out) J.out[(size_t) t * J.ldo + m] = y;
-                            if (J.out_h) J.out_h[(size_t) t * J.ld_h + m] = __float2half_rn(y);
-                        }
-                    }
-                }
+            const uint32_t tcol = tmem_base + ((uint32_t) (q * 32) << 16) + buf * BN;
+            const int m = mt * GT_BM + q * 32 + lane, t0 = nt * BN;
+            switch (J.epi) {
+                case EPI_STORE:        epilogue_tile<EPI_STORE, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_SIGMOID:      epilogue_tile<EPI_SIGMOID, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_RELU_SQ:      epilogue_tile<EPI_RELU_SQ, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_SILU:         epilogue_tile<EPI_SILU, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_TANH:         epilogue_tile<EPI_TANH, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_ADD_TO:       epilogue_tile<EPI_ADD_TO, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_MULADD_TO:    epilogue_tile<EPI_MULADD_TO, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_BIAS_SIGMOID: epilogue_tile<EPI_BIAS_SIGMOID, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_V6_DECAY:     epilogue_tile<EPI_V6_DECAY, BN>(J, tcol, m, t0, B.T, half_id); break;
+                default:               epilogue_tile<EPI_V7_DECAY, BN>(J, tcol, m, t0, B.T, half_id); break;
             }
             tc_fence_before();
             __syncwarp();
@@ -226,7 +251,7 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
         }
     } else if (QUANT) {
         // ===== dequantisers: thread = (row, block) of the 128 x 64 chunk =====
-        const int d = threadIdx.x - 6 * 32;
+        const int d = threadIdx.x - GT_DQ_WARP0 * 32;
         const int row = d & (GT_BM - 1), blk = d >> 7;
         const int e = blk * GT_BM + row;
         uint32_t it = 0;

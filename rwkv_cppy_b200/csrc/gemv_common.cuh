@@ -84,9 +84,10 @@ __device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<
     }
 }
 
-template <typename JobT>
-__device__ __forceinline__ float apply_epilogue(const JobT & J, float y, int t, int m) {
-    switch (J.epi) {
+// `EPI` known at compile time: the caller hoists the switch out of its inner loops.
+template <int EPI, typename JobT>
+__device__ __forceinline__ float apply_epilogue_c(const JobT & J, float y, int t, int m) {
+    switch (EPI) {
         case EPI_STORE:        return y;
         case EPI_SIGMOID:      return sigmoidf_ref(y);
         case EPI_RELU_SQ:      { const float r = fmaxf(y, 0.0f); return __fmul_rn(r, r); }
@@ -97,6 +98,23 @@ __device__ __forceinline__ float apply_epilogue(const JobT & J, float y, int t, 
         case EPI_BIAS_SIGMOID: return sigmoidf_ref(__fadd_rn(y, J.vec[m]));
         case EPI_V6_DECAY:     return expf(-expf(__fadd_rn(y, J.vec[m])));
         case EPI_V7_DECAY:     return expf(__fmul_rn(sigmoidf_ref(__fadd_rn(y, J.vec[m])), -0.606531f));
+        default:               return y;
+    }
+}
+
+template <typename JobT>
+__device__ __forceinline__ float apply_epilogue(const JobT & J, float y, int t, int m) {
+    switch (J.epi) {
+        case EPI_STORE:        return apply_epilogue_c<EPI_STORE>(J, y, t, m);
+        case EPI_SIGMOID:      return apply_epilogue_c<EPI_SIGMOID>(J, y, t, m);
+        case EPI_RELU_SQ:      return apply_epilogue_c<EPI_RELU_SQ>(J, y, t, m);
+        case EPI_SILU:         return apply_epilogue_c<EPI_SILU>(J, y, t, m);
+        case EPI_TANH:         return apply_epilogue_c<EPI_TANH>(J, y, t, m);
+        case EPI_ADD_TO:       return apply_epilogue_c<EPI_ADD_TO>(J, y, t, m);
+        case EPI_MULADD_TO:    return apply_epilogue_c<EPI_MULADD_TO>(J, y, t, m);
+        case EPI_BIAS_SIGMOID: return apply_epilogue_c<EPI_BIAS_SIGMOID>(J, y, t, m);
+        case EPI_V6_DECAY:     return apply_epilogue_c<EPI_V6_DECAY>(J, y, t, m);
+        case EPI_V7_DECAY:     return apply_epilogue_c<EPI_V7_DECAY>(J, y, t, m);
         default:               return y;
     }
 }
