@@ -57,6 +57,7 @@ struct Workspace {
     Act   head_in;                // ln_out rows
     float * r = nullptr, * k = nullptr, * v = nullptr, * g = nullptr, * w = nullptr, * a = nullptr, * vgate = nullptr;
     float * ffn_r = nullptr, * m5 = nullptr /* [5][rows][D] */, * v_first = nullptr;
+    float * yraw = nullptr;       // [rows][D] raw WKV scan outputs (sequence kernels)
     float * logits = nullptr;     // [logit_rows][V]
     int   logit_rows = 0;
     int * tokens = nullptr;

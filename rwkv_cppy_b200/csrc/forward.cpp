@@ -46,6 +46,7 @@ bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows
     ok = ok && dalloc(ws, ws.r, n) && dalloc(ws, ws.k, n) && dalloc(ws, ws.v, n) && dalloc(ws, ws.g, n) && dalloc(ws, ws.w, n)
             && dalloc(ws, ws.a, n) && dalloc(ws, ws.vgate, n) && dalloc(ws, ws.ffn_r, n) && dalloc(ws, ws.v_first, n);
     if (m.arch_major == 6) ok = ok && dalloc(ws, ws.m5, 5 * n);
+    if (m.arch_major >= 5 && rows >= WKV_SEQ_MIN_ROWS) ok = ok && dalloc(ws, ws.yraw, n);
     ok = ok && dalloc(ws, ws.logits, (size_t) logit_rows * m.n_vocab) && dalloc(ws, ws.tokens, (size_t) rows);
     if (!ok) return false;
     ws.rows = rows; ws.logit_rows = logit_rows;
@@ -145,7 +146,7 @@ struct Pass {
         WkvArgs a;
         a.R = R; a.D = (int) D; a.H = m.head_count; a.S = m.head_size; a.batch = fa.batch; a.state_stride = sstride;
         a.state_in = sin(layer, 2 * D); a.state_out = sout(layer, 2 * D);
-        a.r = ws.r; a.k = ws.k; a.v = ws.v; a.y = ws.y; a.layer = (int) layer;
+        a.r = ws.r; a.k = ws.k; a.v = ws.v; a.y = ws.y; a.layer = (int) layer; a.yraw = ws.yraw;
         return a;
     }
 

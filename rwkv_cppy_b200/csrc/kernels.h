@@ -141,7 +141,9 @@ struct WkvArgs {
     float * v_first = nullptr;            // [R][D]; written when layer == 0, read otherwise
     int   layer = 0;
     Act   y;                              // output rows
+    float * yraw = nullptr;               // [R][D] scratch: raw scan outputs of the sequence kernels (before the head norm)
 };
+constexpr int WKV_SEQ_MIN_ROWS = 8;       // sequences at least this long use the scan kernels (same arithmetic, different work split)
 cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st);   // state slots: aa, bb, pp at state + {0,1,2}*D
 cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st);   // v5.1 / v5.2 / v6 (w != nullptr => per-token decay)
 cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st);

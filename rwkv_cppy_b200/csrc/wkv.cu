@@ -86,9 +86,18 @@ __device__ __forceinline__ float head_norm(float y, float * sy, int tid, bool ac
 // v5.1 / v5.2 / v6.  CTA = HPB heads, thread (hl, j) owns column j (value index) of the
 // head state S[i][j]; state[h*S*S + i*S + j] (i = key index).
 // ----------------------------------------------------------------------------------------
+// The output y[j] = sum_i r[i] * (u[i]*k[i]*v[j] + S[i][j]) is accumulated in a fixed order shared
+// by the fused kernel below (one thread per column) and the sequence scan (8 lanes per column):
+// 8 chains over consecutive key ranges of S/8, combined as ((0+1)+(2+3)) + ((4+5)+(6+7)).
+constexpr int WKV_CHAINS = 8;
+__device__ __forceinline__ float wkv_combine(const float (&yc)[WKV_CHAINS]) {
+    return __fadd_rn(__fadd_rn(__fadd_rn(yc[0], yc[1]), __fadd_rn(yc[2], yc[3])), __fadd_rn(__fadd_rn(yc[4], yc[5]), __fadd_rn(yc[6], yc[7])));
+}
+
 template <int S>
 __global__ void wkv5_kernel(const __grid_constant__ WkvArgs a) {
     extern __shared__ float sm[];
+    constexpr int L = S / WKV_CHAINS > 0 ? S / WKV_CHAINS : 1;
     pdl_trigger();
     const int nthr = blockDim.x;
     float * sr = sm, * sk = sm + nthr, * sw = sm + 2 * nthr, * su = sm + 3 * nthr, * sy = sm + 4 * nthr;
@@ -121,13 +130,17 @@ __global__ void wkv5_kernel(const __grid_constant__ WkvArgs a) {
         __syncthreads();
         float y = 0.0f;
         if (active) {
+            float yc[WKV_CHAINS];
+#pragma unroll
+            for (int c = 0; c < WKV_CHAINS; c++) yc[c] = 0.0f;
 #pragma unroll
             for (int i = 0; i < S; i++) {
                 const float kv = __fmul_rn(vj, sk[hb + i]);
                 const float tmp = __fmaf_rn(kv, su[hb + i], st[i]);
-                y = __fmaf_rn(tmp, sr[hb + i], y);
+                yc[i / L] = __fmaf_rn(tmp, sr[hb + i], yc[i / L]);
                 st[i] = __fmaf_rn(st[i], sw[hb + i], kv);
             }
+            y = wkv_combine(yc);
         }
         float o = head_norm<S>(y, sy, tid, active, a.gn_eps);
         if (active) {
@@ -142,8 +155,128 @@ __global__ void wkv5_kernel(const __grid_constant__ WkvArgs a) {
     }
 }
 
+// ----------------------------------------------------------------------------------------
+// v5 / v6 sequence scan (T tokens of one stream).  The recurrence is sequential in t but
+// independent per state column, so a head is spread over S/8 CTAs of 8 columns, and each
+// column over 8 lanes that own S/8 consecutive key rows: the per-step work of a lane is S/8
+// multiply-adds on registers plus a 3-step butterfly.  r, k, w, v of the next 32 tokens are
+// staged in shared memory with cp.async while the current chunk is processed.  The raw y goes
+// to `yraw`; wkv5_norm_kernel applies the per-head norm, ln_x and the gate afterwards
+// (parallel over tokens).  Same accumulation order as wkv5_kernel, so a sequence pass and
+// token-by-token decode agree bit for bit.
+// ----------------------------------------------------------------------------------------
+constexpr int WKV_TCH = 32;       // tokens per staged chunk
+
+__device__ __forceinline__ void cp_async16(void * smem, const void * gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"((uint32_t) __cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+template <int S>
+__global__ void __launch_bounds__(64) wkv5_seq_kernel(const __grid_constant__ WkvArgs a, float * __restrict__ yraw) {
+    constexpr int L = S / WKV_CHAINS;                  // key rows per lane (S >= 8)
+    constexpr int NV = S / 4;                          // float4 per token per array
+    extern __shared__ __align__(16) float sm[];
+    // per buffer: r, k, w [TCH][S], v [TCH][8]
+    constexpr int BUF = WKV_TCH * (3 * S + 8);
+    pdl_trigger();
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int h = blockIdx.x, jc = blockIdx.y * 8;      // this CTA's 8 columns of head h
+    const int jl = warp * 4 + (lane >> 3), p = lane & 7;
+    const int j = jc + jl, D = a.D;
+    const bool dyn_w = a.w != nullptr;
+
+    float st[L], u[L], wst[L];
+#pragma unroll
+    for (int ii = 0; ii < L; ii++) {
+        const int i = p * L + ii;
+        st[ii] = a.state_in[(size_t) h * S * S + (size_t) i * S + j];
+        u[ii] = a.per_head_scalar ? a.u[h] : a.u[h * S + i];
+        wst[ii] = dyn_w ? 0.0f : (a.per_head_scalar ? a.decay[h] : a.decay[h * S + i]);
+    }
+    pdl_wait();
+
+    auto stage = [&](int buf, int t0) {
+        float * b = sm + buf * BUF;
+        const int nt = min(WKV_TCH, a.R - t0);
+        for (int x = tid; x < nt * NV; x += 64) {
+            const int t = x / NV, c = x % NV;
+            const size_t g = (size_t) (t0 + t) * D + h * S + c * 4;
+            cp_async16(b + t * S + c * 4, a.r + g);
+            cp_async16(b + WKV_TCH * S + t * S + c * 4, a.k + g);
+            if (dyn_w) cp_async16(b + 2 * WKV_TCH * S + t * S + c * 4, a.w + g);
+        }
+        for (int x = tid; x < nt * 2; x += 64) {
+            const int t = x >> 1, c = x & 1;
+            cp_async16(b + 3 * WKV_TCH * S + t * 8 + c * 4, a.v + (size_t) (t0 + t) * D + h * S + jc + c * 4);
+        }
+        cp_async_commit();
+    };
+
+    const int nchunks = (a.R + WKV_TCH - 1) / WKV_TCH;
+    stage(0, 0);
+    for (int c = 0; c < nchunks; c++) {
+        const int t0 = c * WKV_TCH, nt = min(WKV_TCH, a.R - t0);
+        if (c + 1 < nchunks) { stage((c + 1) & 1, t0 + WKV_TCH); cp_async_wait<1>(); } else cp_async_wait<0>();
+        __syncthreads();
+        const float * b = sm + (c & 1) * BUF;
+        const float * sr = b, * sk = b + WKV_TCH * S, * sw = b + 2 * WKV_TCH * S, * sv = b + 3 * WKV_TCH * S;
+#pragma unroll 2
+        for (int t = 0; t < nt; t++) {
+            const float vj = sv[t * 8 + jl];
+            float y = 0.0f;
+#pragma unroll
+            for (int ii = 0; ii < L; ii++) {
+                const int i = p * L + ii;
+                const float kv = __fmul_rn(vj, sk[t * S + i]);
+                const float tmp = __fmaf_rn(kv, u[ii], st[ii]);
+                y = __fmaf_rn(tmp, sr[t * S + i], y);
+                st[ii] = __fmaf_rn(st[ii], dyn_w ? sw[t * S + i] : wst[ii], kv);
+            }
+            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 1));
+            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 2));
+            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 4));
+            if (p == 0) yraw[(size_t) (t0 + t) * D + h * S + j] = y;
+        }
+        __syncthreads();                                  // everyone is done with this buffer before it is refilled
+    }
+#pragma unroll
+    for (int ii = 0; ii < L; ii++) a.state_out[(size_t) h * S * S + (size_t) (p * L + ii) * S + j] = st[ii];
+}
+
+// per-head norm + ln_x + gate of raw scan outputs: CTA = 256 consecutive channels of one token
+template <int S>
+__global__ void __launch_bounds__(256) wkv5_norm_kernel(const __grid_constant__ WkvArgs a, const float * __restrict__ yraw) {
+    __shared__ float sy[256];
+    pdl_trigger();
+    pdl_wait();
+    const int tid = threadIdx.x, e = blockIdx.x * 256 + tid, D = a.D;
+    const size_t row = blockIdx.y;
+    const bool active = e < D;
+    const float y = active ? yraw[row * D + e] : 0.0f;
+    float o = head_norm<S>(y, sy, tid, active, a.gn_eps);
+    if (active) {
+        o = __fadd_rn(__fmul_rn(o, a.lnx_w[e]), a.lnx_b[e]);
+        if (a.g) o = __fmul_rn(o, a.g[row * D + e]);
+    }
+    if (e - (tid & 31) < D) act_store_block(a.y, row, e, active, o);     // warps past the row own no q8 block
+}
+
 template <int S>
 static cudaError_t launch_wkv5_t(const WkvArgs & a, cudaStream_t st) {
+    if (!a.batch && a.R >= WKV_SEQ_MIN_ROWS && a.yraw != nullptr) {
+        constexpr size_t smem = 2 * WKV_TCH * (3 * S + 8) * sizeof(float);
+        static bool attr_set = false;                     // per template instance; > 48 KB needs the opt-in
+        if (!attr_set && smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(wkv5_seq_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+            if (e != cudaSuccess) return e;
+            attr_set = true;
+        }
+        cudaError_t e = launch_pdl(wkv5_seq_kernel<S>, dim3(a.H, S / 8), dim3(64), smem, st, a, a.yraw);
+        if (e != cudaSuccess) return e;
+        return launch_pdl(wkv5_norm_kernel<S>, dim3((a.D + 255) / 256, a.R), dim3(256), 0, st, a, (const float *) a.yraw);
+    }
     const int hpb = S >= 32 ? 1 : 32 / S;
     const int threads = ((hpb * S + 31) / 32) * 32;
     dim3 grid((a.H + hpb - 1) / hpb, a.batch ? a.R : 1);
