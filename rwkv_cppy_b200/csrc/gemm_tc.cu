@@ -363,7 +363,19 @@ static cudaError_t launch_gt_bn(const GtBatch & b, int BN, cudaStream_t st) {
 cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t st) {
     if (n_jobs <= 0) return cudaSuccess;
     if (n_jobs > GEMM_MAX_JOBS) return cudaErrorInvalidValue;
-    const int BN = T > 128 ? 256 : T > 64 ? 128 : 64;
+    // Tile width: wide tiles reuse the dequantised weights over more tokens, narrow tiles fill the
+    // 148 SMs when there are few weight rows.  Cost model (cycles per 64-wide K step of one CTA,
+    // L2-bound estimates): 800 / 520 / 330 for BN = 256 / 128 / 64, times the number of tile rounds.
+    int m_tiles_total = 0;
+    for (int j = 0; j < n_jobs; j++) m_tiles_total += ((int) jobs[j].W.M + GT_BM - 1) / GT_BM;
+    int BN = 64; double best = 1e300;
+    const int cand[3] = {256, 128, 64}; const double cost[3] = {800.0, 520.0, 330.0};
+    for (int c = 0; c < 3; c++) {
+        if (cand[c] > 64 && cand[c] / 2 >= T) continue;           // tile would be more than half empty
+        const int tiles = m_tiles_total * ((T + cand[c] - 1) / cand[c]);
+        const double t = (double) ((tiles + 147) / 148) * cost[c];
+        if (t < best) { best = t; BN = cand[c]; }
+    }
     GtBatch b;
     memset(&b, 0, sizeof(b));
     b.n_jobs = n_jobs; b.T = T; b.n_tiles = (T + BN - 1) / BN;

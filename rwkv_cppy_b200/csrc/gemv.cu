@@ -153,6 +153,70 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
     }
 }
 
+// ---- FP32 weights with a very short K (v6 time_maa_w2: K = 32) over many rows ---------------
+// The mat-vec kernel re-reads such a matrix once per 8 columns; here a thread keeps its weight
+// row in registers and walks 32 activation rows staged in shared memory.  The result is
+// bit-identical to gemv_kernel<T_F32>: lane c of that kernel accumulates chunk c (4 weights,
+// FMA chain), lanes >= K/4 hold 0, and the xor-butterfly (16, 8, 4, 2, 1) combines them; the
+// same tree is evaluated here in one thread (x + 0 is exact, so the empty lanes drop out).
+template <int NCH>   // K / 4: 8 or 16
+__global__ void __launch_bounds__(256) smallk_kernel(const __grid_constant__ GemvBatch B) {
+    constexpr int K = NCH * 4, TT = 32;
+    __shared__ __align__(16) float xs[TT][K];
+    pdl_trigger();
+    const GemvJob & J = B.job[blockIdx.z];
+    const int m = blockIdx.x * 256 + threadIdx.x, t0 = blockIdx.y * TT, M = J.W.M, T = B.T;
+    float w[K];
+    {
+        const float4 * wp = reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(J.W.qs) + (size_t) min(m, M - 1) * K);
+#pragma unroll
+        for (int c = 0; c < NCH; c++) { const float4 f = wp[c]; w[4 * c] = f.x; w[4 * c + 1] = f.y; w[4 * c + 2] = f.z; w[4 * c + 3] = f.w; }
+    }
+    pdl_wait();
+    for (int x = threadIdx.x; x < TT * NCH; x += 256) {
+        const int t = x / NCH, c = x % NCH;
+        const float4 f = t0 + t < T ? *reinterpret_cast<const float4 *>(J.x.f + (size_t) (t0 + t) * J.x.K + J.x_off + c * 4) : make_float4(0, 0, 0, 0);
+        *reinterpret_cast<float4 *>(&xs[t][c * 4]) = f;
+    }
+    __syncthreads();
+    if (m >= M) return;
+    const int nt = min(TT, T - t0);
+    for (int t = 0; t < nt; t++) {
+        float p[NCH];
+#pragma unroll
+        for (int c = 0; c < NCH; c++) {
+            float acc = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 4; i++) acc = __fmaf_rn(w[4 * c + i], xs[t][4 * c + i], acc);
+            p[c] = acc;
+        }
+#pragma unroll
+        for (int o = NCH / 2; o > 0; o >>= 1)
+#pragma unroll
+            for (int l = 0; l < o; l++) p[l] = p[l] + p[l + o];          // lane l of the butterfly step `xor o`
+        const float y = apply_epilogue(J, p[0], t0 + t, m);
+        J.out[(size_t) (t0 + t) * J.ldo + m] = y;
+    }
+}
+
+static bool smallk_ok(const GemvBatch & b) {
+    if (b.T < 16 || b.n_jobs < 1) return false;
+    const uint32_t K = b.job[0].W.K;
+    if (K != 32 && K != 64) return false;
+    for (int j = 0; j < b.n_jobs; j++) {
+        const GemvJob & g = b.job[j];
+        if (g.W.type != T_F32 || g.W.K != K || g.W.M != b.job[0].W.M || g.out == nullptr || g.out_act.f != nullptr) return false;
+        if (g.x_off % 4 != 0 || g.x.K % 4 != 0) return false;
+    }
+    return true;
+}
+
+static cudaError_t launch_smallk(const GemvBatch & b, cudaStream_t st) {
+    const dim3 grid((b.job[0].W.M + 255) / 256, (b.T + 31) / 32, b.n_jobs);
+    if (b.job[0].W.K == 32) return launch_pdl(smallk_kernel<8>, grid, dim3(256), 0, st, b);
+    return launch_pdl(smallk_kernel<16>, grid, dim3(256), 0, st, b);
+}
+
 template <int TYPE>
 static cudaError_t launch_typed(const GemvBatch & b, int total_ctas, cudaStream_t st) {
     const dim3 block(GEMV_WARPS * 32);
@@ -174,6 +238,7 @@ cudaError_t launch_gemv(const GemvBatch & b_in, cudaStream_t st) {
     }
     b.cta_begin[b.n_jobs] = total;
     if (type_quantized(type)) return launch_gemv_async(b, total, st);
+    if (type == T_F32 && smallk_ok(b)) return launch_smallk(b, st);
     if (type == T_F32) return launch_typed<T_F32>(b, total, st);
     if (type == T_F16) return launch_typed<T_F16>(b, total, st);
     return cudaErrorInvalidValue;

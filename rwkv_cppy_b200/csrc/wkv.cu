@@ -60,23 +60,34 @@ cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st) {
     return launch_pdl(wkv4_kernel, grid, dim3(256), 0, st, a);
 }
 
-// Per-head normalisation of `y` over the S threads of a head (ggml norm: double sums).
-// sy: shared [threads]; returns normalised value for this thread.
+// Sum over the S consecutive threads of a head (S = 8..64, groups aligned to S); every thread
+// of the group receives the same double.  Butterfly inside the warp, then (S = 64) the two
+// warp totals through shared memory.  All threads of the CTA must call it.
+template <int S>
+__device__ __forceinline__ double head_sum_d(double v, float * sy, int tid) {
+    constexpr int W = S < 32 ? S : 32;
+#pragma unroll
+    for (int o = W / 2; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    if (S > 32) {
+        double * red = reinterpret_cast<double *>(sy);
+        __syncthreads();
+        if ((tid & 31) == 0) red[tid >> 5] = v;
+        __syncthreads();
+        const int w0 = (tid >> 6) << 1;
+        v = red[w0] + red[w0 + 1];
+    }
+    return v;
+}
+
+// Per-head normalisation of `y` over the S threads of a head (ggml norm: mean and variance
+// accumulated in double, ggml-cpu.c:6906-6923).  sy: shared scratch of >= blockDim floats,
+// 8-byte aligned; returns the normalised value for this thread.
 template <int S>
 __device__ __forceinline__ float head_norm(float y, float * sy, int tid, bool active, float eps) {
-    __syncthreads();
-    sy[tid] = y;
-    __syncthreads();
-    const int base = (tid / S) * S;
-    double s = 0.0;
-    if (active) for (int j = 0; j < S; j++) s += (double) sy[base + j];
+    const double s = head_sum_d<S>(active ? (double) y : 0.0, sy, tid);
     const float mean = (float) (s / S);
     const float vv = __fsub_rn(y, mean);
-    __syncthreads();
-    sy[tid] = __fmul_rn(vv, vv);
-    __syncthreads();
-    double s2 = 0.0;
-    if (active) for (int j = 0; j < S; j++) s2 += (double) sy[base + j];
+    const double s2 = head_sum_d<S>(active ? (double) __fmul_rn(vv, vv) : 0.0, sy, tid);
     const float var = (float) (s2 / S);
     const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(var, eps)));
     return __fmul_rn(vv, scale);
@@ -96,7 +107,7 @@ __device__ __forceinline__ float wkv_combine(const float (&yc)[WKV_CHAINS]) {
 
 template <int S>
 __global__ void wkv5_kernel(const __grid_constant__ WkvArgs a) {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) float sm[];
     constexpr int L = S / WKV_CHAINS > 0 ? S / WKV_CHAINS : 1;
     pdl_trigger();
     const int nthr = blockDim.x;
@@ -222,23 +233,49 @@ __global__ void __launch_bounds__(64) wkv5_seq_kernel(const __grid_constant__ Wk
         __syncthreads();
         const float * b = sm + (c & 1) * BUF;
         const float * sr = b, * sk = b + WKV_TCH * S, * sw = b + 2 * WKV_TCH * S, * sv = b + 3 * WKV_TCH * S;
-#pragma unroll 2
-        for (int t = 0; t < nt; t++) {
+        // 4 tokens per trip: the state chain is the only dependency between tokens, so the loads,
+        // the y chains and the butterflies of the 4 tokens overlap
+        auto step = [&](int t, float & y) {
             const float vj = sv[t * 8 + jl];
-            float y = 0.0f;
+            float kk[L], rr[L], ww[L];
+            if constexpr (L % 4 == 0) {
+#pragma unroll
+                for (int q4 = 0; q4 < L / 4; q4++) {
+                    const float4 k4 = *reinterpret_cast<const float4 *>(sk + t * S + p * L + q4 * 4);
+                    const float4 r4 = *reinterpret_cast<const float4 *>(sr + t * S + p * L + q4 * 4);
+                    kk[4 * q4] = k4.x; kk[4 * q4 + 1] = k4.y; kk[4 * q4 + 2] = k4.z; kk[4 * q4 + 3] = k4.w;
+                    rr[4 * q4] = r4.x; rr[4 * q4 + 1] = r4.y; rr[4 * q4 + 2] = r4.z; rr[4 * q4 + 3] = r4.w;
+                    if (dyn_w) {
+                        const float4 w4 = *reinterpret_cast<const float4 *>(sw + t * S + p * L + q4 * 4);
+                        ww[4 * q4] = w4.x; ww[4 * q4 + 1] = w4.y; ww[4 * q4 + 2] = w4.z; ww[4 * q4 + 3] = w4.w;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int ii = 0; ii < L; ii++) { kk[ii] = sk[t * S + p * L + ii]; rr[ii] = sr[t * S + p * L + ii]; if (dyn_w) ww[ii] = sw[t * S + p * L + ii]; }
+            }
+            y = 0.0f;
 #pragma unroll
             for (int ii = 0; ii < L; ii++) {
-                const int i = p * L + ii;
-                const float kv = __fmul_rn(vj, sk[t * S + i]);
+                const float kv = __fmul_rn(vj, kk[ii]);
                 const float tmp = __fmaf_rn(kv, u[ii], st[ii]);
-                y = __fmaf_rn(tmp, sr[t * S + i], y);
-                st[ii] = __fmaf_rn(st[ii], dyn_w ? sw[t * S + i] : wst[ii], kv);
+                y = __fmaf_rn(tmp, rr[ii], y);
+                st[ii] = __fmaf_rn(st[ii], dyn_w ? ww[ii] : wst[ii], kv);
             }
+        };
+        auto finish = [&](int t, float y) {
             y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 1));
             y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 2));
             y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 4));
             if (p == 0) yraw[(size_t) (t0 + t) * D + h * S + j] = y;
+        };
+        int t = 0;
+        for (; t + 4 <= nt; t += 4) {
+            float y0, y1, y2, y3;
+            step(t, y0); step(t + 1, y1); step(t + 2, y2); step(t + 3, y3);
+            finish(t, y0); finish(t + 1, y1); finish(t + 2, y2); finish(t + 3, y3);
         }
+        for (; t < nt; t++) { float y; step(t, y); finish(t, y); }
         __syncthreads();                                  // everyone is done with this buffer before it is refilled
     }
 #pragma unroll
@@ -248,7 +285,7 @@ __global__ void __launch_bounds__(64) wkv5_seq_kernel(const __grid_constant__ Wk
 // per-head norm + ln_x + gate of raw scan outputs: CTA = 256 consecutive channels of one token
 template <int S>
 __global__ void __launch_bounds__(256) wkv5_norm_kernel(const __grid_constant__ WkvArgs a, const float * __restrict__ yraw) {
-    __shared__ float sy[256];
+    __shared__ __align__(8) float sy[256];
     pdl_trigger();
     pdl_wait();
     const int tid = threadIdx.x, e = blockIdx.x * 256 + tid, D = a.D;
@@ -299,7 +336,7 @@ cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st) {
 // ----------------------------------------------------------------------------------------
 template <int S>
 __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) float sm[];
     pdl_trigger();
     const int nthr = blockDim.x;
     float * s_a = sm, * s_b = sm + nthr, * s_k = sm + 2 * nthr, * s_w = sm + 3 * nthr, * s_r = sm + 4 * nthr, * sy = sm + 5 * nthr;
