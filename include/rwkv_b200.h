@@ -57,6 +57,20 @@ RWKV_API size_t rwkv_b200_batch_launches_per_step(const struct rwkv_b200_batch *
  * Logits of the last token are computed when with_logits != 0. */
 RWKV_API bool   rwkv_b200_sequence_run_timed(struct rwkv_context * ctx, const uint32_t * tokens, size_t n, int with_logits, int iters, double * ms);
 
+/* ---- tensor parallel decode (one process per GPU, NCCL over NVLink) --------------------------
+ * The reference is single-device (rwkv.cpp:86); models too large or too latency-critical for
+ * one GPU are split here: column-parallel key / value / receptance (+ the WKV state of those
+ * channels) and ffn key, row-parallel att output and ffn value, one all-reduce per block, the
+ * vocabulary rows of the head sharded and all-gathered.  RWKV v4, n_embed and the ffn width
+ * divisible by 32 * world_size.
+ *   rank 0: rwkv_b200_tp_unique_id(id); broadcast the 128 bytes to the other ranks by any means;
+ *   every rank: ctx = rwkv_b200_tp_init_from_file(path, rank, world, id)   (device: LOCAL_RANK / rwkv_b200_set_device);
+ *   then rwkv_eval / rwkv_eval_sequence / the batch API, called collectively with the same tokens.
+ * Every rank receives the full logits.  State buffers keep the reference layout; a rank updates
+ * the aa / bb / pp slices of its own channels (the shift states are replicated). */
+RWKV_API bool rwkv_b200_tp_unique_id(void * out_128_bytes);
+RWKV_API struct rwkv_context * rwkv_b200_tp_init_from_file(const char * model_file_path, int rank, int world_size, const void * unique_id_128_bytes);
+
 /* ---- codec / mat-vec hooks (parity tests and the roofline microbenchmark) ------------------ */
 /* type ids are the ggmf ones (rwkv_file_format.inc:5-26): 0 F32, 1 F16, 2 Q4_0, 3 Q4_1, 7 Q5_0, 8 Q5_1, 9 Q8_0 */
 /* Uploads n_rows x n_cols weights given as raw ggml rows, repacks them as the loader does and

@@ -301,6 +301,34 @@ bool rwkv_b200_sequence_run_timed(struct rwkv_context * ctx, const uint32_t * to
     return true;
 }
 
+// ---- tensor parallel ---------------------------------------------------------------------------
+bool rwkv_b200_tp_unique_id(void * out_128_bytes) {
+    g_last_error = RWKV_ERROR_NONE;
+    RB_CHECK(out_128_bytes != nullptr, RWKV_ERROR_ARGS, false, "out is NULL");
+    RB_CHECK(tp_available(), RWKV_ERROR_CTX | RWKV_ERROR_UNSUPPORTED, false, "NCCL (libnccl.so.2) not found");
+    RB_CHECK(tp_unique_id(out_128_bytes), RWKV_ERROR_CTX, false, "ncclGetUniqueId failed");
+    return true;
+}
+
+struct rwkv_context * rwkv_b200_tp_init_from_file(const char * model_file_path, int rank, int world_size, const void * unique_id_128_bytes) {
+    g_last_error = RWKV_ERROR_NONE;
+    RB_CHECK(model_file_path && unique_id_128_bytes, RWKV_ERROR_ARGS, nullptr, "NULL argument");
+    RB_CHECK(world_size >= 2 && rank >= 0 && rank < world_size, RWKV_ERROR_ARGS, nullptr, "Bad rank %d / world size %d", rank, world_size);
+    RB_CHECK(tp_available(), RWKV_ERROR_CTX | RWKV_ERROR_UNSUPPORTED, nullptr, "NCCL (libnccl.so.2) not found");
+    const int dev = pick_device();
+    RB_CHECK(dev >= 0, RWKV_ERROR_CTX | RWKV_ERROR_UNSUPPORTED, nullptr, "No CUDA device: this engine has no CPU path");
+    RB_CUDA(cudaSetDevice(dev), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, nullptr);
+    TpInfo tp; tp.rank = rank; tp.world = world_size;
+    RB_CHECK(tp_comm_init(tp, unique_id_128_bytes), RWKV_ERROR_CTX, nullptr, "ncclCommInitRank failed");
+    Model * model = model_load(model_file_path, tp);
+    if (!model) { tp_comm_destroy(tp); return nullptr; }
+    rwkv_context * ctx = new (std::nothrow) rwkv_context();
+    if (!ctx) { model_release(model); RB_FAIL(RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, nullptr, "Failed to allocate context"); }
+    ctx->model = model; ctx->print_errors = g_print_errors;
+    if (!ctx_setup(ctx)) { ctx_destroy(ctx); return nullptr; }
+    return ctx;
+}
+
 // ---- codec / mat-vec hooks ----------------------------------------------------------------------
 bool rwkv_b200_dequantize(int type, const void * raw, size_t n_rows, size_t n_cols, float * out) {
     g_last_error = RWKV_ERROR_NONE;

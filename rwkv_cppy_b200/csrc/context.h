@@ -25,6 +25,8 @@ int  pick_device();
 void ctx_fail(rwkv_context * ctx, int flags, const char * file, int line, const char * fmt, ...);
 void host_init_state(const rb::Model & m, float * s);
 void model_release(rb::Model * m);
+bool ctx_setup(rwkv_context * ctx);
+void ctx_destroy(rwkv_context * ctx);
 bool capture_graph(rwkv_context * ctx, cudaStream_t st, const rb::Model & m, rb::Workspace & ws, const rb::ForwardArgs & fa, cudaGraphExec_t * out);
 }
 #define CTX_CHECK(ctx, cond, flags, ret, ...) do { if (!(cond)) { rbapi::ctx_fail((ctx), (flags), __FILE__, __LINE__, __VA_ARGS__); return ret; } } while (0)

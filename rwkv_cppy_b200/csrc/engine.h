@@ -1,6 +1,7 @@
 // Model (weights in HBM, shared by clones) and Context (stream, workspace, launch graphs).
 #pragma once
 #include "kernels.h"
+#include "tp.h"
 #include <memory>
 
 namespace rb {
@@ -25,6 +26,7 @@ struct LayerW {
 struct Model {
     std::atomic<int> refcount{1};
     int device = 0;
+    TpInfo tp;                               // tensor-parallel rank / world / communicator (world == 1: none)
     uint32_t n_vocab = 0, n_embed = 0, n_layer = 0, data_type = 0;
     int arch_major = 4, arch_minor = 0;
     int head_count = 0, head_size = 0;
@@ -43,7 +45,7 @@ struct Model {
 };
 
 // Returns nullptr with the thread-local error word set on failure.
-Model * model_load(const char * path);
+Model * model_load(const char * path, const TpInfo & tp = TpInfo());
 
 // Activation workspace for up to `rows` rows.
 struct Workspace {
@@ -58,7 +60,10 @@ struct Workspace {
     float * r = nullptr, * k = nullptr, * v = nullptr, * g = nullptr, * w = nullptr, * a = nullptr, * vgate = nullptr;
     float * ffn_r = nullptr, * m5 = nullptr /* [5][rows][D] */, * v_first = nullptr;
     float * yraw = nullptr;       // [rows][D] raw WKV scan outputs (sequence kernels)
+    float * tp_send = nullptr, * tp_recv = nullptr;   // tensor parallel: [rows][2*D] all-reduce buffers of the ffn ([partial Wv k | r shards])
+    float * tp_att = nullptr;                         // [rows][D] partial att output
     float * logits = nullptr;     // [logit_rows][V]
+    float * logits_part = nullptr; // tensor parallel: this rank's vocabulary slice
     int   logit_rows = 0;
     int * tokens = nullptr;
     ~Workspace();

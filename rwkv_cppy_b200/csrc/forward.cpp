@@ -47,7 +47,13 @@ bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows
             && dalloc(ws, ws.a, n) && dalloc(ws, ws.vgate, n) && dalloc(ws, ws.ffn_r, n) && dalloc(ws, ws.v_first, n);
     if (m.arch_major == 6) ok = ok && dalloc(ws, ws.m5, 5 * n);
     if (m.arch_major >= 5 && rows >= WKV_SEQ_MIN_ROWS) ok = ok && dalloc(ws, ws.yraw, n);
-    ok = ok && dalloc(ws, ws.logits, (size_t) logit_rows * m.n_vocab) && dalloc(ws, ws.tokens, (size_t) rows);
+    if (m.tp.world > 1) {
+        ok = ok && dalloc(ws, ws.tp_send, 2 * n) && dalloc(ws, ws.tp_recv, 2 * n) && dalloc(ws, ws.tp_att, n);
+        ok = ok && cudaMemset(ws.tp_send, 0, 2 * n * sizeof(float)) == cudaSuccess;     // the r-shard half stays zero outside this rank's slice
+    }
+    const size_t v_pad = m.tp.world > 1 ? (size_t) m.tp.world * ((m.n_vocab + m.tp.world - 1) / m.tp.world) : m.n_vocab;
+    ok = ok && dalloc(ws, ws.logits, (size_t) logit_rows * v_pad) && dalloc(ws, ws.tokens, (size_t) rows);
+    if (m.tp.world > 1) ok = ok && dalloc(ws, ws.logits_part, (size_t) logit_rows * (v_pad / m.tp.world));
     if (!ok) return false;
     ws.rows = rows; ws.logit_rows = logit_rows;
     return true;
@@ -150,8 +156,45 @@ struct Pass {
         return a;
     }
 
+    // ---- tensor parallel (v4): column-parallel k / v / r and ffn key / receptance, row-parallel
+    // att output and ffn value, one all-reduce per block -------------------------------
+    void tp_all_reduce(const float * send, float * recv, size_t n) { chk(tp_allreduce(m.tp, send, recv, n, st)); }
+
+    void att_v4_tp(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        const int Dl = (int) l.att_key.M;
+        ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false);
+        gemv({job(l.att_key, ws.mix[0], ws.k, Dl, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, Dl, EPI_STORE),
+              job(l.att_receptance, ws.mix[2], ws.r, Dl, EPI_SIGMOID)}, R);
+        WkvArgs a = wkv_base(layer);
+        a.D = Dl; a.state_D = (int) D; a.chan0 = m.tp.rank * Dl;
+        a.y = ws.y; a.y.K = Dl;
+        a.u = l.time_first; a.decay = l.time_decay;
+        chk(launch_wkv4(a, st));
+        Act yl = ws.y; yl.K = Dl;
+        GemvJob o = job(l.att_output, yl, ws.tp_att, (int) D, m.tp.rank == 0 ? EPI_ADD_AUX : EPI_STORE);   // rank 0 carries the residual
+        o.aux = ws.x; o.ld_aux = (int) D;
+        gemv({o}, R);
+        tp_all_reduce(ws.tp_att, ws.x, (size_t) R * D);
+    }
+
+    void ffn_v4_tp(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        const int Fl = (int) l.ffn_key.M, Dl = (int) l.ffn_receptance.M;
+        ln_mix(layer, false, MIX_LERP, 2, l.ffn_mu, false);
+        GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = Fl;
+        // this rank's slice of r goes straight into the second half of the send buffer (zero elsewhere)
+        GemvJob r = job(l.ffn_receptance, ws.mix[1], ws.tp_send + D + (size_t) m.tp.rank * Dl, 2 * (int) D, EPI_SIGMOID);
+        gemv({k, r}, R);
+        Act kin = ws.ffn_k; kin.K = Fl;
+        gemv({job(l.ffn_value, kin, ws.tp_send, 2 * (int) D, EPI_STORE)}, R);
+        tp_all_reduce(ws.tp_send, ws.tp_recv, (size_t) R * 2 * D);
+        chk(launch_tp_ffn_combine(ws.x, ws.tp_recv, R, (int) D, st));
+    }
+
     void ffn(uint32_t layer) {
         const LayerW & l = m.layers[layer];
+        if (m.tp.world > 1) { ffn_v4_tp(layer); return; }
         if (m.arch_major == 7) {
             ln_mix(layer, false, MIX_SX, 1, l.ffn_mu, false);
             GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
@@ -255,7 +298,7 @@ struct Pass {
         chk(launch_embed_ln0(m.emb, ws.tokens, R, m.ln0_w, m.ln0_b, ws.x, st));
         for (uint32_t i = 0; i < m.n_layer; i++) {
             switch (m.arch_major) {
-                case 4: att_v4(i); break;
+                case 4: if (m.tp.world > 1) att_v4_tp(i); else att_v4(i); break;
                 case 5: att_v5(i); break;
                 case 6: att_v6(i); break;
                 default: att_v7(i); break;
@@ -266,6 +309,12 @@ struct Pass {
             const int rows = fa.batch ? R : 1;
             const float * x = fa.batch ? ws.x : ws.x + (size_t) (R - 1) * D;
             chk(launch_ln_act(x, (int) D, rows, (int) D, m.ln_out_w, m.ln_out_b, ws.head_in, st));
+            if (m.tp.world > 1) {      // vocabulary rows are sharded: gather the slices (equal-sized, zero-padded at the end)
+                const int Vl = (int) ((m.n_vocab + m.tp.world - 1) / m.tp.world);
+                gemv({job(m.head, ws.head_in, ws.logits_part, Vl, EPI_STORE)}, rows);
+                if (rows == 1) chk(tp_allgather(m.tp, ws.logits_part, ws.logits, (size_t) Vl, st));
+                else err = err == cudaSuccess ? cudaErrorNotSupported : err;     // batched logits under TP: not needed by any caller yet
+            } else
             gemv({job(m.head, ws.head_in, ws.logits, (int) m.n_vocab, EPI_STORE)}, rows);
         }
     }

@@ -243,6 +243,7 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
                 case EPI_MULADD_TO:    epilogue_tile<EPI_MULADD_TO, BN>(J, tcol, m, t0, B.T, half_id); break;
                 case EPI_BIAS_SIGMOID: epilogue_tile<EPI_BIAS_SIGMOID, BN>(J, tcol, m, t0, B.T, half_id); break;
                 case EPI_V6_DECAY:     epilogue_tile<EPI_V6_DECAY, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_ADD_AUX:      epilogue_tile<EPI_ADD_AUX, BN>(J, tcol, m, t0, B.T, half_id); break;
                 default:               epilogue_tile<EPI_V7_DECAY, BN>(J, tcol, m, t0, B.T, half_id); break;
             }
             tc_fence_before();

@@ -98,6 +98,7 @@ __device__ __forceinline__ float apply_epilogue_c(const JobT & J, float y, int t
         case EPI_BIAS_SIGMOID: return sigmoidf_ref(__fadd_rn(y, J.vec[m]));
         case EPI_V6_DECAY:     return expf(-expf(__fadd_rn(y, J.vec[m])));
         case EPI_V7_DECAY:     return expf(__fmul_rn(sigmoidf_ref(__fadd_rn(y, J.vec[m])), -0.606531f));
+        case EPI_ADD_AUX:      return __fadd_rn(J.aux[(size_t) t * J.ld_aux + m], y);
         default:               return y;
     }
 }
@@ -115,6 +116,7 @@ __device__ __forceinline__ float apply_epilogue(const JobT & J, float y, int t, 
         case EPI_BIAS_SIGMOID: return apply_epilogue_c<EPI_BIAS_SIGMOID>(J, y, t, m);
         case EPI_V6_DECAY:     return apply_epilogue_c<EPI_V6_DECAY>(J, y, t, m);
         case EPI_V7_DECAY:     return apply_epilogue_c<EPI_V7_DECAY>(J, y, t, m);
+        case EPI_ADD_AUX:      return apply_epilogue_c<EPI_ADD_AUX>(J, y, t, m);
         default:               return y;
     }
 }

@@ -33,6 +33,7 @@ enum Epilogue : int {
     EPI_BIAS_SIGMOID,    // out = sigmoid(y + vec[m])           (v7 a, v-gate)
     EPI_V6_DECAY,        // out = exp(-exp(y + vec[m]))         (rwkv_graph.inc:349-356)
     EPI_V7_DECAY,        // out = exp(-0.606531 * sigmoid(y + vec[m]))   (rwkv_graph.inc:418-426)
+    EPI_ADD_AUX,         // out = aux[t][m] + y                 (tensor parallel: rank 0 folds the residual into its partial sum)
 };
 
 struct GemvJob {
@@ -128,6 +129,7 @@ cudaError_t launch_quantize_act(Act a, int R, cudaStream_t st);
 // ---- WKV recurrences --------------------------------------------------------------------
 struct WkvArgs {
     int R = 1, D = 0, H = 0, S = 0, batch = 0;
+    int state_D = 0, chan0 = 0;           // v4 tensor parallel: the rows hold D local channels [chan0, chan0 + D) of state slots state_D wide (0 = D)
     size_t state_stride = 0;
     const float * state_in = nullptr; float * state_out = nullptr;   // pointers at this layer's att state slot(s)
     const float * r = nullptr, * k = nullptr, * v = nullptr, * w = nullptr, * g = nullptr, * a = nullptr;   // [R][D]
@@ -147,5 +149,8 @@ constexpr int WKV_SEQ_MIN_ROWS = 8;       // sequences at least this long use th
 cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st);   // state slots: aa, bb, pp at state + {0,1,2}*D
 cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st);   // v5.1 / v5.2 / v6 (w != nullptr => per-token decay)
 cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st);
+
+// tensor parallel ffn tail: x[t][m] += recv[t][D + m] * recv[t][m]  (recv = all-reduced [partial Wv k | r shards], 2*D per row)
+cudaError_t launch_tp_ffn_combine(float * x, const float * recv, int R, int D, cudaStream_t st);
 
 } // namespace rb

@@ -12,6 +12,7 @@ namespace rb {
 
 Model::~Model() {
     cudaSetDevice(device);
+    tp_comm_destroy(tp);
     for (void * p : allocations) cudaFree(p);
 }
 
@@ -80,38 +81,83 @@ struct Loader {
 
     // Matrix view: M rows of K weights starting `elem_off` elements into the tensor.
     bool mat_from(const FileTensor * t, size_t M, size_t K, size_t elem_off, DevMat & out) {
-        out.type = t->type; out.M = (uint32_t) M; out.K = (uint32_t) K;
         const size_t blk = type_block(t->type), bb = type_block_bytes(t->type);
         if (K % blk != 0 || elem_off % blk != 0) {
             ok = false; global_fail(RWKV_ERROR_MODEL_PARAMS | RWKV_ERROR_SHAPE, __FILE__, __LINE__, "Parameter %s: row length %llu not a multiple of %llu",
                                     t->name.c_str(), (unsigned long long) K, (unsigned long long) blk);
             return false;
         }
-        const uint8_t * src = t->data + elem_off / blk * bb;
+        return upload(t->type, t->data + elem_off / blk * bb, M, K, out);
+    }
+
+    // Column slice [k0, k0 + Kl) of every row (tensor parallel row-split matrices): gathered on the host.
+    bool mat_cols(const FileTensor * t, size_t M, size_t K, size_t k0, size_t Kl, DevMat & out) {
+        const size_t blk = type_block(t->type), bb = type_block_bytes(t->type);
+        if (K % blk != 0 || k0 % blk != 0 || Kl % blk != 0 || k0 + Kl > K) {
+            ok = false; global_fail(RWKV_ERROR_MODEL_PARAMS | RWKV_ERROR_SHAPE, __FILE__, __LINE__, "Parameter %s: cannot slice columns [%llu, +%llu)",
+                                    t->name.c_str(), (unsigned long long) k0, (unsigned long long) Kl);
+            return false;
+        }
+        const size_t row_b = K / blk * bb, off_b = k0 / blk * bb, len_b = Kl / blk * bb;
+        std::vector<uint8_t> tmp(M * len_b);
+        for (size_t r = 0; r < M; r++) memcpy(tmp.data() + r * len_b, t->data + r * row_b + off_b, len_b);
+        return upload(t->type, tmp.data(), M, Kl, out);
+    }
+
+    bool upload(uint32_t type, const uint8_t * src, size_t M, size_t K, DevMat & out) {
+        out.type = type; out.M = (uint32_t) M; out.K = (uint32_t) K;
+        const size_t blk = type_block(type), bb = type_block_bytes(type);
         const size_t n_blocks = M * K / blk, nbytes = n_blocks * bb;
         out.bytes = nbytes;
         m.weight_bytes += nbytes;
-        if (!type_quantized(t->type)) {
+        if (!type_quantized(type)) {
             void * d = bump(nbytes);
             if (!d) return false;
             if (cudaMemcpy(d, src, nbytes, cudaMemcpyHostToDevice) != cudaSuccess) { ok = false; return false; }
             out.qs = d;
             return true;
         }
-        void * tiled = bump(tiled_bytes(t->type, M, K));
+        void * tiled = bump(tiled_bytes(type, M, K));
         if (!tiled) return false;
         if (nbytes > scratch_size) { ok = false; return false; }
         if (cudaMemcpyAsync(scratch, src, nbytes, cudaMemcpyHostToDevice, st) != cudaSuccess) { ok = false; return false; }
-        if (launch_repack(t->type, scratch, M, K, tiled, st) != cudaSuccess) { ok = false; return false; }
+        if (launch_repack(type, scratch, M, K, tiled, st) != cudaSuccess) { ok = false; return false; }
         if (cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
-        out.qs = tiled; out.rg_stride = (uint32_t) tiled_rg_stride(t->type, K);
+        out.qs = tiled; out.rg_stride = (uint32_t) tiled_rg_stride(type, K);
         if (gemm_tc_enabled() && K >= TC_KB) {                 // second copy in the tensor-core chunk layout (scratch still holds the raw rows)
-            void * tc = bump(tc_bytes(t->type, M, K));
+            void * tc = bump(tc_bytes(type, M, K));
             if (!tc) return false;
-            if (launch_repack_tc(t->type, scratch, M, K, tc, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
+            if (launch_repack_tc(type, scratch, M, K, tc, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
             out.tc = tc; out.tc_kblocks = (uint32_t) ((K + TC_KB - 1) / TC_KB);
         }
         return true;
+    }
+
+    // Tensor-parallel views of a 2-D tensor (K, M): this rank's rows / this rank's columns.
+    bool mat_row_shard(const std::string & name, size_t expect_K, size_t expect_M, DevMat & out) {
+        const FileTensor * t = checked(name, expect_K, expect_M);
+        if (!t) return false;
+        const size_t K = t->ne[0], M = t->ne[1] * t->ne[2], n = (size_t) m.tp.world;
+        const size_t Ml = (M + n - 1) / n, r0 = std::min(M, Ml * m.tp.rank), cnt = std::min(Ml, M - r0);
+        return mat_from(t, cnt, K, r0 * K, out);
+    }
+    bool mat_col_shard(const std::string & name, size_t expect_K, size_t expect_M, DevMat & out) {
+        const FileTensor * t = checked(name, expect_K, expect_M);
+        if (!t) return false;
+        const size_t K = t->ne[0], M = t->ne[1] * t->ne[2], n = (size_t) m.tp.world;
+        if (K % (n * 32) != 0) { ok = false; global_fail(RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, __FILE__, __LINE__, "Parameter %s: %llu columns do not split over %d ranks in blocks of 32", name.c_str(), (unsigned long long) K, m.tp.world); return false; }
+        return mat_cols(t, M, K, K / n * m.tp.rank, K / n, out);
+    }
+    const FileTensor * checked(const std::string & name, size_t expect_K, size_t expect_M) {
+        const FileTensor * t = need(name);
+        if (!t) return nullptr;
+        const size_t K = t->ne[0], M = t->ne[1] * t->ne[2];
+        if ((expect_K && K != expect_K) || (expect_M && M != expect_M)) {
+            ok = false; global_fail(RWKV_ERROR_MODEL_PARAMS | RWKV_ERROR_SHAPE, __FILE__, __LINE__, "Parameter %s has shape (%llu, %llu), expected (%llu, %llu)",
+                                    name.c_str(), (unsigned long long) K, (unsigned long long) M, (unsigned long long) expect_K, (unsigned long long) expect_M);
+            return nullptr;
+        }
+        return t;
     }
 
     // 2-D ggml tensor (K, M); expect_K / expect_M == 0 means "any".
@@ -130,7 +176,7 @@ struct Loader {
 
 } // namespace
 
-Model * model_load(const char * path) {
+Model * model_load(const char * path, const TpInfo & tp) {
     GgmfFile f;
     if (!ggmf_open(path, f)) { g_last_error |= RWKV_ERROR_FILE; return nullptr; }
 
@@ -138,7 +184,7 @@ Model * model_load(const char * path) {
     RB_CUDA(cudaGetDevice(&dev), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, nullptr);
     std::unique_ptr<Model> mp(new Model());
     Model & m = *mp;
-    m.device = dev;
+    m.device = dev; m.tp = tp;
     m.n_vocab = f.n_vocab; m.n_embed = f.n_embed; m.n_layer = f.n_layer; m.data_type = f.data_type;
     RB_CHECK(m.n_layer > 0 && m.n_embed > 0 && m.n_vocab > 0, RWKV_ERROR_MODEL_PARAMS | RWKV_ERROR_SHAPE, nullptr, "Empty model");
 
@@ -163,6 +209,11 @@ Model * model_load(const char * path) {
                  RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr, "Head size %d is not supported (8, 16, 32, 64)", m.head_size);
     }
 
+    const bool TP = tp.world > 1;
+    if (TP) {
+        RB_CHECK(m.arch_major == 4, RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr, "Tensor parallelism is implemented for RWKV v4 models");
+        RB_CHECK(m.n_embed % (32 * tp.world) == 0, RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr, "n_embed %u does not split over %d ranks in blocks of 32", m.n_embed, tp.world);
+    }
     Loader L(f, m);
     size_t arena = 0, scratch = 0;
     for (const FileTensor & t : f.tensors) {
@@ -193,10 +244,17 @@ Model * model_load(const char * path) {
         const std::string p = "blocks." + std::to_string(i) + ".";
         l.ln1_w = L.vec(p + "ln1.weight", D); l.ln1_b = L.vec(p + "ln1.bias", D);
         l.ln2_w = L.vec(p + "ln2.weight", D); l.ln2_b = L.vec(p + "ln2.bias", D);
-        L.mat(p + "att.key.weight", D, D, l.att_key);
-        L.mat(p + "att.value.weight", D, D, l.att_value);
-        L.mat(p + "att.receptance.weight", D, D, l.att_receptance);
-        L.mat(p + "att.output.weight", D, D, l.att_output);
+        if (TP) {     // column-parallel k, v, r (output channels), row-parallel output (input channels)
+            L.mat_row_shard(p + "att.key.weight", D, D, l.att_key);
+            L.mat_row_shard(p + "att.value.weight", D, D, l.att_value);
+            L.mat_row_shard(p + "att.receptance.weight", D, D, l.att_receptance);
+            L.mat_col_shard(p + "att.output.weight", D, D, l.att_output);
+        } else {
+            L.mat(p + "att.key.weight", D, D, l.att_key);
+            L.mat(p + "att.value.weight", D, D, l.att_value);
+            L.mat(p + "att.receptance.weight", D, D, l.att_receptance);
+            L.mat(p + "att.output.weight", D, D, l.att_output);
+        }
         switch (m.arch_major) {
             case 4:
                 l.att_mu[0] = L.vec(p + "att.time_mix_k", D); l.att_mu[1] = L.vec(p + "att.time_mix_v", D); l.att_mu[2] = L.vec(p + "att.time_mix_r", D);
@@ -253,14 +311,21 @@ Model * model_load(const char * path) {
         } else {
             l.ffn_mu[0] = L.vec(p + "ffn.time_mix_k", D); l.ffn_mu[1] = L.vec(p + "ffn.time_mix_r", D);
         }
-        L.mat(p + "ffn.key.weight", D, 0, l.ffn_key);
-        L.mat(p + "ffn.value.weight", l.ffn_key.M, D, l.ffn_value);
-        if (m.arch_major != 7) L.mat(p + "ffn.receptance.weight", D, D, l.ffn_receptance);
+        if (TP) {
+            L.mat_row_shard(p + "ffn.key.weight", D, 0, l.ffn_key);
+            L.mat_col_shard(p + "ffn.value.weight", 0, D, l.ffn_value);
+            L.mat_row_shard(p + "ffn.receptance.weight", D, D, l.ffn_receptance);
+            if (L.ok && l.ffn_value.K != l.ffn_key.M) { L.ok = false; global_fail(RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, __FILE__, __LINE__, "ffn width does not split evenly over %d ranks", tp.world); }
+        } else {
+            L.mat(p + "ffn.key.weight", D, 0, l.ffn_key);
+            L.mat(p + "ffn.value.weight", l.ffn_key.M, D, l.ffn_value);
+            if (m.arch_major != 7) L.mat(p + "ffn.receptance.weight", D, D, l.ffn_receptance);
+        }
         m.ffn_dim = std::max(m.ffn_dim, (int) l.ffn_key.M);
     }
     if (L.ok) {
         m.ln_out_w = L.vec("ln_out.weight", D); m.ln_out_b = L.vec("ln_out.bias", D);
-        L.mat("head.weight", D, V, m.head);
+        if (TP) L.mat_row_shard("head.weight", D, V, m.head); else L.mat("head.weight", D, V, m.head);
     }
     cudaStreamSynchronize(L.st);
     cudaStreamDestroy(L.st);

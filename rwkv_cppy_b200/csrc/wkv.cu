@@ -21,14 +21,15 @@ namespace rb {
 __global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvArgs a) {
     pdl_trigger();
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    const int D = a.D;
+    const int D = a.D;                          // channels in the rows (a shard under tensor parallelism)
+    const int SD = a.state_D ? a.state_D : D;   // width of a state slot
     const bool valid = e < D;
     const int stream = a.batch ? blockIdx.y : 0;
-    const size_t soff = (size_t) stream * a.state_stride;
+    const size_t soff = (size_t) stream * a.state_stride + a.chan0;
     float aa = 0, bb = 0, pp = 0, u = 0, w = 0;
     if (valid) {
-        aa = a.state_in[soff + e]; bb = a.state_in[soff + D + e]; pp = a.state_in[soff + 2 * D + e];
-        u = a.u[e]; w = a.decay[e];
+        aa = a.state_in[soff + e]; bb = a.state_in[soff + SD + e]; pp = a.state_in[soff + 2 * SD + e];
+        u = a.u[a.chan0 + e]; w = a.decay[a.chan0 + e];
     }
     pdl_wait();                                 // r, k, v come from the preceding mat-vec; the input state is read-only
     const int steps = a.batch ? 1 : a.R;
@@ -52,7 +53,7 @@ __global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvAr
         }
         act_store_block(a.y, row, e, valid, out);
     }
-    if (valid) { a.state_out[soff + e] = aa; a.state_out[soff + D + e] = bb; a.state_out[soff + 2 * D + e] = pp; }
+    if (valid) { a.state_out[soff + e] = aa; a.state_out[soff + SD + e] = bb; a.state_out[soff + 2 * SD + e] = pp; }
 }
 
 cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st) {
@@ -428,6 +429,19 @@ cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st) {
         case 64: return launch_wkv7_t<64>(a, st);
         default: return cudaErrorInvalidValue;
     }
+}
+
+// ---- tensor parallel: x += r * (Wv k) after the all-reduce of [partial Wv k | r shards] ----
+__global__ void __launch_bounds__(256) tp_ffn_combine_kernel(float * __restrict__ x, const float * __restrict__ recv, int D) {
+    pdl_trigger();
+    pdl_wait();
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    const size_t row = blockIdx.y;
+    if (e < D) x[row * D + e] = __fadd_rn(x[row * D + e], __fmul_rn(recv[row * 2 * D + D + e], recv[row * 2 * D + e]));
+}
+
+cudaError_t launch_tp_ffn_combine(float * x, const float * recv, int R, int D, cudaStream_t st) {
+    return launch_pdl(tp_ffn_combine_kernel, dim3((D + 255) / 256, R), dim3(256), 0, st, x, recv, D);
 }
 
 } // namespace rb

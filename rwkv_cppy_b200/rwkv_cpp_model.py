@@ -33,7 +33,11 @@ class RWKVModel:
         if not (gpu_layer_count >= 0):
             raise ValueError("GPU layer count must be >= 0")
         self._library = shared_library
-        self._ctx = shared_library.rwkv_init_from_file(model_path, thread_count, gpu_layer_count)
+        tp = kwargs.get("tensor_parallel")      # additive: (rank, world_size, unique_id) -> one shard of the model per process / GPU
+        if tp is not None:
+            self._ctx = shared_library.rwkv_b200_tp_init_from_file(model_path, int(tp[0]), int(tp[1]), tp[2])
+        else:
+            self._ctx = shared_library.rwkv_init_from_file(model_path, thread_count, gpu_layer_count)
         self._state_buffer_element_count = shared_library.rwkv_get_state_buffer_element_count(self._ctx)
         self._logits_buffer_element_count = shared_library.rwkv_get_logits_buffer_element_count(self._ctx)
         self._valid = True

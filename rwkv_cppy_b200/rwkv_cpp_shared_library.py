@@ -79,6 +79,8 @@ class RWKVSharedLibrary:
         sig("rwkv_b200_matrix_mul_tc", [vp, P_FLOAT, sz, P_FLOAT], b)
         sig("rwkv_b200_matrix_bench_tc", [vp, sz, ctypes.c_int, ctypes.POINTER(ctypes.c_double)], b)
         sig("rwkv_b200_matrix_bytes", [vp], sz)
+        sig("rwkv_b200_tp_unique_id", [vp], b)
+        sig("rwkv_b200_tp_init_from_file", [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, vp], vp)
         self.nullptr = ctypes.cast(0, P_FLOAT)
 
     # ---- reference surface ---------------------------------------------------------------
@@ -86,6 +88,22 @@ class RWKVSharedLibrary:
         ptr = self.library.rwkv_init_from_file(model_file_path.encode("utf-8"), ctypes.c_uint32(thread_count), ctypes.c_uint32(offload_layers))
         if not ptr:
             raise ValueError(f"rwkv_init_from_file failed (error 0x{self.library.rwkv_get_last_error(None):x}), check stderr")
+        return RWKVContext(ptr)
+
+    # ---- tensor parallel (additive) -------------------------------------------------------
+    def rwkv_b200_tp_unique_id(self) -> bytes:
+        """128-byte NCCL unique id; create on rank 0 and broadcast it to the other ranks."""
+        buf = ctypes.create_string_buffer(128)
+        if not self.library.rwkv_b200_tp_unique_id(buf):
+            raise ValueError("rwkv_b200_tp_unique_id failed (NCCL not available?)")
+        return buf.raw
+
+    def rwkv_b200_tp_init_from_file(self, model_file_path: str, rank: int, world_size: int, unique_id: bytes) -> RWKVContext:
+        assert len(unique_id) == 128
+        buf = ctypes.create_string_buffer(unique_id, 128)
+        ptr = self.library.rwkv_b200_tp_init_from_file(model_file_path.encode("utf-8"), rank, world_size, buf)
+        if not ptr:
+            raise ValueError(f"rwkv_b200_tp_init_from_file failed (error 0x{self.library.rwkv_get_last_error(None):x}), check stderr")
         return RWKVContext(ptr)
 
     def rwkv_clone_context(self, ctx: RWKVContext, thread_count: int) -> RWKVContext:
