@@ -452,14 +452,71 @@ def run_streams(args):
     return out
 
 
+def run_tp(args):
+    """BASELINE configs[4]: v4 14B-shape, single-stream decode tensor-parallel over the ranks (NCCL)."""
+    import rwkv_cppy_b200
+    from rwkv_cppy_b200 import synth
+    d = Dist()
+    lib = rwkv_cppy_b200.load_rwkv_shared_library()
+    lib.library.rwkv_b200_set_device(d.local)
+    shape = args.shape or "v4-14b"
+    fmt = args.format or "FP16-to-Q4_1"
+    if d.rank == 0:
+        synth.ensure_model(lib, shape, fmt)
+    d.barrier()
+    path = synth.ensure_model(lib, shape, fmt)
+    if d.world > 1:
+        ids = [lib.rwkv_b200_tp_unique_id() if d.rank == 0 else None]
+        d.dist.broadcast_object_list(ids, src=0)
+        model = rwkv_cppy_b200.RWKVModel(lib, path, tensor_parallel=(d.rank, d.world, ids[0]))
+    else:
+        model = rwkv_cppy_b200.RWKVModel(lib, path)
+    batch = model.create_batch(1)
+    K, W = args.steps, max(args.warmup, 3)
+    toks = np.random.default_rng(1).integers(0, model.n_vocab, size=(W + K, 1)).astype(np.uint32)     # same stream on every rank
+    batch.run_timed(toks[:W], True)
+    d.barrier()
+    sampler = ClockSampler(d.local); sampler.start()
+    ms = batch.run_timed(toks[W:], True)
+    d.barrier()
+    clocks = sampler.stop()
+    ms_max = d.max(ms)
+    # end to end through the C ABI: host state in / out and logits out on every rank
+    state = np.zeros(model.state_len, np.float32); logits = np.zeros(model.n_vocab, np.float32)
+    n_e2e = min(K, 16)
+    d.barrier()
+    t0 = time.perf_counter()
+    for i in range(n_e2e):
+        assert lib.library.rwkv_eval(model._ctx.ptr, int(toks[W + i, 0]), state.ctypes.data_as(PF), state.ctypes.data_as(PF), logits.ctypes.data_as(PF))
+    e2e = d.max((time.perf_counter() - t0) / n_e2e)
+    launches = batch.launches_per_step(True)
+    shp = synth.SHAPES[shape]
+    wbytes = os.path.getsize(path)
+    out = None
+    if d.rank == 0:
+        step_ms = ms_max / K
+        out = {"metric": f"decode tokens/s ({shape} {fmt}, 1 stream, tensor parallel over {d.world} GPU)", "value": K / (ms_max * 1e-3), "unit": "tokens/s",
+               "n_gpus": d.world, "steps": K, "warmup": W, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+               "dtype": "int8 dp4a blocks + f32 accumulate" if "Q" in fmt else "f16 weights, f32 accumulate", "data": "synthetic",
+               "config": {"workload": f"{shape} {fmt} single-stream decode, TP={d.world} (column/row-split weights, NCCL all-reduce x2 per layer + logits all-gather)",
+                          "file_bytes": wbytes, "bytes_per_gpu_per_step": wbytes / d.world,
+                          "hbm_gbs_per_gpu": wbytes / d.world / (step_ms * 1e-3) / 1e9, "layers": shp.n_layer},
+               "clocks": clocks, "gpu_launches": launches * K,
+               "e2e": {"value": 1.0 / e2e, "unit": "tokens/s", "h2d_bytes_per_step": model.state_len * 4 + 4, "d2h_bytes_per_step": (model.state_len + model.n_vocab) * 4,
+                       "api": "rwkv_eval on every rank (host state in/out, full logits out)"}}
+    batch.free(); model.free(); d.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=256)
     ap.add_argument("--warmup", type=int, default=16)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="decode", choices=["decode", "gemv", "prefill", "streams"])
+    ap.add_argument("--workload", default="decode", choices=["decode", "gemv", "prefill", "streams", "tp"])
     ap.add_argument("--shape", default=None)
+    ap.add_argument("--format", default=None, help="tp workload: model format (FP16 or FP16-to-Q4_1)")
     ap.add_argument("--tokens", type=int, default=1024)
     ap.add_argument("--streams", type=int, default=256)
     ap.add_argument("--only", type=int, default=None, help="gemv workload: index of the single shape to run")
@@ -468,7 +525,7 @@ def main():
     if args.impl == "reference":
         out = run_reference(args)
     else:
-        out = {"decode": run_decode, "gemv": run_gemv, "prefill": run_prefill, "streams": run_streams}[args.workload](args)
+        out = {"decode": run_decode, "gemv": run_gemv, "prefill": run_prefill, "streams": run_streams, "tp": run_tp}[args.workload](args)
     if out is not None:
         print(json.dumps(out), flush=True)
 
