@@ -469,6 +469,10 @@ def run_tp(args):
         ids = [lib.rwkv_b200_tp_unique_id() if d.rank == 0 else None]
         d.dist.broadcast_object_list(ids, src=0)
         model = rwkv_cppy_b200.RWKVModel(lib, path, tensor_parallel=(d.rank, d.world, ids[0]))
+        if os.environ.get("RWKV_B200_TP_NCCL_ONLY") != "1":      # one-shot all-reduce over NVLink peer memory instead of NCCL
+            handles = [None] * d.world
+            d.dist.all_gather_object(handles, lib.rwkv_b200_tp_ipc_handle(model._ctx))
+            lib.rwkv_b200_tp_connect(model._ctx, handles)
     else:
         model = rwkv_cppy_b200.RWKVModel(lib, path)
     batch = model.create_batch(1)
@@ -498,7 +502,8 @@ def run_tp(args):
         out = {"metric": f"decode tokens/s ({shape} {fmt}, 1 stream, tensor parallel over {d.world} GPU)", "value": K / (ms_max * 1e-3), "unit": "tokens/s",
                "n_gpus": d.world, "steps": K, "warmup": W, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                "dtype": "int8 dp4a blocks + f32 accumulate" if "Q" in fmt else "f16 weights, f32 accumulate", "data": "synthetic",
-               "config": {"workload": f"{shape} {fmt} single-stream decode, TP={d.world} (column/row-split weights, NCCL all-reduce x2 per layer + logits all-gather)",
+               "config": {"workload": f"{shape} {fmt} single-stream decode, TP={d.world} (column/row-split weights, all-reduce x2 per layer + logits all-gather)",
+                          "collective": "NCCL" if os.environ.get("RWKV_B200_TP_NCCL_ONLY") == "1" or d.world == 1 else "one-shot P2P kernel over NVLink peer memory (csrc/tp_p2p.cu)",
                           "file_bytes": wbytes, "bytes_per_gpu_per_step": wbytes / d.world,
                           "hbm_gbs_per_gpu": wbytes / d.world / (step_ms * 1e-3) / 1e9, "layers": shp.n_layer},
                "clocks": clocks, "gpu_launches": launches * K,

@@ -70,6 +70,13 @@ RWKV_API bool   rwkv_b200_sequence_run_timed(struct rwkv_context * ctx, const ui
  * the aa / bb / pp slices of its own channels (the shift states are replicated). */
 RWKV_API bool rwkv_b200_tp_unique_id(void * out_128_bytes);
 RWKV_API struct rwkv_context * rwkv_b200_tp_init_from_file(const char * model_file_path, int rank, int world_size, const void * unique_id_128_bytes);
+/* Optional, right after init and before the first eval: replaces the NCCL calls on the small
+ * per-layer vectors by a one-shot all-reduce over NVLink peer memory (one kernel per collective:
+ * P2P stores into every peer's inbox + epoch flags; csrc/tp_p2p.cu).  Every rank exports a
+ * 64-byte CUDA IPC handle, the host gathers the world_size handles in rank order and gives the
+ * table to every rank.  RWKV_B200_TP_NCCL_ONLY=1 keeps NCCL (the baseline it is measured against). */
+RWKV_API bool rwkv_b200_tp_ipc_handle(struct rwkv_context * ctx, void * out_64_bytes);
+RWKV_API bool rwkv_b200_tp_connect(struct rwkv_context * ctx, const void * handles_world_x_64_bytes);
 
 /* ---- codec / mat-vec hooks (parity tests and the roofline microbenchmark) ------------------ */
 /* type ids are the ggmf ones (rwkv_file_format.inc:5-26): 0 F32, 1 F16, 2 Q4_0, 3 Q4_1, 7 Q5_0, 8 Q5_1, 9 Q8_0 */

@@ -329,6 +329,23 @@ struct rwkv_context * rwkv_b200_tp_init_from_file(const char * model_file_path, 
     return ctx;
 }
 
+bool rwkv_b200_tp_ipc_handle(struct rwkv_context * ctx, void * out_64_bytes) {
+    RB_CHECK(ctx && out_64_bytes, RWKV_ERROR_ARGS, false, "NULL argument");
+    CTX_CHECK(ctx, ctx->model->tp.world > 1, RWKV_ERROR_ARGS, false, "Not a tensor-parallel context");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->model->device), false);
+    CTX_CHECK(ctx, tp_p2p_alloc(ctx->model->tp, out_64_bytes), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, false, "Failed to allocate / export the peer-memory region");
+    return true;
+}
+
+bool rwkv_b200_tp_connect(struct rwkv_context * ctx, const void * handles) {
+    RB_CHECK(ctx && handles, RWKV_ERROR_ARGS, false, "NULL argument");
+    CTX_CHECK(ctx, ctx->model->tp.world > 1, RWKV_ERROR_ARGS, false, "Not a tensor-parallel context");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->model->device), false);
+    CTX_CHECK(ctx, tp_p2p_connect(ctx->model->tp, handles), RWKV_ERROR_CTX, false, "Failed to map the peers' memory (no P2P / NVLink access?)");
+    for (int i = 0; i < 2; i++) if (ctx->graph[i]) { cudaGraphExecDestroy(ctx->graph[i]); ctx->graph[i] = nullptr; }   // captured with NCCL nodes
+    return true;
+}
+
 // ---- codec / mat-vec hooks ----------------------------------------------------------------------
 bool rwkv_b200_dequantize(int type, const void * raw, size_t n_rows, size_t n_cols, float * out) {
     g_last_error = RWKV_ERROR_NONE;

@@ -4,6 +4,7 @@
 #include <dlfcn.h>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 
 namespace rb {
 
@@ -57,16 +58,24 @@ bool tp_comm_init(TpInfo & tp, const void * id128) {
 }
 
 void tp_comm_destroy(TpInfo & tp) {
+    tp_p2p_destroy(tp);
     if (tp.comm && api().ok) api().CommDestroy(tp.comm);
     tp.comm = nullptr;
 }
 
+static bool use_p2p(const TpInfo & tp, size_t n) {
+    static const bool off = [] { const char * e = getenv("RWKV_B200_TP_NCCL_ONLY"); return e && e[0] == '1'; }();
+    return !off && tp.p2p.connected && n <= TP_NMAX;
+}
+
 cudaError_t tp_allreduce(const TpInfo & tp, const float * send, float * recv, size_t n, cudaStream_t st) {
+    if (use_p2p(tp, n)) return tp_p2p_collective(tp, send, recv, n, false, st);
     if (!tp.comm) return cudaErrorInvalidValue;
     return api().AllReduce(send, recv, n, NCCL_FLOAT32, NCCL_SUM, tp.comm, st) == 0 ? cudaSuccess : cudaErrorUnknown;
 }
 
 cudaError_t tp_allgather(const TpInfo & tp, const float * send, float * recv, size_t n, cudaStream_t st) {
+    if (use_p2p(tp, n)) return tp_p2p_collective(tp, send, recv, n, true, st);
     if (!tp.comm) return cudaErrorInvalidValue;
     return api().AllGather(send, recv, n, NCCL_FLOAT32, tp.comm, st) == 0 ? cudaSuccess : cudaErrorUnknown;
 }

@@ -1,0 +1,131 @@
+// One-shot all-reduce / all-gather over NVLink peer memory for the small vectors of
+// tensor-parallel decode ([D] or [2D] floats twice per layer, the logits shards once per token).
+// NCCL needs ~20 us for these latency-bound collectives; here a rank pushes its vector straight
+// into an inbox in every peer's HBM (P2P stores), publishes a per-CTA epoch flag with release
+// semantics and polls its own flags, so the cost is one NVLink round trip.  Each CTA owns a
+// fixed slice of the vector, which removes any grid-wide synchronisation: CTA c of rank a only
+// waits for CTA c of the other ranks.  The sum runs over the slots in rank order on every rank,
+// so all ranks hold bit-identical results (the replicated layer norms stay in lockstep).
+// Two inbox generations alternate by epoch parity: a peer can be at most one call ahead.
+#include "tp.h"
+#include "launch.cuh"
+#include <cstdio>
+#include <cstring>
+
+namespace rb {
+
+struct P2pArgs {
+    uint8_t * peer[TP_MAX_WORLD];
+    int rank, world;
+    const float * send; float * recv;
+    unsigned n;            // floats contributed by this rank
+    int gather;            // 0: recv[i] = sum_r slot_r[i];  1: recv[r * n + i] = slot_r[i]
+};
+
+__device__ __forceinline__ uint32_t * region_flags(uint8_t * base) { return reinterpret_cast<uint32_t *>(base); }
+__device__ __forceinline__ uint32_t * region_epoch(uint8_t * base) { return reinterpret_cast<uint32_t *>(base) + TP_MAX_WORLD * TP_CTAS; }
+__device__ __forceinline__ uint32_t * region_error(uint8_t * base) { return reinterpret_cast<uint32_t *>(base) + TP_MAX_WORLD * TP_CTAS + TP_CTAS; }
+__device__ __forceinline__ float * region_inbox(uint8_t * base, int world, int parity, int src) {
+    return reinterpret_cast<float *>(base + 4096) + ((size_t) parity * world + src) * TP_NMAX;
+}
+
+__global__ void __launch_bounds__(256) tp_p2p_kernel(const __grid_constant__ P2pArgs a) {
+    pdl_trigger();
+    const int cta = blockIdx.x, tid = threadIdx.x;
+    uint8_t * mine = a.peer[a.rank];
+    // this CTA's slice, in float4 units
+    const unsigned n4 = (a.n + 3) / 4, per = (n4 + TP_CTAS - 1) / TP_CTAS;
+    const unsigned lo = min(n4, per * cta), hi = min(n4, lo + per);
+    pdl_wait();                                              // `send` comes from the preceding kernel; the previous collective
+                                                             // (a few launches back, possibly still running under PDL) owns the epoch until it exits
+    const uint32_t e = region_epoch(mine)[cta] + 1;          // this CTA's call counter (only this CTA writes it)
+    const int par = e & 1;
+    for (unsigned i = lo + tid; i < hi; i += 256) {
+        float4 v;
+        if (4 * i + 3 < a.n) v = reinterpret_cast<const float4 *>(a.send)[i];
+        else { v.x = 4 * i < a.n ? a.send[4 * i] : 0.0f; v.y = 4 * i + 1 < a.n ? a.send[4 * i + 1] : 0.0f; v.z = 4 * i + 2 < a.n ? a.send[4 * i + 2] : 0.0f; v.w = 0.0f; }
+        for (int p = 0; p < a.world; p++) reinterpret_cast<float4 *>(region_inbox(a.peer[p], a.world, par, a.rank))[i] = v;
+    }
+    __syncthreads();
+    if (tid < a.world) {
+        __threadfence_system();
+        // publish: flags[src = me][cta] on peer `tid`
+        uint32_t * f = region_flags(a.peer[tid]) + a.rank * TP_CTAS + cta;
+        asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(f), "r"(e) : "memory");
+        // wait for source rank `tid` to have delivered epoch e into my inbox
+        const uint32_t * w = region_flags(mine) + tid * TP_CTAS + cta;
+        uint32_t seen = 0;
+        const long long t0 = clock64();
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(w) : "memory");
+            if ((int) (seen - e) >= 0) break;
+            if (clock64() - t0 > 4000000000LL) { *region_error(mine) = 1; break; }      // ~2 s: a peer is gone; never hang the GPU
+        }
+    }
+    __syncthreads();
+    for (unsigned i = lo + tid; i < hi; i += 256) {
+        if (a.gather) {
+            for (int r = 0; r < a.world; r++) {
+                const float4 v = reinterpret_cast<const float4 *>(region_inbox(mine, a.world, par, r))[i];
+                float * o = a.recv + (size_t) r * a.n + 4 * i;
+                if (4 * i + 3 < a.n && (((size_t) r * a.n) & 3) == 0) *reinterpret_cast<float4 *>(o) = v;
+                else { if (4 * i < a.n) o[0] = v.x; if (4 * i + 1 < a.n) o[1] = v.y; if (4 * i + 2 < a.n) o[2] = v.z; if (4 * i + 3 < a.n) o[3] = v.w; }
+            }
+        } else {
+            float4 s = reinterpret_cast<const float4 *>(region_inbox(mine, a.world, par, 0))[i];
+            for (int r = 1; r < a.world; r++) {
+                const float4 v = reinterpret_cast<const float4 *>(region_inbox(mine, a.world, par, r))[i];
+                s.x = __fadd_rn(s.x, v.x); s.y = __fadd_rn(s.y, v.y); s.z = __fadd_rn(s.z, v.z); s.w = __fadd_rn(s.w, v.w);
+            }
+            if (4 * i + 3 < a.n) reinterpret_cast<float4 *>(a.recv)[i] = s;
+            else { if (4 * i < a.n) a.recv[4 * i] = s.x; if (4 * i + 1 < a.n) a.recv[4 * i + 1] = s.y; if (4 * i + 2 < a.n) a.recv[4 * i + 2] = s.z; }
+        }
+    }
+    if (tid == 0) region_epoch(mine)[cta] = e;
+}
+
+bool tp_p2p_alloc(TpInfo & tp, void * handle_out_64) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (tp.world < 2 || tp.world > TP_MAX_WORLD) return false;
+    if (!tp.p2p.base) {
+        if (cudaMalloc(&tp.p2p.base, tp_region_bytes(tp.world)) != cudaSuccess) { tp.p2p.base = nullptr; return false; }
+        if (cudaMemset(tp.p2p.base, 0, tp_region_bytes(tp.world)) != cudaSuccess) return false;
+        if (cudaDeviceSynchronize() != cudaSuccess) return false;
+    }
+    cudaIpcMemHandle_t h;
+    if (cudaIpcGetMemHandle(&h, tp.p2p.base) != cudaSuccess) return false;
+    memcpy(handle_out_64, &h, 64);
+    return true;
+}
+
+bool tp_p2p_connect(TpInfo & tp, const void * handles) {
+    if (!tp.p2p.base) return false;
+    for (int r = 0; r < tp.world; r++) {
+        if (r == tp.rank) { tp.p2p.peer[r] = (uint8_t *) tp.p2p.base; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const uint8_t *) handles + (size_t) r * 64, 64);
+        void * p = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { fprintf(stderr, "cudaIpcOpenMemHandle(rank %d) failed: %s\n", r, cudaGetErrorString(e)); return false; }
+        tp.p2p.peer[r] = (uint8_t *) p;
+    }
+    tp.p2p.connected = true;
+    return true;
+}
+
+void tp_p2p_destroy(TpInfo & tp) {
+    for (int r = 0; r < tp.world; r++)
+        if (r != tp.rank && tp.p2p.peer[r]) cudaIpcCloseMemHandle(tp.p2p.peer[r]);
+    if (tp.p2p.base) cudaFree(tp.p2p.base);
+    tp.p2p = TpPeer();
+}
+
+cudaError_t tp_p2p_collective(const TpInfo & tp, const float * send, float * recv, size_t n, bool gather, cudaStream_t st) {
+    if (!tp.p2p.connected || n > TP_NMAX) return cudaErrorInvalidValue;
+    P2pArgs a;
+    for (int r = 0; r < TP_MAX_WORLD; r++) a.peer[r] = r < tp.world ? tp.p2p.peer[r] : nullptr;
+    a.rank = tp.rank; a.world = tp.world; a.send = send; a.recv = recv; a.n = (unsigned) n; a.gather = gather ? 1 : 0;
+    return launch_pdl(tp_p2p_kernel, dim3(TP_CTAS), dim3(256), 0, st, a);
+}
+
+} // namespace rb

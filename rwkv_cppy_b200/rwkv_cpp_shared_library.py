@@ -81,6 +81,8 @@ class RWKVSharedLibrary:
         sig("rwkv_b200_matrix_bytes", [vp], sz)
         sig("rwkv_b200_tp_unique_id", [vp], b)
         sig("rwkv_b200_tp_init_from_file", [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, vp], vp)
+        sig("rwkv_b200_tp_ipc_handle", [vp, vp], b)
+        sig("rwkv_b200_tp_connect", [vp, vp], b)
         self.nullptr = ctypes.cast(0, P_FLOAT)
 
     # ---- reference surface ---------------------------------------------------------------
@@ -105,6 +107,18 @@ class RWKVSharedLibrary:
         if not ptr:
             raise ValueError(f"rwkv_b200_tp_init_from_file failed (error 0x{self.library.rwkv_get_last_error(None):x}), check stderr")
         return RWKVContext(ptr)
+
+    def rwkv_b200_tp_ipc_handle(self, ctx: RWKVContext) -> bytes:
+        buf = ctypes.create_string_buffer(64)
+        if not self.library.rwkv_b200_tp_ipc_handle(ctx.ptr, buf):
+            raise ValueError("rwkv_b200_tp_ipc_handle failed, check stderr")
+        return buf.raw
+
+    def rwkv_b200_tp_connect(self, ctx: RWKVContext, handles: List[bytes]) -> None:
+        blob = b"".join(handles)
+        buf = ctypes.create_string_buffer(blob, len(blob))
+        if not self.library.rwkv_b200_tp_connect(ctx.ptr, buf):
+            raise ValueError("rwkv_b200_tp_connect failed, check stderr")
 
     def rwkv_clone_context(self, ctx: RWKVContext, thread_count: int) -> RWKVContext:
         ptr = self.library.rwkv_clone_context(ctx.ptr, ctypes.c_uint32(thread_count))

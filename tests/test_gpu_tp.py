@@ -16,13 +16,15 @@ def n_gpus():
     return torch.cuda.device_count()
 
 
+@pytest.mark.parametrize("collective", ["p2p", "nccl"])
 @pytest.mark.parametrize("fmt", ["FP16", "FP16-to-Q4_1"])
-def test_tp2_matches_single_gpu(fmt):
+def test_tp2_matches_single_gpu(fmt, collective):
     if n_gpus() < 2:
         pytest.skip("needs 2 GPUs")
+    env = dict(os.environ, RWKV_B200_TP_NCCL_ONLY="1" if collective == "nccl" else "0")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", "29541", os.path.join(ROOT, "tests", "tp_worker.py"), "v4-mini", fmt]
-    p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600, env=env)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
     line = [l for l in p.stdout.splitlines() if l.startswith("TPRESULT ")][-1]
     r = json.loads(line[len("TPRESULT "):])

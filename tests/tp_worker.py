@@ -24,6 +24,10 @@ def main():
     ids = [lib.rwkv_b200_tp_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(ids, src=0)
     model = rwkv_cppy_b200.RWKVModel(lib, path, tensor_parallel=(rank, world, ids[0]))
+    if os.environ.get("RWKV_B200_TP_NCCL_ONLY") != "1":          # one-shot collectives over peer memory
+        handles = [None] * world
+        dist.all_gather_object(handles, lib.rwkv_b200_tp_ipc_handle(model._ctx))
+        lib.rwkv_b200_tp_connect(model._ctx, handles)
     toks = [int(t) for t in np.random.default_rng(3).integers(0, model.n_vocab, size=24)]
     state, logits = None, None
     for t in toks:
