@@ -60,7 +60,7 @@ __device__ __forceinline__ void act_store_block(const Act & a, size_t row, int e
     const int   q  = valid ? __float2int_rn(__fmul_rn(v, id)) : 0;
     const int   sum = warp_sum_i(q);
     if (valid) a.q[row * a.K + e] = (int8_t) q;
-    if ((threadIdx.x & 31) == 0) {
+    if ((threadIdx.x & 31) == 0 && e < a.K) {          // a warp past the end of the row owns no block (its index would alias the next row's)
         const size_t b = row * (size_t) (a.K >> 5) + (e >> 5);
         a.d[b] = round_f16(d);
         a.s[b] = round_f16(__fmul_rn(d, (float) sum));

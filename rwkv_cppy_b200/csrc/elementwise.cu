@@ -38,7 +38,7 @@ __device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, i
         if (valid) a.f[row * a.K + e] = v[o];
         if (a.q == nullptr) continue;
         if (valid) a.q[row * a.K + e] = (int8_t) q[o];
-        if ((threadIdx.x & 31) == 0) {
+        if ((threadIdx.x & 31) == 0 && e < a.K) {      // warps past the end of the row own no block
             const float d = __fdiv_rn(amax[o], 127.0f);
             const size_t b = row * (size_t) (a.K >> 5) + (e >> 5);
             a.d[b] = round_f16(d);

@@ -117,7 +117,8 @@ struct Pass {
             if (done[i]) continue;
             GemvBatch b; b.T = rows;
             for (size_t k = i; k < jobs.size() && b.n_jobs < GEMV_MAX_JOBS; k++)
-                if (!done[k] && jobs[k].W.type == jobs[i].W.type) {
+                if (!done[k] && jobs[k].W.type == jobs[i].W.type &&
+                    (!type_quantized(jobs[i].W.type) || gemv_ksplit(jobs[k].W.M, jobs[k].W.K) == gemv_ksplit(jobs[i].W.M, jobs[i].W.K))) {
                     const GemvJob & j = jobs[k];
                     if (type_quantized(j.W.type) && tc_written.count(j.x.f)) {   // produced by a GEMM: q8 blocks are stale
                         Act a = j.x; chk(launch_quantize_act(a, rows, st)); tc_written.erase(j.x.f);

@@ -19,6 +19,7 @@
 // epilogue (one q8 block per column), so chained products need no extra launch.
 #include "gemv_common.cuh"
 #include "launch.cuh"
+#include <cstdlib>
 
 namespace rb {
 
@@ -226,15 +227,26 @@ static cudaError_t launch_typed(const GemvBatch & b, int total_ctas, cudaStream_
     else               return launch_pdl(gemv_kernel<TYPE, 8>, dim3(total_ctas, (b.T + 7) / 8), block, 0, st, b);
 }
 
+static bool gemv_ksplit_disabled() {
+    static const bool off = [] { const char * e = getenv("RWKV_B200_NO_KSPLIT"); return e && e[0] == '1'; }();
+    return off;
+}
+
 cudaError_t launch_gemv(const GemvBatch & b_in, cudaStream_t st) {
     if (b_in.n_jobs == 0) return cudaSuccess;
     GemvBatch b = b_in;
     const uint32_t type = b.job[0].W.type;
     int total = 0;
+    b.ks = 1;
+    if (type_quantized(type)) {
+        b.ks = gemv_ksplit(b.job[0].W.M, b.job[0].W.K);
+        for (int j = 1; j < b.n_jobs; j++) if (gemv_ksplit(b.job[j].W.M, b.job[j].W.K) != b.ks) return cudaErrorInvalidValue;   // callers group by split
+        if (gemv_ksplit_disabled()) b.ks = 1;
+    }
     for (int j = 0; j < b.n_jobs; j++) {
         if (b.job[j].W.type != type) return cudaErrorInvalidValue;
         b.cta_begin[j] = total;
-        total += ((int) b.job[j].W.M + GEMV_ROWS - 1) / GEMV_ROWS;
+        total += (((int) b.job[j].W.M + GEMV_ROWS - 1) / GEMV_ROWS) * b.ks;
     }
     b.cta_begin[b.n_jobs] = total;
     if (type_quantized(type)) return launch_gemv_async(b, total, st);

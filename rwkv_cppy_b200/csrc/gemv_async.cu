@@ -23,6 +23,7 @@
 namespace rb {
 
 constexpr int GA_WARPS = 8, GA_R = TILE_ROWS, GA_KC = TILE_BLOCKS;
+constexpr int GA_KSPLIT_MAX = 4;
 
 template <int TYPE> struct QFmt;
 template <> struct QFmt<T_Q4_0> { static constexpr int QB = 16, HB = 0, DB = 2, STAGES = 4; };
@@ -49,12 +50,12 @@ struct XCursor {
     // Fire-and-forget loads of this lane's share of chunks [0, nch): pulls the whole activation
     // row into L1 in one round trip.  Under a saturated L2 a dependent load per chunk costs a
     // microsecond each; this way the later load() calls hit L1 (or merge with the miss in flight).
-    __device__ __forceinline__ void warm(int nch, int nb, int lane) const {
+    __device__ __forceinline__ void warm(int c_lo, int c_hi, int nb, int lane) const {
 #pragma unroll
         for (int cc = 0; cc < NCOL; cc++) {
             const int dt = NCOL == 1 ? 0 : min(cc, tmax);
 #pragma unroll 1
-            for (int c = 0; c < nch; c++) {
+            for (int c = c_lo; c < c_hi; c++) {
                 if (c * GA_KC + lane < nb) {
                     uint32_t t0, t1;
                     asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t0) : "l"(q + (size_t) dt * K + c * (GA_KC * 32)));
@@ -100,16 +101,23 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     const GemvJob & J = B.job[j];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int M = J.W.M, nb = J.W.K >> 5, T = B.T;
-    const int tile_row0 = ((int) blockIdx.x - B.cta_begin[j]) * GA_WARPS * GA_R;
+    // K split: the `ks` CTAs of a cluster share one block of 32 rows, CTA kr takes a contiguous range
+    // of the row's chunks; partial sums meet in the leader's shared memory (see the tail).
+    const int ks = B.ks, local = (int) blockIdx.x - B.cta_begin[j];
+    const int kr = ks > 1 ? local % ks : 0;
+    const int tile_row0 = (ks > 1 ? local / ks : local) * GA_WARPS * GA_R;
     const int row0 = tile_row0 + warp * GA_R;
     const int col0 = blockIdx.y * NCOL;
-    const int nch = row0 < M ? (nb + GA_KC - 1) / GA_KC : 0;     // warps past the last row stay idle
+    const int nch_all = (nb + GA_KC - 1) / GA_KC;
+    const int cbase = ks > 1 ? kr * nch_all / ks : 0;
+    const int cend  = ks > 1 ? (kr + 1) * nch_all / ks : nch_all;
+    const int nch = row0 < M ? cend - cbase : 0;                 // warps past the last row stay idle
 
     uint8_t * my = ga_smem + (size_t) warp * S * STAGE;
     const uint32_t my_s = smem_u32(my);
     const uint32_t bars = smem_u32(ga_smem + (size_t) GA_WARPS * S * STAGE) + warp * S * 8;
-    const uint8_t * src0 = reinterpret_cast<const uint8_t *>(J.W.qs) + (size_t) (row0 / GA_R) * J.W.rg_stride;
-    const uint32_t last_bytes = (uint32_t) ((GA_R * (nb - (nch - 1) * GA_KC) * BB + 15) & ~15);
+    const uint8_t * src0 = reinterpret_cast<const uint8_t *>(J.W.qs) + (size_t) (row0 / GA_R) * J.W.rg_stride + (size_t) cbase * STAGE;
+    const uint32_t last_bytes = (uint32_t) ((GA_R * (nb - (nch_all - 1) * GA_KC) * BB + 15) & ~15);   // the row's final (possibly short) chunk
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < S; s++) mbar_init(bars + s * 8, 1);
@@ -119,7 +127,7 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
 #pragma unroll
         for (int s = 0; s < S; s++) {
             if (s < nch) {
-                const uint32_t bytes = (s == nch - 1) ? last_bytes : (uint32_t) STAGE;
+                const uint32_t bytes = (cbase + s == nch_all - 1) ? last_bytes : (uint32_t) STAGE;
                 mbar_expect_tx(bars + s * 8, bytes);
                 bulk_g2s(my_s + s * STAGE, src0 + (size_t) s * STAGE, bytes, bars + s * 8);
             }
@@ -135,16 +143,16 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     for (int r = 0; r < GA_R; r++) ra[r].clear();
 
     XBlock<NCOL> xb, xn;
-    if (NCOL <= 2 && nch > 2) xc.warm(nch, nb, lane);
-    if (PREFETCH_X && nch > 0 && lane < min(GA_KC, nb)) xc.load(xb, 0);
+    if (NCOL <= 2 && nch > 2) xc.warm(cbase, cbase + nch, nb, lane);
+    if (PREFETCH_X && nch > 0 && lane < nb - cbase * GA_KC) xc.load(xb, cbase);
     int s = 0;
     uint32_t phase = 0;
 #pragma unroll 1
-    for (int c = 0; c < nch; c++) {
-        const int cnt = min(GA_KC, nb - c * GA_KC);
+    for (int c = 0; c < nch; c++) {                      // c counts this CTA's chunks; cbase + c is the chunk of the row
+        const int cnt = min(GA_KC, nb - (cbase + c) * GA_KC);
         const bool act = lane < cnt;
-        if (PREFETCH_X) { if (c + 1 < nch && lane < nb - (c + 1) * GA_KC) xc.load(xn, c + 1); }
-        else if (act) xc.load(xb, c);                   // before the wait: independent of the tile
+        if (PREFETCH_X) { if (c + 1 < nch && lane < nb - (cbase + c + 1) * GA_KC) xc.load(xn, cbase + c + 1); }
+        else if (act) xc.load(xb, cbase + c);           // before the wait: independent of the tile
         mbar_wait(bars + s * 8, phase);
 
         // the warp's 4 rows x (this lane's block) from the stage into registers, then hand the
@@ -178,7 +186,7 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
         }
         __syncwarp();                                   // every lane has read the stage
         if (lane == 0 && c + S < nch) {
-            const uint32_t bytes = (c + S == nch - 1) ? last_bytes : (uint32_t) STAGE;
+            const uint32_t bytes = (cbase + c + S == nch_all - 1) ? last_bytes : (uint32_t) STAGE;
             mbar_expect_tx(bars + s * 8, bytes);
             bulk_g2s(my_s + s * STAGE, src0 + (size_t) (c + S) * STAGE, bytes, bars + s * 8);
         }
@@ -205,6 +213,22 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
             if (HAS_M) v = __fadd_rn(v, warp_sum(ra[r].summ[c]));
             if (lane == r * NCOL + c) mine = v;
         }
+    if (ks > 1) {
+        // partial sums of the cluster -> leader (DSMEM), summed there in rank order
+        __shared__ float part[GA_KSPLIT_MAX][GA_WARPS * GA_R * NCOL];
+        const int slot = warp * GA_R * NCOL + min(lane, GA_R * NCOL - 1);
+        uint32_t remote;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(remote) : "r"(smem_u32(&part[kr][slot])));
+        if (lane < GA_R * NCOL) asm volatile("st.shared::cluster.f32 [%0], %1;" :: "r"(remote), "f"(mine) : "memory");
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (kr != 0) return;
+        if (lane < GA_R * NCOL) {
+            float tsum = part[0][slot];
+            for (int k = 1; k < ks; k++) tsum = __fadd_rn(tsum, part[k][slot]);
+            mine = tsum;
+        }
+    }
     const bool want_q = (J.out_act.f != nullptr);
     if (lane < GA_R * NCOL) {
         const int r = lane / NCOL, c = lane % NCOL;
@@ -238,8 +262,9 @@ static cudaError_t launch_async_n(const GemvBatch & b, int total_ctas, int ygrid
     // The depth never changes the arithmetic.
     int S = (QFmt<TYPE>::QB == 32 || total_ctas * ygrid >= 3 * 148) ? 3 : 4;
     if (ga_stage_override() == 3 || ga_stage_override() == 4) S = ga_stage_override();
-    if (S == 3) return launch_pdl(gemv_async_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, b);
-    return launch_pdl(gemv_async_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, b);
+    const int cl = b.ks > 1 ? b.ks : 0;
+    if (S == 3) return launch_pdl_cluster(gemv_async_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, cl, b);
+    return launch_pdl_cluster(gemv_async_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, cl, b);
 }
 
 template <int TYPE>

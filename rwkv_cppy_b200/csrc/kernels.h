@@ -55,7 +55,18 @@ struct GemvBatch {
     int     cta_begin[GEMV_MAX_JOBS + 1];   // prefix sum of CTAs per job (filled by launch_gemv)
     int     n_jobs = 0;
     int     T = 1;
+    int     ks = 1;                         // K split (cluster size along x) of the quantised kernel; all jobs of a batch share it
 };
+// K split of a quantised (M x K) mat-vec: a function of the shape only, so that every evaluation
+// of the same matrix adds its partial sums in the same order.  Splits while the row blocks alone
+// would leave most SMs idle and every CTA keeps at least five 1024-weight chunks (below that the
+// fixed cost of a CTA outweighs the extra parallelism: measured on 5120x5120 vs 5120x20480).
+inline int gemv_ksplit(uint32_t M, uint32_t K) {
+    const int row_blocks = (int) ((M + 31) / 32), nch = (int) ((K / 32 + TILE_BLOCKS - 1) / TILE_BLOCKS);
+    int ks = 1;
+    while (row_blocks * ks < 3 * 148 && ks < 4 && nch / (ks * 2) >= 5) ks *= 2;
+    return ks;
+}
 
 // All jobs of a batch must have the same weight type.
 cudaError_t launch_gemv(const GemvBatch & b, cudaStream_t st);
