@@ -263,8 +263,10 @@ def run_decode(args):
     batch.free()
 
     # ---- e2e: the rwkv.h call a user makes, host buffers, copies inside the timed region ----
-    state = np.zeros(S, np.float32)
-    logits = np.zeros(V, np.float32)
+    import torch
+    state_t = torch.zeros(S, dtype=torch.float32).pin_memory()   # pinned host buffers (bench contract); the ABI takes any host pointer
+    logits_t = torch.zeros(V, dtype=torch.float32).pin_memory()
+    state, logits = state_t.numpy(), logits_t.numpy()
     L = lib.library
     ctxp = model._ctx.ptr
     L.rwkv_init_state(ctxp, state.ctypes.data_as(PF))
@@ -295,7 +297,7 @@ def run_decode(args):
                            step_hbm_gbs=129.8e6 / (ms_max / K * 1e-3) / 1e9),
             "clocks": clocks,
             "e2e": {"value": d.world * K / e2e_s, "unit": "tokens/s", "h2d_bytes_per_step": S * 4 + 4, "d2h_bytes_per_step": S * 4 + V * 4,
-                    "api": "rwkv_eval(ctx, token, state_in, state_out, logits_out) with host buffers"},
+                    "api": "rwkv_eval(ctx, token, state_in, state_out, logits_out) with pinned host buffers"},
             "gpu_launches": launches * K,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": ncu_traffic("head_gemv_f16_50277x768"),
                          "kernel": "gemv_kernel<F16,1> head 50277x768 (77.2 MB), dominant launch of the step",

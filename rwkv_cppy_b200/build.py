@@ -21,6 +21,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden,-Wall,-Wno-unused-function",
           "-DRWKV_BUILD", "-DRWKV_SHARED"]
+COMMON += os.environ.get("RWKV_B200_NVCC_FLAGS", "").split()      # e.g. -DRWKV_B200_TRACE (tools/decode_trace.py)
 PER_FILE = {"quantize.cpp": ["-Xcompiler", "-ffp-contract=off"]}
 
 
@@ -35,6 +36,7 @@ def _stamp() -> str:
         if os.path.isfile(p):
             h.update(f.encode())
             h.update(open(p, "rb").read())
+    h.update(os.environ.get("RWKV_B200_NVCC_FLAGS", "").encode())
     return h.hexdigest()
 
 

@@ -180,8 +180,6 @@ __global__ void embed_ln0_kernel(DevMat emb, const int * __restrict__ tokens, co
                                  const float * __restrict__ b, float * __restrict__ x) {
     extern __shared__ float smem[];
     __shared__ double red[32];
-    __shared__ float  tmp_unused;
-    (void) tmp_unused;
     pdl_trigger();
     pdl_wait();
     const int t = blockIdx.x, D = emb.K;
@@ -193,10 +191,40 @@ __global__ void embed_ln0_kernel(DevMat emb, const int * __restrict__ tokens, co
     for (int i = threadIdx.x; i < D; i += blockDim.x) x[(size_t) t * D + i] = smem[i];
 }
 
+// Register-resident variant for rows up to 256 * ITEMS wide: every load is issued up front and the
+// statistics use the shared row reduction (device_utils.cuh ln_rows_stats).
+template <int ITEMS>
+__global__ void __launch_bounds__(256) embed_ln0_reg_kernel(DevMat emb, const int * __restrict__ tokens, const float * __restrict__ w,
+                                                            const float * __restrict__ b, float * __restrict__ x) {
+    __shared__ double red[2][32];
+    pdl_trigger();
+    const int t = blockIdx.x, D = emb.K;
+    const int tok = tokens[t];
+    float v[1][ITEMS], lw[ITEMS], lb[ITEMS];
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * 256 + threadIdx.x;
+        const bool valid = e < D;
+        v[0][it] = valid ? mat_element(emb, (size_t) tok, e) : 0.0f;
+        lw[it] = valid ? w[e] : 0.0f; lb[it] = valid ? b[e] : 0.0f;
+    }
+    float scale[1];
+    ln_rows_stats<ITEMS, 1>(v, D, 256, red, scale, 1e-5f);
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * 256 + threadIdx.x;
+        if (e < D) x[(size_t) t * D + e] = __fadd_rn(__fmul_rn(__fmul_rn(v[0][it], scale[0]), lw[it]), lb[it]);
+    }
+}
+
 cudaError_t launch_embed_ln0(const DevMat & emb, const int * tokens, int T, const float * w, const float * b, float * x, cudaStream_t st) {
     // Plain stream-ordered launch on purpose: the first kernel of a pass is a full fence, so nothing of
     // this pass (which may prefetch the input state before its pdl_wait) overlaps the previous pass.
-    embed_ln0_kernel<<<T, 256, 2 * emb.K * sizeof(float), st>>>(emb, tokens, w, b, x);
+    if (emb.K <= 1024)      embed_ln0_reg_kernel<4><<<T, 256, 0, st>>>(emb, tokens, w, b, x);
+    else if (emb.K <= 2048) embed_ln0_reg_kernel<8><<<T, 256, 0, st>>>(emb, tokens, w, b, x);
+    else if (emb.K <= 4096) embed_ln0_reg_kernel<16><<<T, 256, 0, st>>>(emb, tokens, w, b, x);
+    else if (emb.K <= 8192) embed_ln0_reg_kernel<32><<<T, 256, 0, st>>>(emb, tokens, w, b, x);
+    else embed_ln0_kernel<<<T, 256, 2 * emb.K * sizeof(float), st>>>(emb, tokens, w, b, x);
     return cudaGetLastError();
 }
 

@@ -32,6 +32,15 @@ __device__ __forceinline__ double warp_sum_d(double v) {
     return v;
 }
 
+// Butterfly over the warp totals held by lanes < nw (zero elsewhere).  With nw <= 8 the xor-16 and
+// xor-8 steps would only add zeros, so they are skipped: same value, two dependent shuffles less.
+__device__ __forceinline__ double warp_totals_sum_d(double v, int nw) {
+    if (nw > 8) return warp_sum_d(v);
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return __shfl_sync(FULL, v, 0);
+}
+
 // Block-wide double sum; `red` is >= 32 doubles of shared memory.  All threads get the result.
 __device__ __forceinline__ double block_sum_d(double v, double * red) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
@@ -45,6 +54,63 @@ __device__ __forceinline__ double block_sum_d(double v, double * red) {
 }
 
 __device__ __forceinline__ float round_f16(float v) { return __half2float(__float2half_rn(v)); }
+
+// Layer-norm statistics of NR rows held by a CTA of `nt` threads, ITEMS elements per thread
+// (element it*nt + tid, 0.0f where that is past the row).  Mean and variance are accumulated in
+// double like ggml_compute_forward_norm_f32 (ggml-cpu.c:6880-6930).  This is THE summation
+// order of every kernel that normalises a residual row (ln_mix_kernel for sequences and
+// batches, the mat-vec prologue for decode): per-thread sums in `it` order, xor-butterfly in the
+// warp, butterfly over the warp totals -- so for a given (D, nt) they agree bit for bit.
+// On return x holds x - mean and scale[k] = 1/sqrt(var + eps).  red: [2*NR][32] doubles shared.
+template <int ITEMS, int NR>
+__device__ __forceinline__ void ln_rows_stats(float (&x)[NR][ITEMS], int D, int nt, double (*red)[32], float (&scale)[NR], float eps) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = nt >> 5;
+    double s[NR];
+#pragma unroll
+    for (int k = 0; k < NR; k++) {
+        s[k] = 0.0;
+#pragma unroll
+        for (int it = 0; it < ITEMS; it++) s[k] += (double) x[k][it];
+    }
+#pragma unroll
+    for (int k = 0; k < NR; k++) { s[k] = warp_sum_d(s[k]); if (lane == 0) red[k][warp] = s[k]; }
+    __syncthreads();
+    float mean[NR];
+#pragma unroll
+    for (int k = 0; k < NR; k++) { const double t = warp_totals_sum_d(lane < nw ? red[k][lane] : 0.0, nw); mean[k] = (float) (t / D); }
+    double s2[NR];
+#pragma unroll
+    for (int k = 0; k < NR; k++) {
+        s2[k] = 0.0;
+#pragma unroll
+        for (int it = 0; it < ITEMS; it++) {
+            const bool valid = it * nt + (int) threadIdx.x < D;
+            const float v = valid ? __fsub_rn(x[k][it], mean[k]) : 0.0f;
+            x[k][it] = v; s2[k] += (double) __fmul_rn(v, v);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < NR; k++) { s2[k] = warp_sum_d(s2[k]); if (lane == 0) red[NR + k][warp] = s2[k]; }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < NR; k++) {
+        const double t = warp_totals_sum_d(lane < nw ? red[NR + k][lane] : 0.0, nw);
+        scale[k] = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn((float) (t / D), eps)));
+    }
+}
+
+// The q8 block of 32 consecutive values held one per lane, exactly as act_store_block computes
+// it; returns q, and d / s / isum (identical in every lane).
+__device__ __forceinline__ int q8_block(float v, bool valid, float & d16, float & s16, int & isum) {
+    const float amax = warp_max(valid ? fabsf(v) : 0.0f);
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+    const int   q  = valid ? __float2int_rn(__fmul_rn(v, id)) : 0;
+    isum = warp_sum_i(q);
+    d16 = round_f16(d);
+    s16 = round_f16(__fmul_rn(d, (float) isum));
+    return q;
+}
 
 // One warp holds one block of 32 consecutive activations (lane = element).  Writes the
 // FP32 value and -- when the row has quantised planes -- the q8 block exactly as ggml's

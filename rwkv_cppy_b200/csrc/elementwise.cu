@@ -53,11 +53,10 @@ __device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, i
 // aligned 32-element blocks.  LN(x[r]) and -- in sequence mode -- LN(x[r-1]) (the token-shift
 // source, recomputed instead of waiting for the neighbouring CTA) run through the same
 // reductions; both use identical arithmetic, so the recomputed row is bit-identical.
-template <int ITEMS, int NOUT>
-__global__ void __launch_bounds__(1024) ln_mix_kernel(const __grid_constant__ LnMixArgs a) {
+template <int ITEMS, int NOUT, int NT>
+__global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMixArgs a) {
     __shared__ double red[4][32];
     const int r = blockIdx.x, D = a.D, nt = blockDim.x;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = nt >> 5;
     const bool from_state = a.batch || r == 0;
     const size_t soff = a.batch ? (size_t) r * a.state_stride : 0;
 
@@ -82,37 +81,8 @@ __global__ void __launch_bounds__(1024) ln_mix_kernel(const __grid_constant__ Ln
         x[1][it] = (valid && !from_state) ? a.x[(size_t) (r - 1) * D + e] : 0.0f;
     }
     const int nrow = from_state ? 1 : 2;                     // rows to normalise (uniform per CTA)
-    // ---- mean (double accumulation as ggml_compute_forward_norm_f32) ----
-    double s[2] = {0.0, 0.0};
-#pragma unroll
-    for (int k = 0; k < 2; k++)
-#pragma unroll
-        for (int it = 0; it < ITEMS; it++) s[k] += (double) x[k][it];
-#pragma unroll
-    for (int k = 0; k < 2; k++) { s[k] = warp_sum_d(s[k]); if (lane == 0) red[k][warp] = s[k]; }
-    __syncthreads();
-    float mean[2];
-#pragma unroll
-    for (int k = 0; k < 2; k++) { const double t = warp_sum_d(lane < nw ? red[k][lane] : 0.0); mean[k] = (float) (t / D); }
-    // ---- variance ----
-    double s2[2] = {0.0, 0.0};
-#pragma unroll
-    for (int k = 0; k < 2; k++)
-#pragma unroll
-        for (int it = 0; it < ITEMS; it++) {
-            const bool valid = it * nt + (int) threadIdx.x < D;
-            const float v = valid ? __fsub_rn(x[k][it], mean[k]) : 0.0f;
-            x[k][it] = v; s2[k] += (double) __fmul_rn(v, v);
-        }
-#pragma unroll
-    for (int k = 0; k < 2; k++) { s2[k] = warp_sum_d(s2[k]); if (lane == 0) red[2 + k][warp] = s2[k]; }
-    __syncthreads();
     float scale[2];
-#pragma unroll
-    for (int k = 0; k < 2; k++) {
-        const double t = warp_sum_d(lane < nw ? red[2 + k][lane] : 0.0);
-        scale[k] = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn((float) (t / D), 1e-5f)));
-    }
+    ln_rows_stats<ITEMS, 2>(x, D, nt, red, scale, 1e-5f);
     // ---- affine, shift state, mixes ----
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
@@ -135,28 +105,33 @@ __global__ void __launch_bounds__(1024) ln_mix_kernel(const __grid_constant__ Ln
     }
 }
 
-template <int ITEMS>
+template <int ITEMS, int NT>
 static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_t st) {
     switch (a.n_out) {
-        case 1: return launch_pdl(ln_mix_kernel<ITEMS, 1>, dim3(a.R), dim3(threads), 0, st, a);
-        case 2: return launch_pdl(ln_mix_kernel<ITEMS, 2>, dim3(a.R), dim3(threads), 0, st, a);
-        case 3: return launch_pdl(ln_mix_kernel<ITEMS, 3>, dim3(a.R), dim3(threads), 0, st, a);
-        case 4: return launch_pdl(ln_mix_kernel<ITEMS, 4>, dim3(a.R), dim3(threads), 0, st, a);
-        case 6: return launch_pdl(ln_mix_kernel<ITEMS, 6>, dim3(a.R), dim3(threads), 0, st, a);
+        case 1: return launch_pdl(ln_mix_kernel<ITEMS, 1, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 2: return launch_pdl(ln_mix_kernel<ITEMS, 2, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 3: return launch_pdl(ln_mix_kernel<ITEMS, 3, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 4: return launch_pdl(ln_mix_kernel<ITEMS, 4, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 6: return launch_pdl(ln_mix_kernel<ITEMS, 6, NT>, dim3(a.R), dim3(threads), 0, st, a);
         default: return cudaErrorInvalidValue;
     }
 }
 
 cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
-    const int items = a.D <= 1024 ? 1 : a.D <= 2048 ? 2 : a.D <= 4096 ? 4 : 8;
     if (a.D > 8192) return cudaErrorInvalidValue;
-    const int threads = (((a.D + items - 1) / items) + 31) / 32 * 32;
-    switch (items) {
-        case 1: return launch_ln_mix_i<1>(a, threads, st);
-        case 2: return launch_ln_mix_i<2>(a, threads, st);
-        case 4: return launch_ln_mix_i<4>(a, threads, st);
-        default: return launch_ln_mix_i<8>(a, threads, st);
+    if (a.D <= LN_SMALL_D) {
+        // Rows up to 2048 wide: 256 threads, element it*256 + tid.  The decode mat-vecs rebuild these
+        // rows in their prologue (gemv_async.cu) with the same thread shape, hence the same sums.
+        const int items = (a.D + 255) / 256;
+        if (items <= 1) return launch_ln_mix_i<1, 256>(a, 256, st);
+        if (items <= 2) return launch_ln_mix_i<2, 256>(a, 256, st);
+        if (items <= 4) return launch_ln_mix_i<4, 256>(a, 256, st);
+        return launch_ln_mix_i<8, 256>(a, 256, st);
     }
+    const int items = a.D <= 4096 ? 4 : 8;
+    const int threads = (((a.D + items - 1) / items) + 31) / 32 * 32;
+    if (items == 4) return launch_ln_mix_i<4, 1024>(a, threads, st);
+    return launch_ln_mix_i<8, 1024>(a, threads, st);
 }
 
 __global__ void __launch_bounds__(256) ln_act_kernel(const float * __restrict__ x, int ldx, int D, const float * __restrict__ w,
@@ -174,7 +149,40 @@ __global__ void __launch_bounds__(256) ln_act_kernel(const float * __restrict__ 
     }
 }
 
+// Register-resident variant (rows up to 256 * ITEMS wide), same structure as ln_mix_kernel.
+template <int ITEMS>
+__global__ void __launch_bounds__(256) ln_act_reg_kernel(const float * __restrict__ x, int ldx, int D, const float * __restrict__ w,
+                                                         const float * __restrict__ b, Act out) {
+    __shared__ double red[2][32];
+    const int r = blockIdx.x;
+    pdl_trigger();
+    float v[1][ITEMS], lw[ITEMS], lb[ITEMS];
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * 256 + threadIdx.x;
+        lw[it] = e < D ? w[e] : 0.0f; lb[it] = e < D ? b[e] : 0.0f;
+    }
+    pdl_wait();
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * 256 + threadIdx.x;
+        v[0][it] = e < D ? x[(size_t) r * ldx + e] : 0.0f;
+    }
+    float scale[1];
+    ln_rows_stats<ITEMS, 1>(v, D, 256, red, scale, 1e-5f);
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * 256 + threadIdx.x;
+        const float y = __fadd_rn(__fmul_rn(__fmul_rn(v[0][it], scale[0]), lw[it]), lb[it]);
+        if (e - (int) (threadIdx.x & 31) < D) act_store_block(out, (size_t) r, e, e < D, e < D ? y : 0.0f);
+    }
+}
+
 cudaError_t launch_ln_act(const float * x, int ldx, int R, int D, const float * w, const float * b, Act out, cudaStream_t st) {
+    if (D <= 1024) return launch_pdl(ln_act_reg_kernel<4>, dim3(R), dim3(256), 0, st, x, ldx, D, w, b, out);
+    if (D <= 2048) return launch_pdl(ln_act_reg_kernel<8>, dim3(R), dim3(256), 0, st, x, ldx, D, w, b, out);
+    if (D <= 4096) return launch_pdl(ln_act_reg_kernel<16>, dim3(R), dim3(256), 0, st, x, ldx, D, w, b, out);
+    if (D <= 8192) return launch_pdl(ln_act_reg_kernel<32>, dim3(R), dim3(256), 0, st, x, ldx, D, w, b, out);
     return launch_pdl(ln_act_kernel, dim3(R), dim3(256), D * sizeof(float), st, x, ldx, D, w, b, out);
 }
 

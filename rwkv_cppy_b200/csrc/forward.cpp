@@ -4,6 +4,8 @@
 // (R = T tokens of one stream) and batched decode (R independent streams): the kernels take
 // the row count and the "rows are streams" flag.
 #include "engine.h"
+#include <cstdlib>
+#include <initializer_list>
 #include <unordered_map>
 
 namespace rb {
@@ -81,7 +83,7 @@ struct Pass {
 
     // launches the jobs grouped by weight type, `rows` rows each; wide row counts go to the
     // tensor-core GEMM (FP16 operands), everything else to the exact mat-vec kernels
-    void gemv(std::vector<GemvJob> jobs, int rows) {
+    void gemv(std::vector<GemvJob> jobs, int rows, const GemvPrologue * pro = nullptr) {
         std::vector<bool> done(jobs.size(), false);
         // ---- tensor-core path ----
         for (size_t i = 0; i < jobs.size(); i++) {
@@ -116,6 +118,7 @@ struct Pass {
         for (size_t i = 0; i < jobs.size(); i++) {
             if (done[i]) continue;
             GemvBatch b; b.T = rows;
+            if (pro) b.pro = *pro;
             for (size_t k = i; k < jobs.size() && b.n_jobs < GEMV_MAX_JOBS; k++)
                 if (!done[k] && jobs[k].W.type == jobs[i].W.type &&
                     (!type_quantized(jobs[i].W.type) || gemv_ksplit(jobs[k].W.M, jobs[k].W.K) == gemv_ksplit(jobs[i].W.M, jobs[i].W.K))) {
@@ -132,6 +135,28 @@ struct Pass {
     std::vector<const float *> to_half_marks;
     bool tc_job(const GemvJob & j, int rows) const {
         return j.x.h != nullptr && (j.x_off % 8) == 0 && (j.x.K % 8) == 0 && gemm_tc_supported(j.W, rows);
+    }
+
+    // Decode of narrow models is a chain of dependent launches: fold the layer norm + token-shift mix
+    // (and the v4 recurrence) into the prologue of the mat-vec that consumes them.  Possible when
+    // one row is evaluated and every consumer is a quantised matrix of D columns.
+    static bool fusion_enabled() {
+        static const bool on = [] { const char * e = getenv("RWKV_B200_NO_FUSE"); return !(e && e[0] == '1'); }();
+        return on;
+    }
+    bool can_fuse(std::initializer_list<const DevMat *> mats) const {
+        if (!fusion_enabled() || R != 1 || D > (size_t) LN_SMALL_D || D % 32 != 0 || m.tp.world > 1) return false;
+        for (const DevMat * W : mats) if (!type_quantized(W->type) || W->K != D) return false;
+        return true;
+    }
+    GemvPrologue ln_prologue(uint32_t layer, bool att, int kind) const {
+        const LayerW & l = m.layers[layer];
+        GemvPrologue P;
+        P.kind = PRO_LNMIX; P.D = (int) D; P.mix_kind = kind;
+        P.x = ws.x; P.ln_w = att ? l.ln1_w : l.ln2_w; P.ln_b = att ? l.ln1_b : l.ln2_b;
+        const size_t slot = att ? D : 0;
+        P.state_in = sin(layer, slot); P.state_out = sout(layer, slot);
+        return P;
     }
 
     const float * sin(uint32_t layer, size_t off) const { return fa.state_in + (size_t) layer * m.layer_state_len() + off; }
@@ -197,16 +222,30 @@ struct Pass {
         const LayerW & l = m.layers[layer];
         if (m.tp.world > 1) { ffn_v4_tp(layer); return; }
         if (m.arch_major == 7) {
-            ln_mix(layer, false, MIX_SX, 1, l.ffn_mu, false);
             GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
-            gemv({k}, R);
+            if (can_fuse({&l.ffn_key})) {
+                const GemvPrologue P = ln_prologue(layer, false, MIX_SX);
+                k.pro_mu = l.ffn_mu[0];
+                gemv({k}, R, &P);
+            } else {
+                ln_mix(layer, false, MIX_SX, 1, l.ffn_mu, false);
+                gemv({k}, R);
+            }
             Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
             gemv({job(l.ffn_value, kin, ws.x, (int) D, EPI_ADD_TO)}, R);
             return;
         }
-        ln_mix(layer, false, m.arch_major == 6 ? MIX_SX : MIX_LERP, 2, l.ffn_mu, false);
+        const int kind = m.arch_major == 6 ? MIX_SX : MIX_LERP;
         GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
-        gemv({k, job(l.ffn_receptance, ws.mix[1], ws.ffn_r, (int) D, EPI_SIGMOID)}, R);
+        GemvJob r = job(l.ffn_receptance, ws.mix[1], ws.ffn_r, (int) D, EPI_SIGMOID);
+        if (can_fuse({&l.ffn_key, &l.ffn_receptance})) {
+            const GemvPrologue P = ln_prologue(layer, false, kind);
+            k.pro_mu = l.ffn_mu[0]; r.pro_mu = l.ffn_mu[1];
+            gemv({k, r}, R, &P);
+        } else {
+            ln_mix(layer, false, kind, 2, l.ffn_mu, false);
+            gemv({k, r}, R);
+        }
         Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
         GemvJob v = job(l.ffn_value, kin, ws.x, (int) D, EPI_MULADD_TO); v.aux = ws.ffn_r; v.ld_aux = (int) D;
         gemv({v}, R);
@@ -214,23 +253,45 @@ struct Pass {
 
     void att_v4(uint32_t layer) {
         const LayerW & l = m.layers[layer];
-        ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false);
-        gemv({job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
-              job(l.att_receptance, ws.mix[2], ws.r, (int) D, EPI_SIGMOID)}, R);
+        std::vector<GemvJob> kvr = {job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
+                                    job(l.att_receptance, ws.mix[2], ws.r, (int) D, EPI_SIGMOID)};
+        if (can_fuse({&l.att_key, &l.att_value, &l.att_receptance})) {
+            const GemvPrologue P = ln_prologue(layer, true, MIX_LERP);
+            for (int i = 0; i < 3; i++) kvr[i].pro_mu = l.att_mu[i];
+            gemv(kvr, R, &P);
+        } else {
+            ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false);
+            gemv(kvr, R);
+        }
         WkvArgs a = wkv_base(layer);
         a.u = l.time_first; a.decay = l.time_decay;
-        chk(launch_wkv4(a, st));
-        gemv({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
+        GemvJob o = job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO);
+        if (can_fuse({&l.att_output})) {
+            GemvPrologue P;
+            P.kind = PRO_WKV4; P.D = (int) D;
+            P.k = ws.k; P.v = ws.v; P.r = ws.r; P.u = a.u; P.decay = a.decay;
+            P.state_in = a.state_in; P.state_out = a.state_out;
+            gemv({o}, R, &P);
+        } else {
+            chk(launch_wkv4(a, st));
+            gemv({o}, R);
+        }
     }
 
     void att_v5(uint32_t layer) {
         const LayerW & l = m.layers[layer];
         const bool gate = m.arch_minor >= 2;
-        ln_mix(layer, true, MIX_LERP, gate ? 4 : 3, l.att_mu, false);
         std::vector<GemvJob> jobs = {job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
                                      job(l.att_receptance, ws.mix[2], ws.r, (int) D, EPI_STORE)};
         if (gate) jobs.push_back(job(l.att_gate, ws.mix[3], ws.g, (int) D, EPI_SILU));
-        gemv(jobs, R);
+        if (gate ? can_fuse({&l.att_key, &l.att_value, &l.att_receptance, &l.att_gate}) : can_fuse({&l.att_key, &l.att_value, &l.att_receptance})) {
+            const GemvPrologue P = ln_prologue(layer, true, MIX_LERP);
+            for (size_t i = 0; i < jobs.size(); i++) jobs[i].pro_mu = l.att_mu[i];
+            gemv(jobs, R, &P);
+        } else {
+            ln_mix(layer, true, MIX_LERP, gate ? 4 : 3, l.att_mu, false);
+            gemv(jobs, R);
+        }
         WkvArgs a = wkv_base(layer);
         a.u = l.time_first; a.decay = l.time_decay; a.per_head_scalar = gate ? 0 : 1;
         a.g = gate ? ws.g : nullptr; a.lnx_w = l.lnx_w; a.lnx_b = l.lnx_b; a.gn_eps = 1e-5f;

@@ -250,6 +250,7 @@ cudaError_t launch_gemv(const GemvBatch & b_in, cudaStream_t st) {
     }
     b.cta_begin[b.n_jobs] = total;
     if (type_quantized(type)) return launch_gemv_async(b, total, st);
+    if (b.pro.kind != PRO_NONE) return cudaErrorInvalidValue;      // prologues exist in the quantised kernel only
     if (type == T_F32 && smallk_ok(b)) return launch_smallk(b, st);
     if (type == T_F32) return launch_typed<T_F32>(b, total, st);
     if (type == T_F16) return launch_typed<T_F16>(b, total, st);

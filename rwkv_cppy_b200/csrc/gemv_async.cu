@@ -83,9 +83,159 @@ struct XCursor {
     }
 };
 
-template <int TYPE, int NCOL, int S>
+// ---- optional timeline of CTA 0 (RWKV_B200_TRACE builds only; tools/decode_trace.py) -----------
+#ifdef RWKV_B200_TRACE
+__device__ unsigned long long g_trace[8192 * 12];
+__device__ unsigned int g_trace_n;
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define TRACE_DECL unsigned long long tr_[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}
+#define TRACE(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) tr_[i] = gtimer(); } while (0)
+#define TRACE_FLUSH(pro, grid) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { \
+    const unsigned int n_ = atomicAdd(&g_trace_n, 1u) & 8191u; \
+    for (int i_ = 0; i_ < 10; i_++) g_trace[n_ * 12 + i_] = tr_[i_]; g_trace[n_ * 12 + 10] = (pro); g_trace[n_ * 12 + 11] = (grid); } } while (0)
+#define TRACE_ARG , unsigned long long * tr_
+#define TRACE_PASS , tr_
+#else
+#define TRACE_DECL
+#define TRACE(i)
+#define TRACE_FLUSH(pro, grid)
+#define TRACE_ARG
+#define TRACE_PASS
+#endif
+
+// ---- decode prologues (kernels.h GemvPrologue) ---------------------------------------------------
+// The input vector of the launch as q8 blocks in shared memory (what the chunk loop otherwise
+// reads from the Act planes in global memory).
+template <bool ON>
+struct ProXT {
+    static constexpr int N = ON ? LN_SMALL_D : 32;           // kernels without a prologue carry a stub
+    __align__(16) int8_t q[N];
+    float d[N / 32], s[N / 32];
+    int   isum[N / 32];
+};
+using ProX = ProXT<true>;
+constexpr int PRO_NT = GA_WARPS * 32;                        // thread `tid` holds elements it * 256 + tid, it < ITEMS
+
+// values of elements it*256 + tid -> q8 blocks (it*8 + warp) in shared memory; the blocks of all
+// items are reduced together so their shuffle chains overlap (same values as act_store_block)
+template <int ITEMS>
+__device__ __forceinline__ void pro_store_all(ProX & px, const float (&v)[ITEMS], int D) {
+    const int tid = threadIdx.x;
+    float amax[ITEMS]; int q[ITEMS], sum[ITEMS];
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) amax[it] = it * PRO_NT + tid < D ? fabsf(v[it]) : 0.0f;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+        for (int it = 0; it < ITEMS; it++) amax[it] = fmaxf(amax[it], __shfl_xor_sync(FULL, amax[it], off));
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const float id = amax[it] != 0.0f ? __fdiv_rn(127.0f, amax[it]) : 0.0f;
+        q[it] = it * PRO_NT + tid < D ? __float2int_rn(__fmul_rn(v[it], id)) : 0;
+        sum[it] = q[it];
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+        for (int it = 0; it < ITEMS; it++) sum[it] += __shfl_xor_sync(FULL, sum[it], off);
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * PRO_NT + tid;
+        if (e - (tid & 31) < D) {                            // warps past the row own no block (uniform)
+            px.q[e] = (int8_t) q[it];
+            if ((tid & 31) == 0) {
+                const float d = __fdiv_rn(amax[it], 127.0f);
+                px.d[e >> 5] = round_f16(d); px.s[e >> 5] = round_f16(__fmul_rn(d, (float) sum[it])); px.isum[e >> 5] = sum[it];
+            }
+        }
+    }
+}
+
+// part 1 (before pdl_wait): constants and the read-only input state
+template <int ITEMS> struct ProLnRegs { float xs[ITEMS], w[ITEMS], b[ITEMS], mu[ITEMS]; };
+template <int ITEMS>
+__device__ __forceinline__ void pro_lnmix_pre(const GemvPrologue & P, const float * __restrict__ mu, ProLnRegs<ITEMS> & r) {
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * PRO_NT + threadIdx.x;
+        const bool valid = e < P.D;
+        r.xs[it] = valid ? P.state_in[e] : 0.0f;
+        r.w[it] = valid ? P.ln_w[e] : 0.0f; r.b[it] = valid ? P.ln_b[e] : 0.0f;
+        r.mu[it] = valid ? mu[e] : 0.0f;
+    }
+}
+// part 2 (after pdl_wait): the row itself; same arithmetic as ln_mix_kernel<., ., 256> (elementwise.cu)
+template <int ITEMS>
+__device__ __forceinline__ void pro_lnmix_post(const GemvPrologue & P, const ProLnRegs<ITEMS> & r, ProX & px, double (*red)[32] TRACE_ARG) {
+    float x[1][ITEMS];
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * PRO_NT + threadIdx.x;
+        x[0][it] = e < P.D ? P.x[e] : 0.0f;
+    }
+    float scale[1];
+    ln_rows_stats<ITEMS, 1>(x, P.D, PRO_NT, red, scale, 1e-5f);
+    TRACE(7);
+    float v[ITEMS];
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * PRO_NT + threadIdx.x;
+        const float x0 = __fadd_rn(__fmul_rn(__fmul_rn(x[0][it], scale[0]), r.w[it]), r.b[it]);
+        const float xp = r.xs[it];
+        if (P.mix_kind == MIX_LERP) v[it] = __fadd_rn(__fmul_rn(x0, r.mu[it]), __fsub_rn(xp, __fmul_rn(xp, r.mu[it])));
+        else                        v[it] = __fadd_rn(__fmul_rn(__fsub_rn(xp, x0), r.mu[it]), x0);
+        if (e < P.D && blockIdx.x == 0) P.state_out[e] = x0;
+    }
+    pro_store_all<ITEMS>(px, v, P.D);
+    TRACE(8);
+}
+
+template <int ITEMS> struct ProWkvRegs { float aa[ITEMS], bb[ITEMS], pp[ITEMS], u[ITEMS], w[ITEMS]; };
+template <int ITEMS>
+__device__ __forceinline__ void pro_wkv4_pre(const GemvPrologue & P, ProWkvRegs<ITEMS> & r) {
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * PRO_NT + threadIdx.x;
+        const bool valid = e < P.D;
+        r.aa[it] = valid ? P.state_in[e] : 0.0f; r.bb[it] = valid ? P.state_in[P.D + e] : 0.0f; r.pp[it] = valid ? P.state_in[2 * P.D + e] : 0.0f;
+        r.u[it] = valid ? P.u[e] : 0.0f; r.w[it] = valid ? P.decay[e] : 0.0f;
+    }
+}
+// same arithmetic as wkv4_kernel (wkv.cu; rwkv_operators.inc / rwkv_graph.inc v4 att)
+template <int ITEMS>
+__device__ __forceinline__ void pro_wkv4_post(const GemvPrologue & P, const ProWkvRegs<ITEMS> & g, ProX & px) {
+    float k[ITEMS], v[ITEMS], r[ITEMS], out[ITEMS];
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * PRO_NT + threadIdx.x;
+        const bool valid = e < P.D;
+        k[it] = valid ? P.k[e] : 0.0f; v[it] = valid ? P.v[e] : 0.0f; r[it] = valid ? P.r[e] : 0.0f;
+    }
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+        const int e = it * PRO_NT + threadIdx.x;
+        float aa = g.aa[it], bb = g.bb[it];
+        const float pp = g.pp[it];
+        float ww = __fadd_rn(g.u[it], k[it]);
+        float qq = fmaxf(pp, ww);
+        float e1 = expf(__fsub_rn(pp, qq)), e2 = expf(__fsub_rn(ww, qq));
+        const float num = __fadd_rn(__fmul_rn(e1, aa), __fmul_rn(e2, v[it]));
+        const float den = __fadd_rn(__fmul_rn(e1, bb), e2);
+        ww = __fadd_rn(pp, g.w[it]);
+        qq = fmaxf(ww, k[it]);
+        e1 = expf(__fsub_rn(ww, qq)); e2 = expf(__fsub_rn(k[it], qq));
+        aa = __fadd_rn(__fmul_rn(e1, aa), __fmul_rn(e2, v[it]));
+        bb = __fadd_rn(__fmul_rn(e1, bb), e2);
+        out[it] = e < P.D ? __fmul_rn(r[it], __fdiv_rn(num, den)) : 0.0f;
+        if (e < P.D && blockIdx.x == 0) { P.state_out[e] = aa; P.state_out[P.D + e] = bb; P.state_out[2 * P.D + e] = qq; }
+    }
+    pro_store_all<ITEMS>(px, out, P.D);
+}
+
+template <int TYPE, int NCOL, int S, int PRO = PRO_NONE, int PIT = 4>
 __global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? (QFmt<TYPE>::QB == 32 ? 2 : 3) : (NCOL == 2 ? 2 : 1))
 gemv_async_kernel(const __grid_constant__ GemvBatch B) {
+    static_assert(PRO == PRO_NONE || NCOL == 1, "prologues are single-row");
     using F = QFmt<TYPE>;
     constexpr int BB = F::QB + F::HB + F::DB;              // bytes per block
     constexpr int STAGE = ga_stage_bytes<TYPE>();
@@ -93,7 +243,10 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     constexpr bool PREFETCH_X = (NCOL == 1);               // next chunk's activations one iteration ahead
     extern __shared__ __align__(128) uint8_t ga_smem[];
     __shared__ float tile[NCOL][GA_WARPS * GA_R];
+    __shared__ ProXT<PRO != PRO_NONE> pro_xs;
+    __shared__ double pro_red[PRO == PRO_LNMIX ? 2 : 1][32];
 
+    TRACE_DECL; TRACE(0);
     pdl_trigger();
     int j = 0;
 #pragma unroll 1
@@ -134,16 +287,37 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
         }
     }
     XCursor<TYPE, NCOL> xc;
-    xc.init(J.x, J.x_off, col0, T, lane);
+    if (PRO == PRO_NONE) xc.init(J.x, J.x_off, col0, T, lane);
+    ProLnRegs<PIT> pln; ProWkvRegs<PIT> pwk;
+    if (PRO == PRO_LNMIX) pro_lnmix_pre<PIT>(B.pro, J.pro_mu, pln);
+    if (PRO == PRO_WKV4)  pro_wkv4_pre<PIT>(B.pro, pwk);
     __syncwarp();
+    TRACE(1);
     pdl_wait();                                         // activations (and the residual) come from the preceding kernels
+    TRACE(2);
+    if constexpr (PRO != PRO_NONE) {
+        if (PRO == PRO_LNMIX) pro_lnmix_post<PIT>(B.pro, pln, pro_xs, pro_red TRACE_PASS);
+        if (PRO == PRO_WKV4)  pro_wkv4_post<PIT>(B.pro, pwk, pro_xs);
+        __syncthreads();
+        xc.q = pro_xs.q + lane * 32; xc.d = pro_xs.d + lane; xc.s = pro_xs.s + lane; xc.isum = pro_xs.isum + lane;
+        xc.K = 0; xc.nbrow = 0; xc.tmax = 0;
+    }
+
+    TRACE(3);
+    // The epilogue's operands, one (row, column) per lane.  Fetched up front in the variants that run
+    // the small, latency-bound grids (4-stage ring / prologue kernels); the 3-stage variants stream
+    // large matrices at the register limit and fetch them in the tail instead.
+    constexpr bool EPI_EARLY = (S == 4) || PRO != PRO_NONE;
+    EpiOperands epre;
+    if (EPI_EARLY && lane < GA_R * NCOL && row0 + lane / NCOL < M && col0 + lane % NCOL < T)
+        epre = load_epilogue_operands(J, col0 + lane % NCOL, row0 + lane / NCOL);
 
     RowAcc<TYPE, NCOL> ra[GA_R];
 #pragma unroll
     for (int r = 0; r < GA_R; r++) ra[r].clear();
 
     XBlock<NCOL> xb, xn;
-    if (NCOL <= 2 && nch > 2) xc.warm(cbase, cbase + nch, nb, lane);
+    if (PRO == PRO_NONE && NCOL <= 2 && nch > 2) xc.warm(cbase, cbase + nch, nb, lane);
     if (PREFETCH_X && nch > 0 && lane < nb - cbase * GA_KC) xc.load(xb, cbase);
     int s = 0;
     uint32_t phase = 0;
@@ -203,6 +377,7 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
         if (++s == S) { s = 0; phase ^= 1; }
     }
 
+    TRACE(4);
     // ---- warp totals; lane (r*NCOL + c) finishes output (row0 + r, col0 + c) ----------------------
     float mine = 0.0f;
 #pragma unroll
@@ -235,7 +410,8 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
         const int m = row0 + r, t = col0 + c;
         float v = 0.0f;
         if (m < M && t < T) {
-            v = apply_epilogue(J, mine, t, m);
+            if (!EPI_EARLY) epre = load_epilogue_operands(J, t, m);
+            v = apply_epilogue_pre(J, mine, epre);
             if (J.out) J.out[(size_t) t * J.ldo + m] = v;
         }
         if (want_q) tile[c][warp * GA_R + r] = v;
@@ -247,7 +423,24 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
             act_store_block(J.out_act, (size_t) (col0 + warp), m, m < M, tile[warp][lane]);
         }
     }
+    TRACE(5);
+    TRACE_FLUSH(PRO, gridDim.x);
 }
+
+#ifdef RWKV_B200_TRACE
+} // namespace rb
+extern "C" __attribute__((visibility("default"))) int rwkv_b200_debug_trace(unsigned long long * out, int max_records) {
+    unsigned int n = 0;
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(&n, rb::g_trace_n, sizeof(n));
+    const int k = (int) (n < 8192u ? n : 8192u) < max_records ? (int) (n < 8192u ? n : 8192u) : max_records;
+    cudaMemcpyFromSymbol(out, rb::g_trace, (size_t) k * 12 * sizeof(unsigned long long));
+    const unsigned int zero = 0;
+    cudaMemcpyToSymbol(rb::g_trace_n, &zero, sizeof(zero));
+    return k;
+}
+namespace rb {
+#endif
 
 static int ga_stage_override() {
     static const int v = [] { const char * e = getenv("RWKV_B200_GA_STAGES"); return e ? atoi(e) : 0; }();
@@ -267,8 +460,22 @@ static cudaError_t launch_async_n(const GemvBatch & b, int total_ctas, int ygrid
     return launch_pdl_cluster(gemv_async_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, cl, b);
 }
 
+template <int TYPE, int PRO>
+static cudaError_t launch_async_pro(const GemvBatch & b, int total, cudaStream_t st) {
+    constexpr int S = QFmt<TYPE>::QB == 32 ? 3 : 4;          // small models: grids well below 3 x 148 CTAs
+    if (b.pro.D <= 4 * PRO_NT)
+        return launch_pdl(gemv_async_kernel<TYPE, 1, S, PRO, 4>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
+    return launch_pdl(gemv_async_kernel<TYPE, 1, S, PRO, 8>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
+}
+
 template <int TYPE>
 static cudaError_t launch_async_t(const GemvBatch & b, int total, cudaStream_t st) {
+    if (b.pro.kind != PRO_NONE) {
+        if (b.T != 1 || b.ks != 1 || b.pro.D > LN_SMALL_D || b.pro.D % 32 != 0) return cudaErrorInvalidValue;
+        for (int j = 0; j < b.n_jobs; j++)
+            if ((int) b.job[j].W.K != b.pro.D || b.job[j].x_off != 0 || (b.pro.kind == PRO_LNMIX && !b.job[j].pro_mu)) return cudaErrorInvalidValue;
+        return b.pro.kind == PRO_LNMIX ? launch_async_pro<TYPE, PRO_LNMIX>(b, total, st) : launch_async_pro<TYPE, PRO_WKV4>(b, total, st);
+    }
     if (b.T == 1)      return launch_async_n<TYPE, 1>(b, total, 1, st);
     else if (b.T == 2) return launch_async_n<TYPE, 2>(b, total, 1, st);
     else if (b.T <= 4) return launch_async_n<TYPE, 4>(b, total, 1, st);
@@ -303,6 +510,11 @@ static cudaError_t set_smem_attr() {
     if (e == cudaSuccess) e = set_smem_one<TYPE, 2, 4>();
     if (e == cudaSuccess) e = set_smem_one<TYPE, 4, 4>();
     if (e == cudaSuccess) e = set_smem_one<TYPE, 8, 4>();
+    constexpr int SP = QFmt<TYPE>::QB == 32 ? 3 : 4;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1, SP, PRO_LNMIX, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1, SP, PRO_LNMIX, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1, SP, PRO_WKV4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     return e;
 }
 

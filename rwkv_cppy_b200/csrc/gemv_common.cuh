@@ -103,6 +103,35 @@ __device__ __forceinline__ float apply_epilogue_c(const JobT & J, float y, int t
     }
 }
 
+// The epilogue's global operands, fetched ahead of the dot products (right after the dependency
+// wait) so that the tail of a short mat-vec is not another L2 round trip.
+struct EpiOperands { float o = 0.0f, a = 0.0f, v = 0.0f; };
+template <typename JobT>
+__device__ __forceinline__ EpiOperands load_epilogue_operands(const JobT & J, int t, int m) {
+    EpiOperands p;
+    const int e = J.epi;
+    if (e == EPI_ADD_TO || e == EPI_MULADD_TO) p.o = J.out[(size_t) t * J.ldo + m];
+    if (e == EPI_MULADD_TO || e == EPI_ADD_AUX) p.a = J.aux[(size_t) t * J.ld_aux + m];
+    if (e == EPI_BIAS_SIGMOID || e == EPI_V6_DECAY || e == EPI_V7_DECAY) p.v = J.vec[m];
+    return p;
+}
+template <typename JobT>
+__device__ __forceinline__ float apply_epilogue_pre(const JobT & J, float y, const EpiOperands & p) {
+    switch (J.epi) {
+        case EPI_SIGMOID:      return sigmoidf_ref(y);
+        case EPI_RELU_SQ:      { const float r = fmaxf(y, 0.0f); return __fmul_rn(r, r); }
+        case EPI_SILU:         return siluf_ref(y);
+        case EPI_TANH:         return tanhf(y);
+        case EPI_ADD_TO:       return __fadd_rn(p.o, y);
+        case EPI_MULADD_TO:    return __fadd_rn(p.o, __fmul_rn(p.a, y));
+        case EPI_BIAS_SIGMOID: return sigmoidf_ref(__fadd_rn(y, p.v));
+        case EPI_V6_DECAY:     return expf(-expf(__fadd_rn(y, p.v)));
+        case EPI_V7_DECAY:     return expf(__fmul_rn(sigmoidf_ref(__fadd_rn(y, p.v)), -0.606531f));
+        case EPI_ADD_AUX:      return __fadd_rn(p.a, y);
+        default:               return y;
+    }
+}
+
 template <typename JobT>
 __device__ __forceinline__ float apply_epilogue(const JobT & J, float y, int t, int m) {
     switch (J.epi) {

@@ -47,10 +47,29 @@ struct GemvJob {
     int           ld_aux = 0;
     const float * vec = nullptr;      // [M] per-row constant (bias / decay base)
     Act           out_act;            // optional quantised copy of `out` (out_act.q may be null)
+    const float * pro_mu = nullptr;   // PRO_LNMIX launches: this job's token-shift mix vector [K]
+};
+
+// Optional prologue of a single-row quantised mat-vec launch (decode of models up to LN_SMALL_D
+// wide, where the step is a chain of dependent launches, not bytes): every CTA rebuilds the
+// input vector of its job in shared memory instead of reading q8 blocks a separate kernel wrote.
+//   PRO_LNMIX  x -> layer norm -> token-shift mix with the job's pro_mu  (what ln_mix_kernel does; CTA 0
+//              stores the new shift state)
+//   PRO_WKV4   k, v, r, state -> r * wkv  (what wkv4_kernel does; CTA 0 stores the new state)
+// Both reproduce the standalone kernels bit for bit (same per-element arithmetic, same
+// reduction order, same q8 blocks).
+constexpr int LN_SMALL_D = 2048;
+enum PrologueKind : int { PRO_NONE = 0, PRO_LNMIX = 1, PRO_WKV4 = 2 };
+struct GemvPrologue {
+    int kind = PRO_NONE, D = 0, mix_kind = 0;
+    const float * x = nullptr, * ln_w = nullptr, * ln_b = nullptr;          // PRO_LNMIX
+    const float * k = nullptr, * v = nullptr, * r = nullptr, * u = nullptr, * decay = nullptr;   // PRO_WKV4
+    const float * state_in = nullptr; float * state_out = nullptr;          // shift slot (LNMIX) / aa slot (WKV4; bb, pp follow at +D, +2D)
 };
 
 constexpr int GEMV_MAX_JOBS = 8;
 struct GemvBatch {
+    GemvPrologue pro;
     GemvJob job[GEMV_MAX_JOBS];
     int     cta_begin[GEMV_MAX_JOBS + 1];   // prefix sum of CTAs per job (filled by launch_gemv)
     int     n_jobs = 0;
