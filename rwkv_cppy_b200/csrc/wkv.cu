@@ -178,6 +178,9 @@ __global__ void wkv5_kernel(const __grid_constant__ WkvArgs a) {
 // token-by-token decode agree bit for bit.
 // ----------------------------------------------------------------------------------------
 constexpr int WKV_TCH = 32;       // tokens per staged chunk
+#ifndef WKV_SEQ_LC
+#define WKV_SEQ_LC 2     // measured on v6-1.6B T=1024: 1 -> 216 us, 2 -> ~125 us, 4 -> slower than 1 (the chain hand-off serialises)
+#endif
 
 __device__ __forceinline__ void cp_async16(void * smem, const void * gmem) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"((uint32_t) __cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
@@ -185,17 +188,23 @@ __device__ __forceinline__ void cp_async16(void * smem, const void * gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
-template <int S>
-__global__ void __launch_bounds__(64) wkv5_seq_kernel(const __grid_constant__ WkvArgs a, float * __restrict__ yraw) {
-    constexpr int L = S / WKV_CHAINS;                  // key rows per lane (S >= 8)
+// LC = lanes per accumulation chain (1 or 2): a column is spread over 8*LC lanes that own
+// L = S/(8*LC) consecutive key rows each.  With LC = 2 the second lane of a chain continues the
+// first lane's partial sum (one shuffle), so the chain is still summed key by key in order.
+template <int S, int LC>
+__global__ void __launch_bounds__(64 * LC) wkv5_seq_kernel(const __grid_constant__ WkvArgs a, float * __restrict__ yraw) {
+    constexpr int P = WKV_CHAINS * LC;                 // lanes per column
+    constexpr int L = S / P;                           // key rows per lane
+    constexpr int NT = 8 * P;                          // threads: 8 columns per CTA
     constexpr int NV = S / 4;                          // float4 per token per array
+    static_assert(L >= 1 && S % P == 0, "head size too small for this lane split");
     extern __shared__ __align__(16) float sm[];
     // per buffer: r, k, w [TCH][S], v [TCH][8]
     constexpr int BUF = WKV_TCH * (3 * S + 8);
     pdl_trigger();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int h = blockIdx.x, jc = blockIdx.y * 8;      // this CTA's 8 columns of head h
-    const int jl = warp * 4 + (lane >> 3), p = lane & 7;
+    const int jl = warp * (32 / P) + lane / P, p = lane % P;
     const int j = jc + jl, D = a.D;
     const bool dyn_w = a.w != nullptr;
 
@@ -212,14 +221,14 @@ __global__ void __launch_bounds__(64) wkv5_seq_kernel(const __grid_constant__ Wk
     auto stage = [&](int buf, int t0) {
         float * b = sm + buf * BUF;
         const int nt = min(WKV_TCH, a.R - t0);
-        for (int x = tid; x < nt * NV; x += 64) {
+        for (int x = tid; x < nt * NV; x += NT) {
             const int t = x / NV, c = x % NV;
             const size_t g = (size_t) (t0 + t) * D + h * S + c * 4;
             cp_async16(b + t * S + c * 4, a.r + g);
             cp_async16(b + WKV_TCH * S + t * S + c * 4, a.k + g);
             if (dyn_w) cp_async16(b + 2 * WKV_TCH * S + t * S + c * 4, a.w + g);
         }
-        for (int x = tid; x < nt * 2; x += 64) {
+        for (int x = tid; x < nt * 2; x += NT) {
             const int t = x >> 1, c = x & 1;
             cp_async16(b + 3 * WKV_TCH * S + t * 8 + c * 4, a.v + (size_t) (t0 + t) * D + h * S + jc + c * 4);
         }
@@ -255,20 +264,30 @@ __global__ void __launch_bounds__(64) wkv5_seq_kernel(const __grid_constant__ Wk
 #pragma unroll
                 for (int ii = 0; ii < L; ii++) { kk[ii] = sk[t * S + p * L + ii]; rr[ii] = sr[t * S + p * L + ii]; if (dyn_w) ww[ii] = sw[t * S + p * L + ii]; }
             }
-            y = 0.0f;
+            float tmp[L];
 #pragma unroll
             for (int ii = 0; ii < L; ii++) {
                 const float kv = __fmul_rn(vj, kk[ii]);
-                const float tmp = __fmaf_rn(kv, u[ii], st[ii]);
-                y = __fmaf_rn(tmp, rr[ii], y);
+                tmp[ii] = __fmaf_rn(kv, u[ii], st[ii]);
                 st[ii] = __fmaf_rn(st[ii], dyn_w ? ww[ii] : wst[ii], kv);
             }
+            y = 0.0f;
+#pragma unroll
+            for (int ii = 0; ii < L; ii++) y = __fmaf_rn(tmp[ii], rr[ii], y);
+            // lane q of a chain restarts from the partial of lane q-1: keys are still added in order
+#pragma unroll
+            for (int q = 1; q < LC; q++) {
+                float y2 = __shfl_up_sync(FULL, y, 1);
+#pragma unroll
+                for (int ii = 0; ii < L; ii++) y2 = __fmaf_rn(tmp[ii], rr[ii], y2);
+                y = (p % LC) == q ? y2 : y;
+            }                                              // the last lane of each chain now holds its total
         };
         auto finish = [&](int t, float y) {
-            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 1));
-            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 2));
-            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 4));
-            if (p == 0) yraw[(size_t) (t0 + t) * D + h * S + j] = y;
+            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, LC));
+            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 2 * LC));
+            y = __fadd_rn(y, __shfl_xor_sync(FULL, y, 4 * LC));
+            if (p == LC - 1) yraw[(size_t) (t0 + t) * D + h * S + j] = y;
         };
         int t = 0;
         for (; t + 4 <= nt; t += 4) {
@@ -305,13 +324,14 @@ template <int S>
 static cudaError_t launch_wkv5_t(const WkvArgs & a, cudaStream_t st) {
     if (!a.batch && a.R >= WKV_SEQ_MIN_ROWS && a.yraw != nullptr) {
         constexpr size_t smem = 2 * WKV_TCH * (3 * S + 8) * sizeof(float);
+        constexpr int LC = S >= 32 ? WKV_SEQ_LC : (S >= 16 ? 2 : 1);   // 8*LC lanes per state column
         static bool attr_set = false;                     // per template instance; > 48 KB needs the opt-in
         if (!attr_set && smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute(wkv5_seq_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+            cudaError_t e = cudaFuncSetAttribute(wkv5_seq_kernel<S, LC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
             if (e != cudaSuccess) return e;
             attr_set = true;
         }
-        cudaError_t e = launch_pdl(wkv5_seq_kernel<S>, dim3(a.H, S / 8), dim3(64), smem, st, a, a.yraw);
+        cudaError_t e = launch_pdl(wkv5_seq_kernel<S, LC>, dim3(a.H, S / 8), dim3(64 * LC), smem, st, a, a.yraw);
         if (e != cudaSuccess) return e;
         return launch_pdl(wkv5_norm_kernel<S>, dim3((a.D + 255) / 256, a.R), dim3(256), 0, st, a, (const float *) a.yraw);
     }
