@@ -35,7 +35,8 @@ __device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, i
 #pragma unroll
     for (int o = 0; o < N; o++) {
         const Act & a = outs[o];
-        if (valid) a.f[row * a.K + e] = v[o];
+        if (valid && a.f) a.f[row * a.K + e] = v[o];
+        if (valid && a.h) a.h[row * a.K + e] = __half_as_ushort(__float2half_rn(v[o]));
         if (a.q == nullptr) continue;
         if (valid) a.q[row * a.K + e] = (int8_t) q[o];
         if ((threadIdx.x & 31) == 0 && e < a.K) {      // warps past the end of the row own no block

@@ -124,10 +124,10 @@ struct Pass {
                     (!type_quantized(jobs[i].W.type) || gemv_ksplit(jobs[k].W.M, jobs[k].W.K) == gemv_ksplit(jobs[i].W.M, jobs[i].W.K))) {
                     const GemvJob & j = jobs[k];
                     if (type_quantized(j.W.type) && tc_written.count(j.x.f)) {   // produced by a GEMM: q8 blocks are stale
-                        Act a = j.x; chk(launch_quantize_act(a, rows, st)); tc_written.erase(j.x.f);
+                        Act a = j.x; a.h = nullptr; chk(launch_quantize_act(a, rows, st)); tc_written.erase(j.x.f);
                     }
                     if (j.out_act.f) tc_written.erase(j.out_act.f);
-                    b.job[b.n_jobs++] = j; done[k] = true;
+                    b.job[b.n_jobs] = j; b.job[b.n_jobs].out_act.h = nullptr; b.n_jobs++; done[k] = true;
                 }
             chk(launch_gemv(b, st));
         }
@@ -135,6 +135,17 @@ struct Pass {
     std::vector<const float *> to_half_marks;
     bool tc_job(const GemvJob & j, int rows) const {
         return j.x.h != nullptr && (j.x_off % 8) == 0 && (j.x.K % 8) == 0 && gemm_tc_supported(j.W, rows);
+    }
+    // The form a producer should emit `a` in: when every consumer is a tensor-core GEMM the rows are
+    // written once as FP16 (no FP32 rows, no q8 blocks, no conversion launch); otherwise FP32 + q8.
+    Act produced(const Act & a, std::initializer_list<const DevMat *> consumers, int rows = -1) {
+        if (rows < 0) rows = R;
+        bool all_tc = a.h != nullptr && (a.K % 8) == 0 && consumers.size() > 0;
+        for (const DevMat * W : consumers) all_tc = all_tc && gemm_tc_supported(*W, rows);
+        Act o = a;
+        if (all_tc) { o.f = nullptr; o.q = nullptr; o.d = nullptr; o.s = nullptr; o.isum = nullptr; tc_written[a.f] = true; }
+        else        { o.h = nullptr; tc_written.erase(a.f); }
+        return o;
     }
 
     // Decode of narrow models is a chain of dependent launches: fold the layer norm + token-shift mix
@@ -162,14 +173,18 @@ struct Pass {
     const float * sin(uint32_t layer, size_t off) const { return fa.state_in + (size_t) layer * m.layer_state_len() + off; }
     float * sout(uint32_t layer, size_t off) const { return fa.state_out + (size_t) layer * m.layer_state_len() + off; }
 
-    void ln_mix(uint32_t layer, bool att, int kind, int n_out, const float * const * mu, bool want_sx) {
+    void ln_mix(uint32_t layer, bool att, int kind, int n_out, const float * const * mu, bool want_sx, const Act * outs = nullptr) {
         const LayerW & l = m.layers[layer];
         LnMixArgs a;
         a.x = ws.x; a.ln_w = att ? l.ln1_w : l.ln2_w; a.ln_b = att ? l.ln1_b : l.ln2_b;
         const size_t slot = att ? D : 0;                       // [ffn_xx, att_xx, ...] (rwkv_graph.inc:545-606)
         a.state_in = sin(layer, slot); a.state_out = sout(layer, slot);
         a.state_stride = sstride; a.batch = fa.batch; a.R = R; a.D = (int) D; a.kind = kind; a.n_out = n_out;
-        for (int i = 0; i < n_out; i++) { a.mu[i] = mu[i]; a.out[i] = ws.mix[i]; }
+        for (int i = 0; i < n_out; i++) {
+            a.mu[i] = mu[i];
+            if (outs) a.out[i] = outs[i];
+            else { a.out[i] = ws.mix[i]; a.out[i].h = nullptr; tc_written.erase(ws.mix[i].f); }
+        }
         if (want_sx) { a.x0 = ws.x0; a.sx = ws.sx; }
         chk(launch_ln_mix(a, st));
     }
@@ -178,7 +193,7 @@ struct Pass {
         WkvArgs a;
         a.R = R; a.D = (int) D; a.H = m.head_count; a.S = m.head_size; a.batch = fa.batch; a.state_stride = sstride;
         a.state_in = sin(layer, 2 * D); a.state_out = sout(layer, 2 * D);
-        a.r = ws.r; a.k = ws.k; a.v = ws.v; a.y = ws.y; a.layer = (int) layer; a.yraw = ws.yraw;
+        a.r = ws.r; a.k = ws.k; a.v = ws.v; a.y = produced(ws.y, {&m.layers[layer].att_output}); a.layer = (int) layer; a.yraw = ws.yraw;
         return a;
     }
 
@@ -194,7 +209,7 @@ struct Pass {
               job(l.att_receptance, ws.mix[2], ws.r, Dl, EPI_SIGMOID)}, R);
         WkvArgs a = wkv_base(layer);
         a.D = Dl; a.state_D = (int) D; a.chan0 = m.tp.rank * Dl;
-        a.y = ws.y; a.y.K = Dl;
+        a.y = ws.y; a.y.K = Dl; a.y.h = nullptr; tc_written.erase(ws.y.f);
         a.u = l.time_first; a.decay = l.time_decay;
         chk(launch_wkv4(a, st));
         Act yl = ws.y; yl.K = Dl;
@@ -228,7 +243,8 @@ struct Pass {
                 k.pro_mu = l.ffn_mu[0];
                 gemv({k}, R, &P);
             } else {
-                ln_mix(layer, false, MIX_SX, 1, l.ffn_mu, false);
+                const Act outs[1] = {produced(ws.mix[0], {&l.ffn_key})};
+                ln_mix(layer, false, MIX_SX, 1, l.ffn_mu, false, outs);
                 gemv({k}, R);
             }
             Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
@@ -243,7 +259,8 @@ struct Pass {
             k.pro_mu = l.ffn_mu[0]; r.pro_mu = l.ffn_mu[1];
             gemv({k, r}, R, &P);
         } else {
-            ln_mix(layer, false, kind, 2, l.ffn_mu, false);
+            const Act outs[2] = {produced(ws.mix[0], {&l.ffn_key}), produced(ws.mix[1], {&l.ffn_receptance})};
+            ln_mix(layer, false, kind, 2, l.ffn_mu, false, outs);
             gemv({k, r}, R);
         }
         Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
@@ -260,7 +277,8 @@ struct Pass {
             for (int i = 0; i < 3; i++) kvr[i].pro_mu = l.att_mu[i];
             gemv(kvr, R, &P);
         } else {
-            ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false);
+            const Act outs[3] = {produced(ws.mix[0], {&l.att_key}), produced(ws.mix[1], {&l.att_value}), produced(ws.mix[2], {&l.att_receptance})};
+            ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false, outs);
             gemv(kvr, R);
         }
         WkvArgs a = wkv_base(layer);
@@ -289,7 +307,9 @@ struct Pass {
             for (size_t i = 0; i < jobs.size(); i++) jobs[i].pro_mu = l.att_mu[i];
             gemv(jobs, R, &P);
         } else {
-            ln_mix(layer, true, MIX_LERP, gate ? 4 : 3, l.att_mu, false);
+            const Act outs[4] = {produced(ws.mix[0], {&l.att_key}), produced(ws.mix[1], {&l.att_value}), produced(ws.mix[2], {&l.att_receptance}),
+                                 gate ? produced(ws.mix[3], {&l.att_gate}) : Act()};
+            ln_mix(layer, true, MIX_LERP, gate ? 4 : 3, l.att_mu, false, outs);
             gemv(jobs, R);
         }
         WkvArgs a = wkv_base(layer);
@@ -301,7 +321,8 @@ struct Pass {
 
     void att_v6(uint32_t layer) {
         const LayerW & l = m.layers[layer];
-        ln_mix(layer, true, MIX_SX, 1, l.att_mu, true);                      // xxx = x + sx*maa_x
+        const Act xxx[1] = {produced(ws.mix[0], {&l.maa_w1})};
+        ln_mix(layer, true, MIX_SX, 1, l.att_mu, true, xxx);                 // xxx = x + sx*maa_x
         const int E5 = (int) l.maa_w1.M, E = E5 / 5;
         GemvJob j1 = job(l.maa_w1, ws.mix[0], nullptr, 0, EPI_TANH);
         j1.out_act = ws.lora[0]; j1.out_act.K = E5;
@@ -312,7 +333,8 @@ struct Pass {
         for (int n = 0; n < 5; n++) { GemvJob j = job(l.maa_w2[n], t5, ws.m5 + (size_t) n * R * D, (int) D, EPI_STORE); j.x_off = n * E; jobs.push_back(j); }
         gemv(jobs, R);
         V6Mix2Args mx; mx.x0 = ws.x0; mx.sx = ws.sx; mx.R = R; mx.D = (int) D;
-        for (int n = 0; n < 5; n++) { mx.m[n] = ws.m5 + (size_t) n * R * D; mx.maa[n] = l.att_mu[1 + n]; mx.out[n] = ws.mix[1 + n]; }
+        const DevMat * cons5[5] = {&l.decay_w1, &l.att_key, &l.att_value, &l.att_receptance, &l.att_gate};
+        for (int n = 0; n < 5; n++) { mx.m[n] = ws.m5 + (size_t) n * R * D; mx.maa[n] = l.att_mu[1 + n]; mx.out[n] = produced(ws.mix[1 + n], {cons5[n]}); }
         chk(launch_v6_mix2(mx, st));                                          // mix[1..5] = xw, xk, xv, xr, xg
         const int DW = (int) l.decay_w1.M;
         GemvJob jd = job(l.decay_w1, ws.mix[1], nullptr, 0, EPI_TANH); jd.out_act = ws.lora[1]; jd.out_act.K = DW;
@@ -330,7 +352,10 @@ struct Pass {
 
     void att_v7(uint32_t layer) {
         const LayerW & l = m.layers[layer];
-        ln_mix(layer, true, MIX_SX, 6, l.att_mu, false);                     // mix = xr, xw, xk, xv, xa, xg
+        const Act outs[6] = {produced(ws.mix[0], {&l.att_receptance}), produced(ws.mix[1], {&l.w1}), produced(ws.mix[2], {&l.att_key}),
+                             layer != 0 ? produced(ws.mix[3], {&l.att_value, &l.v1}) : produced(ws.mix[3], {&l.att_value}),
+                             produced(ws.mix[4], {&l.a1}), produced(ws.mix[5], {&l.g1})};
+        ln_mix(layer, true, MIX_SX, 6, l.att_mu, false, outs);               // mix = xr, xw, xk, xv, xa, xg
         auto lora_in = [&](int slot, const DevMat & W, int epi) {
             GemvJob j = job(W, ws.mix[slot == 0 ? 1 : slot == 1 ? 4 : slot == 2 ? 5 : 3], nullptr, 0, epi);
             j.out = ws.lora[slot].f; j.ldo = (int) W.M;                       // low-rank mats are never quantised: FP32 rows suffice
@@ -370,7 +395,7 @@ struct Pass {
         if (fa.logits) {
             const int rows = fa.batch ? R : 1;
             const float * x = fa.batch ? ws.x : ws.x + (size_t) (R - 1) * D;
-            chk(launch_ln_act(x, (int) D, rows, (int) D, m.ln_out_w, m.ln_out_b, ws.head_in, st));
+            chk(launch_ln_act(x, (int) D, rows, (int) D, m.ln_out_w, m.ln_out_b, produced(ws.head_in, {&m.head}, rows), st));
             if (m.tp.world > 1) {      // vocabulary rows are sharded: gather the slices (equal-sized, zero-padded at the end)
                 const int Vl = (int) ((m.n_vocab + m.tp.world - 1) / m.tp.world);
                 gemv({job(m.head, ws.head_in, ws.logits_part, Vl, EPI_STORE)}, rows);
