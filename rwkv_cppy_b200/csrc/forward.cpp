@@ -49,6 +49,10 @@ bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows
             && dalloc(ws, ws.a, n) && dalloc(ws, ws.vgate, n) && dalloc(ws, ws.ffn_r, n) && dalloc(ws, ws.v_first, n);
     if (m.arch_major == 6) ok = ok && dalloc(ws, ws.m5, 5 * n);
     if (m.arch_major >= 5 && rows >= WKV_SEQ_MIN_ROWS) ok = ok && dalloc(ws, ws.yraw, n);
+    if ((m.arch_major == 5 || m.arch_major == 6) && m.head_size == 64 && gemm_tc_enabled() && rows >= gemm_tc_min_rows()) {
+        const size_t chunks = ((size_t) rows + WKV_CHUNK_TOKENS - 1) / WKV_CHUNK_TOKENS;
+        ok = ok && dalloc(ws, ws.wkv_ds, chunks * D * 64) && dalloc(ws, ws.wkv_pc, chunks * D);
+    }
     if (m.tp.world > 1) {
         ok = ok && dalloc(ws, ws.tp_send, 2 * n) && dalloc(ws, ws.tp_recv, 2 * n) && dalloc(ws, ws.tp_att, n);
         ok = ok && cudaMemset(ws.tp_send, 0, 2 * n * sizeof(float)) == cudaSuccess;     // the r-shard half stays zero outside this rank's slice
@@ -194,6 +198,9 @@ struct Pass {
         a.R = R; a.D = (int) D; a.H = m.head_count; a.S = m.head_size; a.batch = fa.batch; a.state_stride = sstride;
         a.state_in = sin(layer, 2 * D); a.state_out = sout(layer, 2 * D);
         a.r = ws.r; a.k = ws.k; a.v = ws.v; a.y = produced(ws.y, {&m.layers[layer].att_output}); a.layer = (int) layer; a.yraw = ws.yraw;
+        // rows whose projections run on the tensor cores (FP16 operands) are in tolerance mode anyway:
+        // their v5 / v6 recurrence takes the chunk-parallel form; exact-path rows keep the serial order
+        if (!fa.batch && ws.wkv_ds && gemm_tc_supported(m.layers[layer].att_output, R)) { a.chunk_ds = ws.wkv_ds; a.chunk_pc = ws.wkv_pc; }
         return a;
     }
 

@@ -174,11 +174,17 @@ struct WkvArgs {
     int   layer = 0;
     Act   y;                              // output rows
     float * yraw = nullptr;               // [R][D] scratch: raw scan outputs of the sequence kernels (before the head norm)
+    // chunk-parallel form (wkv_chunk.cu): scratch for ceil(R/16) chunks, [H][chunks][S][S] and [H][chunks][S];
+    // both set => long sequences of head-size-64 models take it (tolerance mode, like the tensor-core GEMM)
+    float * chunk_ds = nullptr, * chunk_pc = nullptr;
 };
 constexpr int WKV_SEQ_MIN_ROWS = 8;       // sequences at least this long use the scan kernels (same arithmetic, different work split)
 cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st);   // state slots: aa, bb, pp at state + {0,1,2}*D
 cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st);   // v5.1 / v5.2 / v6 (w != nullptr => per-token decay)
 cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st);
+bool wkv5_chunked_supported(const WkvArgs & a);                // head size 64, one stream, scratch present, RWKV_B200_NO_WKV_CHUNK != 1
+cudaError_t launch_wkv5_chunked(const WkvArgs & a, cudaStream_t st);
+constexpr int WKV_CHUNK_TOKENS = 16;
 
 // tensor parallel ffn tail: x[t][m] += recv[t][D + m] * recv[t][m]  (recv = all-reduced [partial Wv k | r shards], 2*D per row)
 cudaError_t launch_tp_ffn_combine(float * x, const float * recv, int R, int D, cudaStream_t st);

@@ -322,6 +322,7 @@ __global__ void __launch_bounds__(256) wkv5_norm_kernel(const __grid_constant__ 
 
 template <int S>
 static cudaError_t launch_wkv5_t(const WkvArgs & a, cudaStream_t st) {
+    if (S == 64 && wkv5_chunked_supported(a)) return launch_wkv5_chunked(a, st);
     if (!a.batch && a.R >= WKV_SEQ_MIN_ROWS && a.yraw != nullptr) {
         constexpr size_t smem = 2 * WKV_TCH * (3 * S + 8) * sizeof(float);
         constexpr int LC = S >= 32 ? WKV_SEQ_LC : (S >= 16 ? 2 : 1);   // 8*LC lanes per state column

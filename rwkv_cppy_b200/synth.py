@@ -21,7 +21,7 @@ FP32, FP16 = 0, 1
 @dataclass
 class Shape:
     name: str
-    arch: int            # 4, 6 or 7
+    arch: int            # 4, 5 (v5.2), 6 or 7
     n_layer: int
     n_embed: int
     n_vocab: int
@@ -45,6 +45,7 @@ SHAPES = {
     "v7-2b9": Shape("v7-2b9", 7, 32, 2560, 65536, 10240, decay_lora=96, a_lora=96, v_lora=64, g_lora=320),
     # small stand-ins for tests
     "v4-mini": Shape("v4-mini", 4, 2, 256, 512, 1024),
+    "v5-mini": Shape("v5-mini", 5, 2, 256, 512, 1024),
     "v6-mini": Shape("v6-mini", 6, 2, 256, 512, 896, mix_lora=32, decay_lora=64),
     "v7-mini": Shape("v7-mini", 7, 3, 256, 512, 1024, decay_lora=64, a_lora=64, v_lora=32, g_lora=128),
 }
@@ -107,6 +108,12 @@ def write_model(path: str, shape: Shape, data_type: int = FP16, seed: int = 0) -
                 w.tensor(p + f"att.time_mix_{n}", rng.random(D))
             w.tensor(p + "att.time_first", 0.3 * rng.standard_normal(D))
             w.tensor(p + "att.time_decay", -np.exp(rng.uniform(-6, -1, D)))          # stored as -exp(.) (convert :125-126)
+        elif s.arch == 5:
+            # v5.2: per-channel decay stored as exp(-exp(.)), time_faaaa raw (convert :112-123)
+            for n in "kvrg":
+                w.tensor(p + f"att.time_mix_{n}", rng.random(D))
+            w.tensor(p + "att.time_decay", np.exp(-np.exp(rng.uniform(-6, -1, (H, S, 1)))))
+            w.tensor(p + "att.time_faaaa", 0.3 * rng.standard_normal((H, S, 1)))
         elif s.arch == 6:
             for n in "xwkvrg":
                 w.tensor(p + f"att.time_maa_{n}", rng.random(D))
@@ -136,12 +143,12 @@ def write_model(path: str, shape: Shape, data_type: int = FP16, seed: int = 0) -
         w.matrix(p + "att.key.weight", D, D, gain=0.5 if s.arch >= 5 else 1.0)
         w.matrix(p + "att.value.weight", D, D)
         w.matrix(p + "att.receptance.weight", D, D)
-        if s.arch == 6:
+        if s.arch in (5, 6):
             w.matrix(p + "att.gate.weight", D, D)
         w.matrix(p + "att.output.weight", D, D, gain=0.5)
         if s.arch >= 5:
             w.ln(p + "att.ln_x", D)
-        if s.arch == 4:
+        if s.arch in (4, 5):
             w.tensor(p + "ffn.time_mix_k", rng.random(D))
             w.tensor(p + "ffn.time_mix_r", rng.random(D))
         elif s.arch == 6:

@@ -82,3 +82,33 @@ def test_python_wrapper_end_to_end(shared_library):
     m.free()
     with pytest.raises(ValueError):
         m.eval(0, None)
+
+
+# ---- long sequences: the tolerance-mode path (tensor-core GEMM with FP16 operands + chunk-parallel
+# WKV for v5 / v6 heads of 64) against token-by-token decode on the exact kernels -------------------
+LONG_CASES = [("v6-mini", "FP16"), ("v6-mini", "FP16-to-Q5_1"), ("v5-mini", "FP16"), ("v5-mini", "FP16-to-Q4_0"),
+              ("v7-mini", "FP16-to-Q8_0"), ("v4-mini", "FP16-to-Q4_1")]
+
+
+@pytest.mark.parametrize("shape,fmt", LONG_CASES, ids=[f"{s}-{f}" for s, f in LONG_CASES])
+@pytest.mark.parametrize("T", [64, 150, 523])
+def test_long_sequence_matches_serial_decode(shared_library, raw_lib, shape, fmt, T):
+    from rwkv_cppy_b200 import synth
+    path = synth.ensure_model(shared_library, shape, fmt)
+    ctx = raw_lib.load(path, 1, 0)
+    rng = np.random.default_rng(T)
+    tokens = [int(t) for t in rng.integers(0, 512, T)]
+    s_ser, lg_ser = run_serial(ctx, tokens)
+    s_seq, lg_seq = ctx.eval_sequence(tokens, ctx.init_state())
+    assert np.all(np.isfinite(lg_seq)) and np.all(np.isfinite(s_seq))
+    # FP16 operand rounding (2^-11 relative per operand) over K <= 1024 products and a few layers
+    lscale = max(1.0, float(np.abs(lg_ser).max()))
+    finite = np.abs(s_ser) < 1e29                         # v4 pp slots start at -1e30
+    sscale = max(1.0, float(np.abs(s_ser[finite]).max()))
+    assert np.abs(lg_seq - lg_ser).max() <= 3e-2 * lscale, float(np.abs(lg_seq - lg_ser).max() / lscale)
+    assert np.abs(s_seq[finite] - s_ser[finite]).max() <= 3e-2 * sscale, float(np.abs(s_seq[finite] - s_ser[finite]).max() / sscale)
+    # chunks of the sequence (state carried through the host) agree with the single call the same way
+    s_c, lg_c = ctx.eval_sequence(tokens[: T // 2], ctx.init_state())
+    s_c, lg_c = ctx.eval_sequence(tokens[T // 2:], s_c)
+    assert np.abs(lg_c - lg_ser).max() <= 3e-2 * lscale
+    ctx.free()
