@@ -210,6 +210,77 @@ cudaError_t launch_v6_mix2(const V6Mix2Args & a, cudaStream_t st) {
     return launch_pdl(v6_mix2_kernel, dim3(a.R), dim3(256), 0, st, a);
 }
 
+// CTA = 64 channels x 32 tokens; thread = channels (c0 + lane, c0 + lane + 32) x 4 tokens.  The low-rank
+// rows of the 32 tokens sit in shared memory (broadcast reads); the W2 rows of the current mix are staged
+// through shared memory (coalesced loads, transposed so that lanes read consecutive channels) into registers.
+__global__ void __launch_bounds__(256) v6_mix_lora_kernel(const __grid_constant__ V6MixLoraArgs a) {
+    __shared__ __align__(16) float sl[32][160];
+    __shared__ float sw[32][65];                             // sw[j][channel]
+    pdl_trigger();
+    const int tid = threadIdx.x, lane = tid & 31, tg = tid >> 5;
+    const int c0 = blockIdx.x * 64, t0 = blockIdx.y * 32, D = a.D;
+    const int ea = c0 + lane, eb = c0 + lane + 32;
+    const bool a_ok = ea < D, b_ok = eb < D;
+    auto stage_w = [&](int n) {                              // 64 rows x 32 floats, two float4 per thread
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            const int idx = q * 256 + tid, ch = idx >> 3, j4 = (idx & 7) * 4;
+            float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (c0 + ch < D) v = *reinterpret_cast<const float4 *>(a.w2[n] + (size_t) (c0 + ch) * 32 + j4);
+            sw[j4][ch] = v.x; sw[j4 + 1][ch] = v.y; sw[j4 + 2][ch] = v.z; sw[j4 + 3][ch] = v.w;
+        }
+    };
+    stage_w(0);                                              // constants: before the wait
+    pdl_wait();
+#pragma unroll
+    for (int q = 0; q < 5; q++) {
+        const int idx = q * 256 + tid, t = idx / 40, c = idx % 40;
+        float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (t0 + t < a.R) v = *reinterpret_cast<const float4 *>(a.lora + (size_t) (t0 + t) * a.ld_lora + c * 4);
+        *reinterpret_cast<float4 *>(&sl[t][c * 4]) = v;
+    }
+    float x0a[4], x0b[4], sxa[4], sxb[4];
+#pragma unroll
+    for (int tt = 0; tt < 4; tt++) {
+        const int t = t0 + tg * 4 + tt;
+        const bool ok = t < a.R;
+        x0a[tt] = (ok && a_ok) ? a.x0[(size_t) t * D + ea] : 0.0f; sxa[tt] = (ok && a_ok) ? a.sx[(size_t) t * D + ea] : 0.0f;
+        x0b[tt] = (ok && b_ok) ? a.x0[(size_t) t * D + eb] : 0.0f; sxb[tt] = (ok && b_ok) ? a.sx[(size_t) t * D + eb] : 0.0f;
+    }
+#pragma unroll 1
+    for (int n = 0; n < 5; n++) {
+        __syncthreads();                                     // sw (and, first time, sl) staged
+        float wa[32], wb[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++) { wa[j] = sw[j][lane]; wb[j] = sw[j][lane + 32]; }
+        __syncthreads();                                     // everyone holds its rows: sw may be refilled
+        if (n + 1 < 5) stage_w(n + 1);
+        const float ma = a_ok ? a.maa[n][ea] : 0.0f, mb = b_ok ? a.maa[n][eb] : 0.0f;
+#pragma unroll
+        for (int tt = 0; tt < 4; tt++) {
+            const int t = t0 + tg * 4 + tt;
+            const float * lp = &sl[tg * 4 + tt][n * 32];
+            float m0 = 0.0f, m1 = 0.0f;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float4 l4 = *reinterpret_cast<const float4 *>(lp + 4 * j);
+                m0 = fmaf(l4.x, wa[4 * j], m0); m0 = fmaf(l4.y, wa[4 * j + 1], m0); m0 = fmaf(l4.z, wa[4 * j + 2], m0); m0 = fmaf(l4.w, wa[4 * j + 3], m0);
+                m1 = fmaf(l4.x, wb[4 * j], m1); m1 = fmaf(l4.y, wb[4 * j + 1], m1); m1 = fmaf(l4.z, wb[4 * j + 2], m1); m1 = fmaf(l4.w, wb[4 * j + 3], m1);
+            }
+            if (t < a.R) {
+                __half * o = reinterpret_cast<__half *>(a.out_h[n]) + (size_t) t * D;
+                if (a_ok) o[ea] = __float2half_rn(__fadd_rn(__fmul_rn(__fadd_rn(m0, ma), sxa[tt]), x0a[tt]));
+                if (b_ok) o[eb] = __float2half_rn(__fadd_rn(__fmul_rn(__fadd_rn(m1, mb), sxb[tt]), x0b[tt]));
+            }
+        }
+    }
+}
+
+cudaError_t launch_v6_mix_lora(const V6MixLoraArgs & a, cudaStream_t st) {
+    if (a.ld_lora != 160) return cudaErrorInvalidValue;
+    return launch_pdl(v6_mix_lora_kernel, dim3((a.D + 63) / 64, (a.R + 31) / 32), dim3(256), 0, st, a);
+}
+
 __global__ void __launch_bounds__(256) quantize_act_kernel(Act a) {
     pdl_trigger();
     pdl_wait();

@@ -336,13 +336,23 @@ struct Pass {
         if (E5 % 32 != 0) { j1.out = ws.lora[0].f; j1.ldo = E5; j1.out_act = Act(); }
         gemv({j1}, R);
         Act t5 = ws.lora[0]; t5.K = E5; if (E5 % 32 != 0) t5.q = nullptr;
-        std::vector<GemvJob> jobs;
-        for (int n = 0; n < 5; n++) { GemvJob j = job(l.maa_w2[n], t5, ws.m5 + (size_t) n * R * D, (int) D, EPI_STORE); j.x_off = n * E; jobs.push_back(j); }
-        gemv(jobs, R);
         V6Mix2Args mx; mx.x0 = ws.x0; mx.sx = ws.sx; mx.R = R; mx.D = (int) D;
         const DevMat * cons5[5] = {&l.decay_w1, &l.att_key, &l.att_value, &l.att_receptance, &l.att_gate};
-        for (int n = 0; n < 5; n++) { mx.m[n] = ws.m5 + (size_t) n * R * D; mx.maa[n] = l.att_mu[1 + n]; mx.out[n] = produced(ws.mix[1 + n], {cons5[n]}); }
-        chk(launch_v6_mix2(mx, st));                                          // mix[1..5] = xw, xk, xv, xr, xg
+        bool fold = E == 32 && D % 2 == 0 && ws.lora[0].f != nullptr;          // all five mixes feed tensor-core GEMMs: fold the rank-32 stage in
+        for (int n = 0; n < 5; n++) {
+            mx.m[n] = ws.m5 + (size_t) n * R * D; mx.maa[n] = l.att_mu[1 + n]; mx.out[n] = produced(ws.mix[1 + n], {cons5[n]});
+            fold = fold && mx.out[n].f == nullptr && mx.out[n].h != nullptr && l.maa_w2[n].type == T_F32 && l.maa_w2[n].K == 32;
+        }
+        if (fold) {
+            V6MixLoraArgs ml; ml.x0 = ws.x0; ml.sx = ws.sx; ml.lora = ws.lora[0].f; ml.ld_lora = E5; ml.R = R; ml.D = (int) D;
+            for (int n = 0; n < 5; n++) { ml.w2[n] = (const float *) l.maa_w2[n].qs; ml.maa[n] = l.att_mu[1 + n]; ml.out_h[n] = mx.out[n].h; }
+            chk(launch_v6_mix_lora(ml, st));
+        } else {
+            std::vector<GemvJob> jobs;
+            for (int n = 0; n < 5; n++) { GemvJob j = job(l.maa_w2[n], t5, ws.m5 + (size_t) n * R * D, (int) D, EPI_STORE); j.x_off = n * E; jobs.push_back(j); }
+            gemv(jobs, R);
+            chk(launch_v6_mix2(mx, st));                                      // mix[1..5] = xw, xk, xv, xr, xg
+        }
         const int DW = (int) l.decay_w1.M;
         GemvJob jd = job(l.decay_w1, ws.mix[1], nullptr, 0, EPI_TANH); jd.out_act = ws.lora[1]; jd.out_act.K = DW;
         if (DW % 32 != 0) { jd.out = ws.lora[1].f; jd.ldo = DW; jd.out_act = Act(); }

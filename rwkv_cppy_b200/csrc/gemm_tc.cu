@@ -188,8 +188,12 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
                         bulk_g2s(sQ + qs * CH, J.tc + ((size_t) mt * J.kblocks + kb) * CH, CH, bar_qfull + 8 * qs);
                     }
                     mbar_wait(bar_empty + 8 * s, ph ^ 1);
+#ifdef RB_ABL_NOB
+                    mbar_arrive(bar_full + 8 * s);
+#else
                     mbar_expect_tx(bar_full + 8 * s, QUANT ? B_BYTES : B_BYTES + GT_A_BYTES);
                     tma_load_2d(sB + s * B_BYTES, &J.xmap, (int) (kb * GT_BK), nt * BN, bar_full + 8 * s);
+#endif
                     if (!QUANT) tma_load_2d(sA + s * GT_A_BYTES, &J.wmap, (int) (kb * GT_BK), mt * GT_BM, bar_full + 8 * s);
                 }
             }
@@ -213,6 +217,9 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
                     const uint64_t ad = umma_desc_k_sw128(sA + s * GT_A_BYTES), bd = umma_desc_k_sw128(sB + s * B_BYTES);
 #pragma unroll
                     for (int k = 0; k < GT_BK / 16; k++)          // +32 bytes (16 halves) along K inside the swizzle atom
+#ifdef RB_ABL_NOMMA
+                        if (kb == 0 && k == 0)
+#endif
                         tc_mma_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | (uint32_t) k) != 0 ? 1u : 0u);
                     tc_commit(bar_empty + 8 * s);                 // stage free once these MMAs have read it
                     if (kb + 1 == kblocks) tc_commit(bar_tfull + 8 * buf);
@@ -271,13 +278,19 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_qempty + 8 * qs);   // chunk is in registers: hand the slot back
                 uint4 h[4];
+#ifdef RB_ABL_NODQ
+                h[0] = q0; h[1] = q0; h[2] = make_uint4(qh, dm, qh, dm); h[3] = q1;
+#else
                 dequant_block_f16<TYPE>(h, q0, q1, qh, dm);
+#endif
                 mbar_wait(bar_empty + 8 * s, ph ^ 1);               // the MMAs that read this stage have completed
                 uint8_t * ar = pA + s * GT_A_BYTES + row * 128;
 #pragma unroll
                 for (int c = 0; c < 4; c++)
                     *reinterpret_cast<uint4 *>(ar + (((blk * 4 + c) ^ (row & 7)) << 4)) = h[c];
+#ifndef RB_ABL_NOFENCE
                 fence_proxy_async_smem();                           // generic-proxy stores -> visible to tcgen05.mma
+#endif
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_full + 8 * s);
             }

@@ -153,6 +153,12 @@ cudaError_t launch_ln_act(const float * x, int ldx, int R, int D, const float * 
 struct V6Mix2Args { const float * x0, * sx; const float * m[5]; const float * maa[5]; Act out[5]; int R, D; };
 cudaError_t launch_v6_mix2(const V6Mix2Args & a, cudaStream_t st);
 
+// Same mixes with the low-rank second stage folded in (long sequences on the tensor-core path):
+//   m_i[t][e] = sum_j lora[t][i*32 + j] * W2_i[e][j]   (rwkv_graph.inc:312-324; rank 32 per mix),  out_i = fp16(x0 + sx * (maa_i + m_i))
+// so the five [R][D] FP32 products are never written to memory.  W2_i: FP32 [D][32] row-major.
+struct V6MixLoraArgs { const float * x0, * sx, * lora; int ld_lora; const float * w2[5]; const float * maa[5]; uint16_t * out_h[5]; int R, D; };
+cudaError_t launch_v6_mix_lora(const V6MixLoraArgs & a, cudaStream_t st);
+
 // standalone activation quantiser (when a producer could not fuse it)
 cudaError_t launch_quantize_act(Act a, int R, cudaStream_t st);
 

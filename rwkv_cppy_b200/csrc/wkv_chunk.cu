@@ -7,15 +7,16 @@
 //     y_t[j]    = sum_i r_t[i] * (u[i] k_t[i] v_t[j] + S_{t-1}[i][j])
 //     S_t[i][j] = S_{t-1}[i][j] w_t[i] + k_t[i] v_t[j]
 // is sequential in t: the scan kernel spends 180 ns per token whatever the GPU.  Unrolling the
-// recurrence over a chunk of C = 16 tokens with LP_t[i] = sum_{q<t} log w_q[i]:
-//     S_{t-1}  = S_in * exp(LP_t)  +  sum_{s<t} exp(LP_t - LP_{s+1}) k_s v_s^T
-//     y_t[j]   = sum_i r_t[i] exp(LP_t[i]) S_in[i][j]                                  (inter)
-//              + sum_{s<t} (sum_i r_t[i] k_s[i] exp(LP_t[i] - LP_{s+1}[i])) v_s[j]      (intra)
-//              + (sum_i r_t[i] u[i] k_t[i]) v_t[j]                                      (bonus)
-//     S_out    = S_in * exp(LP_C) + sum_s exp(LP_C - LP_{s+1}) k_s v_s^T
-// Every exponent is <= 0 (s + 1 <= t), so nothing overflows however strong the decay is.
+// recurrence over a chunk of C = 16 tokens, with W(a, b)[i] = prod_{a <= q < b} w_q[i]:
+//     S_{t-1}  = S_in * W(0, t)  +  sum_{s<t} W(s+1, t) k_s v_s^T
+//     y_t[j]   = sum_i r_t[i] W(0, t)[i] S_in[i][j]                               (inter)
+//              + sum_{s<t} (sum_i r_t[i] k_s[i] W(s+1, t)[i]) v_s[j]               (intra)
+//              + (sum_i r_t[i] u[i] k_t[i]) v_t[j]                                 (bonus)
+//     S_out    = S_in * W(0, C) + sum_s W(s+1, C) k_s v_s^T
+// Only products of decay factors in (0, 1] appear (no logarithms, no divisions), so nothing can
+// overflow however strong the decay is, and an underflow is the correct limit.
 // Three launches per layer, the first and last parallel over (head, chunk):
-//   wkv_chunk_state_kernel   dS_c = sum_s exp(LP_C - LP_{s+1}) k_s v_s^T and P_c = prod_q w_q (plain product)
+//   wkv_chunk_state_kernel   dS_c = sum_s W(s+1, C) k_s v_s^T and P_c = W(0, C)
 //   wkv_chunk_scan_kernel    S_start[c] = state entering chunk c (T/16 multiply-adds per entry;
 //                            overwrites dS_c in place), final state -> state_out
 //   wkv_chunk_out_kernel     y of the chunk from S_start[c] (+ per-head norm, ln_x, gate fused)
@@ -30,7 +31,6 @@ namespace {
 
 constexpr int CS = 64;            // head size
 constexpr int CC = 16;            // tokens per chunk
-constexpr int KP = CS + 1;        // padded row stride where a warp reads one column of 16 different rows
 
 __device__ __forceinline__ void cpa16(void * smem, const void * gmem) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t) __cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
@@ -39,63 +39,44 @@ __device__ __forceinline__ void cpa_commit_wait() {
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
+__device__ __forceinline__ float4 mul4(float4 a, float4 b) { return make_float4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w); }
+__device__ __forceinline__ float4 & f4(float * p) { return *reinterpret_cast<float4 *>(p); }
+__device__ __forceinline__ const float4 & f4(const float * p) { return *reinterpret_cast<const float4 *>(p); }
 
-// log of one decay factor; w = 0 (exp(-exp(x)) underflowed) behaves as a factor of 1e-38
-__device__ __forceinline__ float log_decay(float w) { return logf(fmaxf(w, 1.0e-38f)); }
-
-// decay factors of token t0 + t for this thread's 4 channels (1 past the end of the sequence)
+// Thread layout of the loads: thread = (token t = tid / 16 of the chunk, channels c4 .. c4 + 3 of the head).
+// decay factors of token t0 + t (1 past the end of the sequence: no decay, and k = v = r = 0 there)
 __device__ __forceinline__ float4 load_decay4(const WkvArgs & a, int h, int t0) {
     const int t = threadIdx.x >> 4, c4 = (threadIdx.x & 15) * 4;
     if (t0 + t >= a.R) return make_float4(1.0f, 1.0f, 1.0f, 1.0f);
-    if (a.w) return *reinterpret_cast<const float4 *>(a.w + (size_t) (t0 + t) * a.D + h * CS + c4);
+    if (a.w) return f4(a.w + (size_t) (t0 + t) * a.D + h * CS + c4);
     if (a.per_head_scalar) { const float v = a.decay[h]; return make_float4(v, v, v, v); }
-    return *reinterpret_cast<const float4 *>(a.decay + h * CS + c4);
+    return f4(a.decay + h * CS + c4);
 }
-// lw[t][i] <- log w of token t0 + t, one float4 per thread
-__device__ __forceinline__ void store_log_decay(const float4 w, float (*lw)[CS]) {
-    const int t = threadIdx.x >> 4, c4 = (threadIdx.x & 15) * 4;
-    *reinterpret_cast<float4 *>(&lw[t][c4]) = make_float4(log_decay(w.x), log_decay(w.y), log_decay(w.z), log_decay(w.w));
-}
-
 __device__ __forceinline__ float4 load_row4(const float * p, const WkvArgs & a, int h, int t0) {
     const int t = threadIdx.x >> 4, c4 = (threadIdx.x & 15) * 4;
     if (t0 + t >= a.R) return make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    return *reinterpret_cast<const float4 *>(p + (size_t) (t0 + t) * a.D + h * CS + c4);
+    return f4(p + (size_t) (t0 + t) * a.D + h * CS + c4);
 }
 
 // ---- 1: chunk-local state increment -------------------------------------------------------------
 __global__ void __launch_bounds__(256) wkv_chunk_state_kernel(const __grid_constant__ WkvArgs a, float * __restrict__ ds, float * __restrict__ pc, int nchunks) {
-    __shared__ __align__(16) float lw[CC][CS];
-    __shared__ __align__(16) float lp[CC + 1][CS];
+    __shared__ __align__(16) float sw[CC][CS];
     __shared__ __align__(16) float kd[CC][CS];
     __shared__ __align__(16) float sv[CC][CS];
     pdl_trigger();
     const int tid = threadIdx.x, c = blockIdx.x, h = blockIdx.y, t0 = c * CC;
     pdl_wait();
     const int t = tid >> 4, c4 = (tid & 15) * 4;
-    {
-        const float4 w4 = load_decay4(a, h, t0);
-        store_log_decay(w4, lw);
-        *reinterpret_cast<float4 *>(&kd[t][c4]) = w4;      // raw factors for the chunk product (kd proper is built below)
-    }
+    const float4 w4 = load_decay4(a, h, t0);
+    f4(&sw[t][c4]) = w4;
     const float4 k4 = load_row4(a.k, a, h, t0);
-    *reinterpret_cast<float4 *>(&sv[t][c4]) = load_row4(a.v, a, h, t0);
-    __syncthreads();
-    if (tid < CS) {
-        // LP by sums of logs (used in ratios inside the chunk only); the factor that carries the state
-        // from chunk to chunk is the plain product, so no log / exp error compounds along the sequence
-        float acc = 0.0f, prod = 1.0f;
-        lp[0][tid] = 0.0f;
-#pragma unroll
-        for (int q = 0; q < CC; q++) { acc += lw[q][tid]; lp[q + 1][tid] = acc; prod *= kd[q][tid]; }
-        pc[((size_t) h * nchunks + c) * CS + tid] = prod;
-    }
+    f4(&sv[t][c4]) = load_row4(a.v, a, h, t0);
     __syncthreads();
     {
-        const float4 le = *reinterpret_cast<const float4 *>(&lp[CC][c4]);
-        const float4 ls = *reinterpret_cast<const float4 *>(&lp[t + 1][c4]);
-        *reinterpret_cast<float4 *>(&kd[t][c4]) = make_float4(k4.x * __expf(le.x - ls.x), k4.y * __expf(le.y - ls.y),
-                                                               k4.z * __expf(le.z - ls.z), k4.w * __expf(le.w - ls.w));
+        float4 sfx = make_float4(1.0f, 1.0f, 1.0f, 1.0f);       // W(t+1, C)
+        for (int q = CC - 1; q > t; q--) sfx = mul4(sfx, f4(&sw[q][c4]));
+        f4(&kd[t][c4]) = mul4(k4, sfx);
+        if (t == 0) f4(pc + ((size_t) h * nchunks + c) * CS + c4) = mul4(sfx, w4);
     }
     __syncthreads();
     // dS[i][j] = sum_s kd[s][i] v[s][j]; thread = 4 x 4 tile
@@ -103,8 +84,8 @@ __global__ void __launch_bounds__(256) wkv_chunk_state_kernel(const __grid_const
     float acc[4][4] = {};
 #pragma unroll
     for (int s = 0; s < CC; s++) {
-        const float4 ka = *reinterpret_cast<const float4 *>(&kd[s][i0]);
-        const float4 vb = *reinterpret_cast<const float4 *>(&sv[s][j0]);
+        const float4 ka = f4(&kd[s][i0]);
+        const float4 vb = f4(&sv[s][j0]);
         const float kk[4] = {ka.x, ka.y, ka.z, ka.w}, vv[4] = {vb.x, vb.y, vb.z, vb.w};
 #pragma unroll
         for (int ii = 0; ii < 4; ii++)
@@ -114,46 +95,55 @@ __global__ void __launch_bounds__(256) wkv_chunk_state_kernel(const __grid_const
     float * out = ds + ((size_t) h * nchunks + c) * CS * CS;
 #pragma unroll
     for (int ii = 0; ii < 4; ii++)
-        *reinterpret_cast<float4 *>(out + (size_t) (i0 + ii) * CS + j0) = make_float4(acc[ii][0], acc[ii][1], acc[ii][2], acc[ii][3]);
+        f4(out + (size_t) (i0 + ii) * CS + j0) = make_float4(acc[ii][0], acc[ii][1], acc[ii][2], acc[ii][3]);
 }
 
 // ---- 2: state entering every chunk ----------------------------------------------------------------
-// grid (H, 4): CTA = 16 key rows of a head, thread = one float4 of the state.
+// grid (H, 4): CTA = 16 key rows of a head, thread = one float4 of the state.  The loads of the
+// next 8 chunks are in flight while the current 8 are chained.
 __global__ void __launch_bounds__(256) wkv_chunk_scan_kernel(const __grid_constant__ WkvArgs a, float * __restrict__ ds, const float * __restrict__ pc, int nchunks) {
     pdl_trigger();
     const int tid = threadIdx.x, h = blockIdx.x;
     const int i = blockIdx.y * 16 + (tid >> 4), j0 = (tid & 15) * 4;
     const size_t so = (size_t) h * CS * CS + (size_t) i * CS + j0;
-    float4 cur = *reinterpret_cast<const float4 *>(a.state_in + so);
+    float4 cur = f4(a.state_in + so);
     pdl_wait();
     float4 * p = reinterpret_cast<float4 *>(ds + (size_t) h * nchunks * CS * CS + (size_t) i * CS + j0);
     const float * pp = pc + (size_t) h * nchunks * CS + i;
     constexpr int U = 8;
-    for (int c0 = 0; c0 < nchunks; c0 += U) {
-        float4 d[U]; float f[U];
+    float4 d[U], dn[U]; float f[U], fn[U];
+    auto fetch = [&](int c0, float4 (&dd)[U], float (&ff)[U]) {
 #pragma unroll
-        for (int q = 0; q < U; q++)
-            if (c0 + q < nchunks) { d[q] = p[(size_t) (c0 + q) * (CS * CS / 4)]; f[q] = pp[(size_t) (c0 + q) * CS]; }
+        for (int q = 0; q < U; q++) {
+            const int c = min(c0 + q, nchunks - 1);          // clamped: the surplus loads are ignored
+            dd[q] = __ldcg(p + (size_t) c * (CS * CS / 4)); ff[q] = __ldcg(pp + (size_t) c * CS);
+        }
+    };
+    fetch(0, d, f);
+    for (int c0 = 0; c0 < nchunks; c0 += U) {
+        if (c0 + U < nchunks) fetch(c0 + U, dn, fn);
 #pragma unroll
         for (int q = 0; q < U; q++)
             if (c0 + q < nchunks) {
                 p[(size_t) (c0 + q) * (CS * CS / 4)] = cur;
                 cur = make_float4(fmaf(cur.x, f[q], d[q].x), fmaf(cur.y, f[q], d[q].y), fmaf(cur.z, f[q], d[q].z), fmaf(cur.w, f[q], d[q].w));
             }
+#pragma unroll
+        for (int q = 0; q < U; q++) { d[q] = dn[q]; f[q] = fn[q]; }
     }
-    *reinterpret_cast<float4 *>(a.state_out + so) = cur;
+    f4(a.state_out + so) = cur;
 }
 
 // ---- 3: outputs of a chunk ----------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) wkv_chunk_out_kernel(const __grid_constant__ WkvArgs a, const float * __restrict__ ds, int nchunks) {
     __shared__ __align__(16) float sst[CS * CS];          // S_start of the chunk; later the 4 partial y tiles, then y
-    __shared__ __align__(16) float lw[CC][CS];            // log w, then rqT[i][t] = r_t[i] exp(LP_t[i])
-    __shared__ float lp[CC + 1][KP];
-    __shared__ float sr[CC][CS];
-    __shared__ float sk[CC][KP];
+    __shared__ __align__(16) float sw[CC][CS];
+    __shared__ __align__(16) float sr[CC][CS];
+    __shared__ __align__(16) float sk[CC][CS];
     __shared__ __align__(16) float sv[CC][CS];
+    __shared__ __align__(16) float rq[CC][CS];            // r_t[i] W(0, t)[i]
     __shared__ __align__(16) float sa[CC][CC];            // sa[s][t] = A[t][s]
-    __shared__ float su[CS];
+    __shared__ __align__(16) float su[CS];
     pdl_trigger();
     const int tid = threadIdx.x, c = blockIdx.x, h = blockIdx.y, t0 = c * CC;
     const int t = tid >> 4, c4 = (tid & 15) * 4;
@@ -164,61 +154,78 @@ __global__ void __launch_bounds__(256) wkv_chunk_out_kernel(const __grid_constan
 #pragma unroll
         for (int q = 0; q < 4; q++) cpa16(sst + (q * 256 + tid) * 4, src + (q * 256 + tid) * 4);
     }
-    store_log_decay(load_decay4(a, h, t0), lw);
-    {
-        const float4 r4 = load_row4(a.r, a, h, t0), k4 = load_row4(a.k, a, h, t0);
-        sr[t][c4] = r4.x; sr[t][c4 + 1] = r4.y; sr[t][c4 + 2] = r4.z; sr[t][c4 + 3] = r4.w;
-        sk[t][c4] = k4.x; sk[t][c4 + 1] = k4.y; sk[t][c4 + 2] = k4.z; sk[t][c4 + 3] = k4.w;
-        *reinterpret_cast<float4 *>(&sv[t][c4]) = load_row4(a.v, a, h, t0);
-    }
+    const float4 r4 = load_row4(a.r, a, h, t0);
+    f4(&sw[t][c4]) = load_decay4(a, h, t0);
+    f4(&sr[t][c4]) = r4;
+    f4(&sk[t][c4]) = load_row4(a.k, a, h, t0);
+    f4(&sv[t][c4]) = load_row4(a.v, a, h, t0);
     __syncthreads();
-    if (tid < CS) {
-        float acc = 0.0f;
-        lp[0][tid] = 0.0f;
+    // rq[t][i] = r_t[i] W(0, t)[i]
+    {
+        float4 pre = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+        for (int q = 0; q < t; q++) pre = mul4(pre, f4(&sw[q][c4]));
+        f4(&rq[t][c4]) = mul4(r4, pre);
+    }
+    // A[.][s] for s = tid / 16 over this thread's 4 keys: g = k_s W(s+1, t) grows token by token
+    {
+        const int s = t;                                   // same thread layout: (s, 4 keys)
+        const int smin = (tid >> 5) * 2;                   // smallest s of the warp
+        float4 g = f4(&sk[s][c4]);
+        float acc[CC];
 #pragma unroll
-        for (int q = 0; q < CC; q++) { acc += lw[q][tid]; lp[q + 1][tid] = acc; }
-    }
-    __syncthreads();
-    // A[t][s]: thread (t, s); rqT (into lw's storage: lw is dead after the prefix sums)
-    {
-        const int s = tid & 15;
-        float acc = 0.0f;
-        if (s < t) {
-#pragma unroll 8
-            for (int i = 0; i < CS; i++) acc = fmaf(sr[t][i] * sk[s][i], __expf(lp[t][i] - lp[s + 1][i]), acc);
-        } else if (s == t) {
-#pragma unroll 8
-            for (int i = 0; i < CS; i++) acc = fmaf(sr[t][i] * sk[t][i], su[i], acc);
+        for (int q = 0; q < CC; q++) acc[q] = 0.0f;
+        {
+            const float4 uu = f4(&su[c4]);
+            const float bonus = fmaf(r4.x * g.x, uu.x, fmaf(r4.y * g.y, uu.y, fmaf(r4.z * g.z, uu.z, r4.w * g.w * uu.w)));
+#pragma unroll
+            for (int q = 0; q < CC; q++) if (q == s) acc[q] = bonus;
         }
-        sa[s][t] = acc;
-    }
-    float (*rqT)[CC] = reinterpret_cast<float (*)[CC]>(&lw[0][0]);     // [CS][CC]
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-        const int e = q * 256 + tid, i = e >> 4, tt = e & 15;
-        rqT[i][tt] = sr[tt][i] * __expf(lp[tt][i]);
+        for (int q = 1; q < CC; q++) {
+            if (q > smin) {                                // warp-uniform
+                const float4 rr = f4(&sr[q][c4]);
+                const float dot = fmaf(rr.x, g.x, fmaf(rr.y, g.y, fmaf(rr.z, g.z, rr.w * g.w)));
+                if (q > s) { acc[q] = dot; g = mul4(g, f4(&sw[q][c4])); }
+            }
+        }
+        // sum over the 16 lanes that share s; lane l of the group ends up with the total of acc[l]
+#pragma unroll
+        for (int off = 8; off > 0; off >>= 1) {
+            const bool up = (tid & off) != 0;
+#pragma unroll
+            for (int q = 0; q < off; q++) {
+                const float send = up ? acc[q] : acc[q + off];
+                const float keep = up ? acc[q + off] : acc[q];
+                acc[q] = keep + __shfl_xor_sync(FULL, send, off);
+            }
+        }
+        sa[s][tid & 15] = acc[0];
     }
     cpa_commit_wait();
     __syncthreads();
     // y[t][j]: thread = 4 tokens x 4 columns, K split over 4 thread groups (16 keys + 4 intra tokens each)
     const int g = tid >> 6, tq = ((tid >> 4) & 3) * 4, j0 = (tid & 15) * 4;
     float acc[4][4] = {};
-#pragma unroll 4
-    for (int ii = 0; ii < 16; ii++) {
-        const int i = g * 16 + ii;
-        const float4 ra = *reinterpret_cast<const float4 *>(&rqT[i][tq]);
-        const float4 sb = *reinterpret_cast<const float4 *>(&sst[i * CS + j0]);
-        const float rr[4] = {ra.x, ra.y, ra.z, ra.w}, ss[4] = {sb.x, sb.y, sb.z, sb.w};
 #pragma unroll
-        for (int x = 0; x < 4; x++)
+    for (int ii = 0; ii < 4; ii++) {
+        const int i = g * 16 + ii * 4;
+        float ra[4][4], sb[4][4];
 #pragma unroll
-            for (int y = 0; y < 4; y++) acc[x][y] = fmaf(rr[x], ss[y], acc[x][y]);
+        for (int x = 0; x < 4; x++) { const float4 v = f4(&rq[tq + x][i]); ra[x][0] = v.x; ra[x][1] = v.y; ra[x][2] = v.z; ra[x][3] = v.w; }
+#pragma unroll
+        for (int z = 0; z < 4; z++) { const float4 v = f4(&sst[(i + z) * CS + j0]); sb[z][0] = v.x; sb[z][1] = v.y; sb[z][2] = v.z; sb[z][3] = v.w; }
+#pragma unroll
+        for (int z = 0; z < 4; z++)
+#pragma unroll
+            for (int x = 0; x < 4; x++)
+#pragma unroll
+                for (int y = 0; y < 4; y++) acc[x][y] = fmaf(ra[x][z], sb[z][y], acc[x][y]);
     }
 #pragma unroll
     for (int ii = 0; ii < 4; ii++) {
         const int s = g * 4 + ii;
-        const float4 aa = *reinterpret_cast<const float4 *>(&sa[s][tq]);
-        const float4 vb = *reinterpret_cast<const float4 *>(&sv[s][j0]);
+        const float4 aa = f4(&sa[s][tq]);
+        const float4 vb = f4(&sv[s][j0]);
         const float av[4] = {aa.x, aa.y, aa.z, aa.w}, vv[4] = {vb.x, vb.y, vb.z, vb.w};
 #pragma unroll
         for (int x = 0; x < 4; x++)
@@ -228,7 +235,7 @@ __global__ void __launch_bounds__(256) wkv_chunk_out_kernel(const __grid_constan
     __syncthreads();                                       // every group is done reading S_start
 #pragma unroll
     for (int x = 0; x < 4; x++)
-        *reinterpret_cast<float4 *>(&sst[(g * CC + tq + x) * CS + j0]) = make_float4(acc[x][0], acc[x][1], acc[x][2], acc[x][3]);
+        f4(&sst[(g * CC + tq + x) * CS + j0]) = make_float4(acc[x][0], acc[x][1], acc[x][2], acc[x][3]);
     __syncthreads();
     // thread (t, 4 columns): total, per-head norm over the 16 threads of a token, ln_x, gate
     float y[4];
