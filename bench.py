@@ -405,10 +405,59 @@ def run_prefill(args):
     e2e = (time.perf_counter() - t0) / args.steps
     out = None
     if d.rank == 0:
+        # algorithmic FLOPs of one pass: 2*T*(every matrix element the sequence multiplies) + the head for the last token
+        sh = synth.SHAPES[shape]
+        D, F, L, V = sh.n_embed, sh.ffn, sh.n_layer, sh.n_vocab
+        per_tok = (5 * D * D + 2 * D * F + D * D + 2 * 5 * sh.mix_lora * D + 2 * sh.decay_lora * D) if sh.arch == 6 else (4 * D * D + 2 * D * F + (D * D if sh.arch != 7 else 0))
+        flops = 2.0 * T * per_tok * L + 2.0 * D * V
+        _, tf_peak, which = peaks()
+        # dominant kernel: the ffn-key GEMM (F x D weights, T rows), timed live on the launching stream with CUDA events
+        roof = {"bound": "tensor", "achieved": None, "peak": tf_peak, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                "peak_source": which + " (MEASURED_PEAKS.json dense bf16, sustained)", "whole_pass_tflops": flops / (ms_max * 1e-3) / 1e12}
+        try:
+            from oracle import rwkv_oracle as O          # only to produce valid ggml blocks for a synthetic matrix
+            rngw = np.random.default_rng(0)
+            w = (rngw.random((256, D), dtype=np.float32) * 2 - 1) / np.float32(np.sqrt(D))
+            raw1 = O.quantize_ref(8, w.reshape(-1))
+            raw = np.ascontiguousarray(np.tile(raw1, (F + 255) // 256)[: (raw1.size // 256) * F])
+            L_ = lib.library
+            L_.rwkv_b200_matrix_create.restype = ctypes.c_void_p
+            L_.rwkv_b200_matrix_create.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_size_t]
+            mh = L_.rwkv_b200_matrix_create(8, raw.ctypes.data, F, D, 4)
+            msl = ctypes.c_double(0)
+            if mh and L_.rwkv_b200_matrix_bench_tc(ctypes.c_void_p(mh), T, 50, ctypes.byref(msl)):
+                ach = 2.0 * F * D * T / (msl.value * 1e-3) / 1e12
+                roof.update({"achieved": ach, "frac": ach / tf_peak, "us_per_launch": msl.value * 1e3,
+                             "kernel": f"gemm_tc_kernel<Q5_1> ffn key {F}x{D} x {T} rows (tcgen05.mma kind::f16, FP32 accumulate in TMEM); 50 launches rotating over 4 weight copies"})
+            if mh:
+                L_.rwkv_b200_matrix_free(ctypes.c_void_p(mh))
+        except Exception as ex:                          # the roofline leg never fails the bench line
+            roof["error"] = str(ex)
         out = {"metric": f"prefill tokens/s ({shape} Q5_1, T={T})", "value": d.world * T / (ms_max * 1e-3), "unit": "tokens/s", "n_gpus": d.world,
                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-               "dtype": "see DESIGN.md (sequence mode)", "data": "synthetic", "config": {"workload": f"{shape} FP16-to-Q5_1 rwkv_eval_sequence T={T}"},
-               "clocks": clocks, "e2e": {"value": d.world * T / e2e, "unit": "tokens/s", "h2d_bytes_per_step": T * 4, "d2h_bytes_per_step": (model.state_len + model.n_vocab) * 4}}
+               "dtype": "f16 operands (weights dequantised in-kernel), f32 accumulate (tcgen05 / TMEM); f32 recurrence", "data": "synthetic (random-init weights in ggmf format, uniform random token ids)",
+               "config": {"workload": f"{shape} FP16-to-Q5_1 rwkv_eval_sequence T={T} (BASELINE.json configs[2])", "algorithmic_flops_per_step": flops,
+                          "l2": "weights 1.26 GB per pass > L2"},
+               "clocks": clocks, "e2e": {"value": d.world * T / e2e, "unit": "tokens/s", "h2d_bytes_per_step": T * 4, "d2h_bytes_per_step": (model.state_len + model.n_vocab) * 4,
+                                         "api": "rwkv_eval_sequence(ctx, tokens, T, NULL, state_out, logits_out) with host buffers"},
+               "gpu_launches": (12 * L + 3) * args.steps if sh.arch == 6 else None,      # v6 sequence pass: 12 launches per layer + embed, ln_out, head (profiles/ launch list)
+               "roofline": roof}
+        if not args.no_cpu:
+            try:
+                Lr = reference_lib()
+                Lr.lib.rwkv_set_print_errors(None, False)
+                n_thr = min(host_cores(), 32)
+                ctx = Lr.load(path, n_thr, 0)
+                Ts = 64                                   # bounded sample of the same workload: a 64-token sequence
+                ctx.eval_sequence([int(t) for t in toks[:8]], None)
+                t0 = time.perf_counter()
+                ctx.eval_sequence([int(t) for t in toks[:Ts]], None)
+                dt = time.perf_counter() - t0
+                ctx.free()
+                out["cpu_baseline"] = {"value": Ts / dt, "unit": "tokens/s", "cores": n_thr, "kind": "reference",
+                                       "sample": f"one rwkv_eval_sequence of {Ts} tokens of the unmodified reference CPU build on the same model file; " + Lr.system_info()}
+            except Exception as ex:
+                out["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": 0, "kind": "reference", "sample": "not run: " + str(ex)}
     model.free(); d.close()
     return out
 

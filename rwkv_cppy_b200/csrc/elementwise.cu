@@ -106,6 +106,101 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
     }
 }
 
+// Sequence rows whose consumers are all tensor-core GEMMs (FP16 outputs only: the tolerance-mode path).
+// CTA = 8 consecutive rows, one warp per row with the row in registers (two-pass statistics in FP32, no
+// block-wide synchronisation), plus a ninth warp that normalises the row before the tile (or fetches the
+// shift state for the first row of the sequence).  The normalised rows meet in shared memory, so every
+// row is normalised once instead of twice; outputs leave as 8-byte FP16 quads.  N4 = D / 128.
+template <int N4>
+__global__ void __launch_bounds__(288, 2) ln_mix_seq_kernel(const __grid_constant__ LnMixArgs a) {
+    extern __shared__ __align__(16) float sm_rows[];          // [9][D]
+    pdl_trigger();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, D = a.D;
+    const int r0 = blockIdx.x * 8;
+    const int r = warp < 8 ? r0 + warp : r0 - 1;              // warp 8: the row before the tile
+    float * mine = sm_rows + (size_t) warp * D;
+    pdl_wait();
+    float4 x[N4];
+    if (r >= 0 && r < a.R) {
+#pragma unroll
+        for (int j = 0; j < N4; j++) x[j] = *reinterpret_cast<const float4 *>(a.x + (size_t) r * D + (j * 32 + lane) * 4);
+        float s = 0.0f;
+#pragma unroll
+        for (int j = 0; j < N4; j++) s += (x[j].x + x[j].y) + (x[j].z + x[j].w);
+        s = warp_sum(s);
+        const float mean = s / (float) D;
+        float s2 = 0.0f;
+#pragma unroll
+        for (int j = 0; j < N4; j++) {
+            x[j].x -= mean; x[j].y -= mean; x[j].z -= mean; x[j].w -= mean;
+            s2 += (x[j].x * x[j].x + x[j].y * x[j].y) + (x[j].z * x[j].z + x[j].w * x[j].w);
+        }
+        s2 = warp_sum(s2);
+        const float scale = 1.0f / sqrtf(s2 / (float) D + 1e-5f);
+#pragma unroll
+        for (int j = 0; j < N4; j++) {
+            const int e = (j * 32 + lane) * 4;
+            const float4 w = *reinterpret_cast<const float4 *>(a.ln_w + e), b = *reinterpret_cast<const float4 *>(a.ln_b + e);
+            x[j].x = __fadd_rn(__fmul_rn(__fmul_rn(x[j].x, scale), w.x), b.x); x[j].y = __fadd_rn(__fmul_rn(__fmul_rn(x[j].y, scale), w.y), b.y);
+            x[j].z = __fadd_rn(__fmul_rn(__fmul_rn(x[j].z, scale), w.z), b.z); x[j].w = __fadd_rn(__fmul_rn(__fmul_rn(x[j].w, scale), w.w), b.w);
+            *reinterpret_cast<float4 *>(mine + e) = x[j];
+        }
+    } else if (r < 0) {                                       // first tile: the token-shift source is the input state
+#pragma unroll
+        for (int j = 0; j < N4; j++) {
+            const int e = (j * 32 + lane) * 4;
+            *reinterpret_cast<float4 *>(mine + e) = *reinterpret_cast<const float4 *>(a.state_in + e);
+        }
+    }
+    __syncthreads();
+    if (warp == 8 || r >= a.R) return;
+    const float * prev = sm_rows + (size_t) (warp == 0 ? 8 : warp - 1) * D;
+#pragma unroll
+    for (int j = 0; j < N4; j++) {
+        const int e = (j * 32 + lane) * 4;
+        const float4 x0 = x[j], xp = *reinterpret_cast<const float4 *>(prev + e);
+        const float4 sx = make_float4(__fsub_rn(xp.x, x0.x), __fsub_rn(xp.y, x0.y), __fsub_rn(xp.z, x0.z), __fsub_rn(xp.w, x0.w));
+        if (r == a.R - 1) *reinterpret_cast<float4 *>(a.state_out + e) = x0;
+        if (a.x0) *reinterpret_cast<float4 *>(a.x0 + (size_t) r * D + e) = x0;
+        if (a.sx) *reinterpret_cast<float4 *>(a.sx + (size_t) r * D + e) = sx;
+#pragma unroll 1
+        for (int o = 0; o < a.n_out; o++) {
+            const float4 mu = *reinterpret_cast<const float4 *>(a.mu[o] + e);
+            float4 v;
+            if (a.kind == MIX_LERP) {
+                v.x = __fadd_rn(__fmul_rn(x0.x, mu.x), __fsub_rn(xp.x, __fmul_rn(xp.x, mu.x))); v.y = __fadd_rn(__fmul_rn(x0.y, mu.y), __fsub_rn(xp.y, __fmul_rn(xp.y, mu.y)));
+                v.z = __fadd_rn(__fmul_rn(x0.z, mu.z), __fsub_rn(xp.z, __fmul_rn(xp.z, mu.z))); v.w = __fadd_rn(__fmul_rn(x0.w, mu.w), __fsub_rn(xp.w, __fmul_rn(xp.w, mu.w)));
+            } else {
+                v.x = __fadd_rn(__fmul_rn(sx.x, mu.x), x0.x); v.y = __fadd_rn(__fmul_rn(sx.y, mu.y), x0.y);
+                v.z = __fadd_rn(__fmul_rn(sx.z, mu.z), x0.z); v.w = __fadd_rn(__fmul_rn(sx.w, mu.w), x0.w);
+            }
+            const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+            uint2 pk; pk.x = *reinterpret_cast<const uint32_t *>(&h0); pk.y = *reinterpret_cast<const uint32_t *>(&h1);
+            *reinterpret_cast<uint2 *>(a.out[o].h + (size_t) r * a.out[o].K + e) = pk;
+        }
+    }
+}
+
+template <int N4>
+static cudaError_t launch_ln_mix_seq_n(const LnMixArgs & a, cudaStream_t st) {
+    const size_t smem = (size_t) 9 * a.D * sizeof(float);
+    static bool attr_set = false;                             // per template instance; > 48 KB needs the opt-in
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(ln_mix_seq_kernel<N4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 9 * N4 * 128 * (int) sizeof(float));
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    return launch_pdl(ln_mix_seq_kernel<N4>, dim3((a.R + 7) / 8), dim3(288), smem, st, a);
+}
+
+static bool ln_mix_seq_ok(const LnMixArgs & a) {
+    static const bool off = [] { const char * e = getenv("RWKV_B200_NO_LN_SEQ"); return e && e[0] == '1'; }();
+    if (off || a.batch || a.R < 16 || a.D % 128 != 0 || a.D > 2560 || a.n_out < 1) return false;
+    for (int o = 0; o < a.n_out; o++)
+        if (a.out[o].h == nullptr || a.out[o].f != nullptr || a.out[o].q != nullptr || a.out[o].K % 4 != 0) return false;
+    return true;
+}
+
 template <int ITEMS, int NT>
 static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_t st) {
     switch (a.n_out) {
@@ -120,6 +215,18 @@ static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_
 
 cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
     if (a.D > 8192) return cudaErrorInvalidValue;
+    if (ln_mix_seq_ok(a)) {
+        switch (a.D / 128) {
+            case 2:  return launch_ln_mix_seq_n<2>(a, st);
+            case 4:  return launch_ln_mix_seq_n<4>(a, st);
+            case 6:  return launch_ln_mix_seq_n<6>(a, st);
+            case 8:  return launch_ln_mix_seq_n<8>(a, st);
+            case 12: return launch_ln_mix_seq_n<12>(a, st);
+            case 16: return launch_ln_mix_seq_n<16>(a, st);
+            case 20: return launch_ln_mix_seq_n<20>(a, st);
+            default: break;                                   // other widths: the general kernel below
+        }
+    }
     if (a.D <= LN_SMALL_D) {
         // Rows up to 2048 wide: 256 threads, element it*256 + tid.  The decode mat-vecs rebuild these
         // rows in their prologue (gemv_async.cu) with the same thread shape, hence the same sums.

@@ -373,9 +373,16 @@ struct Pass {
                              layer != 0 ? produced(ws.mix[3], {&l.att_value, &l.v1}) : produced(ws.mix[3], {&l.att_value}),
                              produced(ws.mix[4], {&l.a1}), produced(ws.mix[5], {&l.g1})};
         ln_mix(layer, true, MIX_SX, 6, l.att_mu, false, outs);               // mix = xr, xw, xk, xv, xa, xg
+        // low-rank pairs (never quantised).  Wide row counts chain the two stages on the tensor cores: the first
+        // stage then also leaves an FP16 copy of its rows for the second (no q8 form: the second stage is FP16 / FP32).
+        auto lora_tc = [&](const DevMat & W1, const DevMat & W2) {
+            return ws.lora[0].h != nullptr && W1.M % 8 == 0 && gemm_tc_supported(W1, R) && gemm_tc_supported(W2, R);
+        };
+        const DevMat * second[4] = {&l.w2, &l.a2, &l.g2, &l.v2};
         auto lora_in = [&](int slot, const DevMat & W, int epi) {
             GemvJob j = job(W, ws.mix[slot == 0 ? 1 : slot == 1 ? 4 : slot == 2 ? 5 : 3], nullptr, 0, epi);
-            j.out = ws.lora[slot].f; j.ldo = (int) W.M;                       // low-rank mats are never quantised: FP32 rows suffice
+            if (lora_tc(W, *second[slot])) { j.out_act.f = ws.lora[slot].f; j.out_act.h = ws.lora[slot].h; j.out_act.K = (int) W.M; }
+            else { j.out = ws.lora[slot].f; j.ldo = (int) W.M; tc_written.erase(ws.lora[slot].f); }
             return j;
         };
         std::vector<GemvJob> jobs = {job(l.att_receptance, ws.mix[0], ws.r, (int) D, EPI_STORE), job(l.att_key, ws.mix[2], ws.k, (int) D, EPI_STORE),
@@ -385,6 +392,7 @@ struct Pass {
         gemv(jobs, R);
         auto lora_out = [&](int slot, const DevMat & W, float * out, int epi, const float * vec) {
             Act x; x.f = ws.lora[slot].f; x.K = (int) W.K;
+            if (tc_written.count(ws.lora[slot].f)) x.h = ws.lora[slot].h;     // first stage ran on the tensor cores and left FP16 rows
             GemvJob j = job(W, x, out, (int) D, epi); j.vec = vec;
             return j;
         };

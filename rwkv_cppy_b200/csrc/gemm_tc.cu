@@ -111,11 +111,28 @@ __device__ __forceinline__ void epilogue_tile(const GtJob & J, uint32_t tcol, in
         tmem_ld_wait();
         const int nv = T - t0 - c0;
         if (row_ok) {
+            // read-modify-write epilogues: all 16 operand loads go out before the first store (the compiler
+            // may not move a load of `out` above a store to `out`, which made this 16 dependent round trips)
+            constexpr bool RMW = (EPI == EPI_ADD_TO || EPI == EPI_MULADD_TO);
+            constexpr bool AUX = (EPI == EPI_MULADD_TO || EPI == EPI_ADD_AUX);
+            float po[16], pa[16];
+            if (RMW) {
+#pragma unroll
+                for (int i = 0; i < 16; i++) po[i] = i < nv ? out[(size_t) (t0 + c0 + i) * ldo + m] : 0.0f;
+            }
+            if (AUX) {
+#pragma unroll
+                for (int i = 0; i < 16; i++) pa[i] = i < nv ? J.aux[(size_t) (t0 + c0 + i) * J.ld_aux + m] : 0.0f;
+            }
 #pragma unroll
             for (int i = 0; i < 16; i++) {
                 if (i < nv) {
                     const int t = t0 + c0 + i;
-                    const float y = apply_epilogue_c<EPI>(J, __uint_as_float(v[i]), t, m);
+                    float y = __uint_as_float(v[i]);
+                    if (EPI == EPI_ADD_TO)         y = __fadd_rn(po[i], y);
+                    else if (EPI == EPI_MULADD_TO) y = __fadd_rn(po[i], __fmul_rn(pa[i], y));
+                    else if (EPI == EPI_ADD_AUX)   y = __fadd_rn(pa[i], y);
+                    else                           y = apply_epilogue_c<EPI>(J, y, t, m);
                     if (out) out[(size_t) t * ldo + m] = y;
                     if (out_h) out_h[(size_t) t * ld_h + m] = __float2half_rn(y);
                 }
@@ -275,8 +292,9 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
                 const uint32_t qh = HB ? *reinterpret_cast<const uint32_t *>(cq + 2 * GT_BM * QB + e * 4) : 0u;
                 const uint8_t * dp = cq + 2 * GT_BM * (QB + HB) + e * DB;
                 const uint32_t dm = DB == 4 ? *reinterpret_cast<const uint32_t *>(dp) : (uint32_t) *reinterpret_cast<const uint16_t *>(dp);
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_qempty + 8 * qs);   // chunk is in registers: hand the slot back
+                // the slot goes back to the producer only once the loads have RETURNED: the arrive consumes the loaded words
+                const uint32_t dep = __reduce_or_sync(0xffffffffu, (q0.x ^ q0.w) | (q1.x ^ q1.w) | qh | dm);
+                if (lane == 0) mbar_arrive_after(bar_qempty + 8 * qs, dep);
                 uint4 h[4];
 #ifdef RB_ABL_NODQ
                 h[0] = q0; h[1] = q0; h[2] = make_uint4(qh, dm, qh, dm); h[3] = q1;
@@ -384,7 +402,9 @@ cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t
     for (int j = 0; j < n_jobs; j++) m_tiles_total += ((int) jobs[j].W.M + GT_BM - 1) / GT_BM;
     int BN = 64; double best = 1e300;
     const int cand[3] = {256, 128, 64}; const double cost[3] = {800.0, 520.0, 330.0};
+    static const int force_bn = [] { const char * e = getenv("RWKV_B200_TC_BN"); return e ? atoi(e) : 0; }();   // tests: pin the tile width
     for (int c = 0; c < 3; c++) {
+        if (force_bn && cand[c] != force_bn) continue;
         if (cand[c] > 64 && cand[c] / 2 >= T) continue;           // tile would be more than half empty
         const int tiles = m_tiles_total * ((T + cand[c] - 1) / cand[c]);
         const double t = (double) ((tiles + 147) / 148) * cost[c];

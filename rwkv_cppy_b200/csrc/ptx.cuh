@@ -21,6 +21,11 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
 }
+// arrive that may not be issued before `dep` is available: used to hand a shared-memory slot back after
+// reading it -- the loads must have RETURNED (not merely been issued) before the slot can be refilled
+__device__ __forceinline__ void mbar_arrive_after(uint32_t bar, uint32_t dep) {
+    asm volatile("{\n\t.reg .b32 t;\n\tmov.b32 t, %1;\n\tmbarrier.arrive.shared::cta.b64 _, [%0];\n\t}" :: "r"(bar), "r"(dep) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"

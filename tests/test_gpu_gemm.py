@@ -71,3 +71,21 @@ def test_gemm_tc_full_size(raw_lib, t):
     assert np.array_equal(y[1], -2.0 * w16[:, K - 1])
     assert np.all(y[2] == 0.0)
     dm.free()
+
+
+@pytest.mark.parametrize("t", [O.TYPE_Q4_0, O.TYPE_Q5_1], ids=["Q4_0", "Q5_1"])
+def test_gemm_tc_repeatable(raw_lib, t):
+    """Stress of the producer / dequantiser / MMA hand-offs: the same product many times over, every
+    repetition checked (a stale weight sub-tile shows up as a 32-row x tile-width block of wrong outputs)."""
+    M, K, T = 4096, 2048, 1024
+    rng = np.random.default_rng(3)
+    _, raw = make_matrix(rng, t, M, K)
+    dm = DevMatrix(raw_lib.lib, t, raw, M, K)
+    x = rng.standard_normal((T, K)).astype(np.float32)
+    ref = O.matmul_fp16(t, raw, M, K, x)
+    scale = float(np.abs(ref).max())
+    for rep in range(12):
+        y = mul_tc(dm, x)
+        bad = np.abs(y - ref) > 1e-3 * scale
+        assert not bad.any(), (rep, int(bad.sum()))
+    dm.free()
