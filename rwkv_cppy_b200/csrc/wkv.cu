@@ -371,13 +371,26 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
     const int stream = a.batch ? blockIdx.y : 0;
     const size_t soff = (size_t) stream * a.state_stride;
 
+    // The head states of the CTA are one contiguous run of hpb*S*S floats.  They move between global and
+    // shared memory as consecutive 16-byte pieces (fully coalesced: with 256 streams this kernel is the
+    // state traffic, 2 x 16 KB per head and step) and between shared memory and the owner's registers as
+    // float4 rows; the row stride S + 4 keeps both access patterns free of bank conflicts.
+    constexpr int RS = S + 4, Q = S / 4;
+    float * s_st = sm + 6 * nthr;
+    const int h0 = blockIdx.x * hpb, nh = min(hpb, a.H - h0);
+    const float * gin = a.state_in + soff + (size_t) h0 * S * S;
+    for (int f = tid; f < nh * S * Q; f += nthr)
+        cp_async16(s_st + (f / Q) * RS + (f % Q) * 4, gin + (size_t) f * 4);
+    cp_async_commit();
     float st[S];
     float kkc = 0, kac = 0, rkc = 0, lw = 0, lb = 0;
+    if (active) { kkc = a.k_k[e]; kac = a.k_a[e]; rkc = a.r_k[e]; lw = a.lnx_w[e]; lb = a.lnx_b[e]; }
+    cp_async_wait<0>();
+    __syncthreads();
     if (active) {
-        const float4 * p = reinterpret_cast<const float4 *>(a.state_in + soff + (size_t) h * S * S + (size_t) i * S);
+        const float4 * p = reinterpret_cast<const float4 *>(s_st + (size_t) tid * RS);
 #pragma unroll
-        for (int j = 0; j < S / 4; j++) { const float4 f = p[j]; st[4 * j] = f.x; st[4 * j + 1] = f.y; st[4 * j + 2] = f.z; st[4 * j + 3] = f.w; }
-        kkc = a.k_k[e]; kac = a.k_a[e]; rkc = a.r_k[e]; lw = a.lnx_w[e]; lb = a.lnx_b[e];
+        for (int j = 0; j < Q; j++) { const float4 f = p[j]; st[4 * j] = f.x; st[4 * j + 1] = f.y; st[4 * j + 2] = f.z; st[4 * j + 3] = f.w; }
     }
     pdl_wait();
     const int steps = a.batch ? 1 : a.R;
@@ -427,11 +440,16 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
         }
         act_store_block(a.y, row, e, active, o);
     }
+    __syncthreads();
     if (active) {
-        float4 * p = reinterpret_cast<float4 *>(a.state_out + soff + (size_t) h * S * S + (size_t) i * S);
+        float4 * p = reinterpret_cast<float4 *>(s_st + (size_t) tid * RS);
 #pragma unroll
-        for (int j = 0; j < S / 4; j++) p[j] = make_float4(st[4 * j], st[4 * j + 1], st[4 * j + 2], st[4 * j + 3]);
+        for (int j = 0; j < Q; j++) p[j] = make_float4(st[4 * j], st[4 * j + 1], st[4 * j + 2], st[4 * j + 3]);
     }
+    __syncthreads();
+    float * gout = a.state_out + soff + (size_t) h0 * S * S;
+    for (int f = tid; f < nh * S * Q; f += nthr)
+        *reinterpret_cast<float4 *>(gout + (size_t) f * 4) = *reinterpret_cast<const float4 *>(s_st + (f / Q) * RS + (f % Q) * 4);
 }
 
 template <int S>
@@ -439,7 +457,7 @@ static cudaError_t launch_wkv7_t(const WkvArgs & a, cudaStream_t st) {
     const int hpb = S >= 32 ? 1 : 32 / S;
     const int threads = ((hpb * S + 31) / 32) * 32;
     dim3 grid((a.H + hpb - 1) / hpb, a.batch ? a.R : 1);
-    return launch_pdl(wkv7_kernel<S>, grid, dim3(threads), 6 * threads * sizeof(float), st, a);
+    return launch_pdl(wkv7_kernel<S>, grid, dim3(threads), (6 * threads + hpb * S * (S + 4)) * sizeof(float), st, a);
 }
 
 cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st) {
