@@ -195,7 +195,7 @@ static cudaError_t launch_ln_mix_seq_n(const LnMixArgs & a, cudaStream_t st) {
 
 static bool ln_mix_seq_ok(const LnMixArgs & a) {
     static const bool off = [] { const char * e = getenv("RWKV_B200_NO_LN_SEQ"); return e && e[0] == '1'; }();
-    if (off || a.batch || a.R < 16 || a.D % 128 != 0 || a.D > 2560 || a.n_out < 1) return false;
+    if (off || a.batch || a.R < 16 || a.D % 128 != 0 || a.D > 2560 || a.n_out < 1) return false;   // (a warp per row starves the GPU when the rows are only a few hundred streams)
     for (int o = 0; o < a.n_out; o++)
         if (a.out[o].h == nullptr || a.out[o].f != nullptr || a.out[o].q != nullptr || a.out[o].K % 4 != 0) return false;
     return true;
