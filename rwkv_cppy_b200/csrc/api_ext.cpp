@@ -28,6 +28,7 @@ struct rwkv_b200_matrix {
     float * y = nullptr; size_t y_cap = 0;
     cudaStream_t stream = nullptr;
     size_t next = 0;
+    GemmScratch scratch;              // K-split partial tiles (tensor-core hook)
 };
 
 namespace {
@@ -395,6 +396,15 @@ size_t rwkv_b200_matrix_bytes(const struct rwkv_b200_matrix * m) { return m && !
 
 static bool matrix_prepare(rwkv_b200_matrix * m, size_t n_vec) {
     const DevMat & W = m->copies[0];
+    if (!m->scratch.buf && gemm_tc_enabled()) {
+        void * p = nullptr, * f = nullptr;
+        RB_CUDA(cudaMalloc(&p, GEMM_SCRATCH_FLOATS * sizeof(float)), RWKV_ERROR_ALLOC, false);
+        m->allocations.push_back(p);
+        RB_CUDA(cudaMalloc(&f, GEMM_SCRATCH_FLAGS * sizeof(unsigned int)), RWKV_ERROR_ALLOC, false);
+        m->allocations.push_back(f);
+        RB_CUDA(cudaMemset(f, 0, GEMM_SCRATCH_FLAGS * sizeof(unsigned int)), RWKV_ERROR_ALLOC, false);
+        m->scratch.buf = (float *) p; m->scratch.flags = (unsigned int *) f; m->scratch.floats = GEMM_SCRATCH_FLOATS;
+    }
     if ((int) n_vec > m->x_rows) {
         RB_CHECK(act_dev_alloc(m->allocations, m->x, (int) n_vec, (int) W.K), RWKV_ERROR_ALLOC, false, "alloc failed");
         m->x_rows = (int) n_vec;
@@ -435,7 +445,7 @@ bool rwkv_b200_matrix_mul_tc(struct rwkv_b200_matrix * m, const float * x, size_
     RB_CUDA(cudaMemcpyAsync(m->x.f, x, n_vec * W.K * sizeof(float), cudaMemcpyHostToDevice, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(launch_to_half(m->x.f, m->x.h, n_vec * W.K, m->stream), RWKV_ERROR_GRAPH, false);
     GemmJob g; g.W = W; g.x16 = m->x.h; g.ldx = (int) W.K; g.out = m->y; g.ldo = (int) W.M; g.epi = EPI_STORE;
-    RB_CUDA(launch_gemm_tc(&g, 1, (int) n_vec, m->stream), RWKV_ERROR_GRAPH, false);
+    RB_CUDA(launch_gemm_tc(&g, 1, (int) n_vec, m->stream, &m->scratch), RWKV_ERROR_GRAPH, false);
     RB_CUDA(cudaMemcpyAsync(y, m->y, n_vec * W.M * sizeof(float), cudaMemcpyDeviceToHost, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(cudaStreamSynchronize(m->stream), RWKV_ERROR_GRAPH, false);
     return true;
@@ -454,7 +464,7 @@ bool rwkv_b200_matrix_bench_tc(struct rwkv_b200_matrix * m, size_t n_vec, int it
     cudaError_t err = cudaSuccess;
     auto one = [&](size_t c) {
         GemmJob g; g.W = m->copies[c % m->copies.size()]; g.x16 = m->x.h; g.ldx = (int) W0.K; g.out = m->y; g.ldo = (int) W0.M; g.epi = EPI_STORE;
-        return launch_gemm_tc(&g, 1, (int) n_vec, m->stream);
+        return launch_gemm_tc(&g, 1, (int) n_vec, m->stream, &m->scratch);
     };
     for (size_t c = 0; c < m->copies.size() && err == cudaSuccess; c++) err = one(c);
     cudaEventRecord(e0, m->stream);

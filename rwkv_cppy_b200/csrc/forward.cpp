@@ -49,6 +49,12 @@ bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows
             && dalloc(ws, ws.a, n) && dalloc(ws, ws.vgate, n) && dalloc(ws, ws.ffn_r, n) && dalloc(ws, ws.v_first, n);
     if (m.arch_major == 6) ok = ok && dalloc(ws, ws.m5, 5 * n);
     if (m.arch_major >= 5 && rows >= WKV_SEQ_MIN_ROWS) ok = ok && dalloc(ws, ws.yraw, n);
+    ws.gemm_scratch = GemmScratch();
+    if (gemm_tc_enabled() && rows >= gemm_tc_min_rows()) {
+        ok = ok && dalloc(ws, ws.gemm_scratch.buf, GEMM_SCRATCH_FLOATS) && dalloc(ws, ws.gemm_scratch.flags, GEMM_SCRATCH_FLAGS);
+        ok = ok && cudaMemset(ws.gemm_scratch.flags, 0, GEMM_SCRATCH_FLAGS * sizeof(unsigned int)) == cudaSuccess;
+        if (ok) ws.gemm_scratch.floats = GEMM_SCRATCH_FLOATS;
+    }
     if ((m.arch_major == 5 || m.arch_major == 6) && m.head_size == 64 && gemm_tc_enabled() && rows >= gemm_tc_min_rows()) {
         const size_t chunks = ((size_t) rows + WKV_CHUNK_TOKENS - 1) / WKV_CHUNK_TOKENS;
         ok = ok && dalloc(ws, ws.wkv_ds, chunks * D * 64) && dalloc(ws, ws.wkv_pc, chunks * D);
@@ -111,7 +117,7 @@ struct Pass {
                 }
                 done[k] = true;
             }
-            chk(launch_gemm_tc(g, n, rows, st));
+            chk(launch_gemm_tc(g, n, rows, st, &ws.gemm_scratch));
             // inputs converted for this launch keep a valid q8 form: only the marks of GEMM outputs persist
             for (const float * p : to_half_marks) tc_written.erase(p);
             to_half_marks.clear();

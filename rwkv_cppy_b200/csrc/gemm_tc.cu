@@ -49,6 +49,11 @@ struct GtJob {
 struct GtBatch {
     GtJob job[GEMM_MAX_JOBS];
     int n_jobs, T, n_tiles, total_tiles;
+    // K split (ks = 2): CTAs 2c and 2c+1 share output tile(s) c, c + gridDim/2, ...; the odd CTA takes the upper half of
+    // K, leaves its raw accumulators in `scratch` ([tile][BN tokens][128 rows] FP32) and raises one flag per epilogue
+    // warp; the even CTA adds them to its own before the epilogue op (own + peer: a fixed order) and clears the flag.
+    int ks;
+    float * scratch; unsigned int * flags;
 };
 
 template <int BN> __host__ __device__ constexpr int gt_stages() { return BN == 256 ? 3 : BN == 128 ? 4 : 5; }
@@ -98,8 +103,22 @@ __device__ __forceinline__ void dequant_block_f16(uint4 (&out)[4], const uint4 q
 // One warp's share of a finished accumulator tile: lane = weight row m; the warp takes the
 // 16-column (token) chunks `half_id`, `half_id + 2`, ... of the BN columns.  Stores are 128-byte
 // coalesced (32 lanes = 32 consecutive m of one token row).
+// K-split, upper half: raw accumulators -> scratch tile (row = TMEM lane of this thread)
+template <int BN>
+__device__ __forceinline__ void epilogue_spill(float * scr, uint32_t tcol, int lane_row, int t0, int T, int half_id) {
+#pragma unroll 1
+    for (int c0 = half_id * 16; c0 < BN; c0 += 32) {
+        if (t0 + c0 >= T) break;                                  // warp-uniform
+        uint32_t v[16];
+        tmem_ld_32x16(tcol + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; i++) __stcg(scr + (size_t) (c0 + i) * GT_BM + lane_row, __uint_as_float(v[i]));
+    }
+}
+
 template <int EPI, int BN>
-__device__ __forceinline__ void epilogue_tile(const GtJob & J, uint32_t tcol, int m, int t0, int T, int half_id) {
+__device__ __forceinline__ void epilogue_tile(const GtJob & J, uint32_t tcol, int m, int t0, int T, int half_id, const float * peer = nullptr, int lane_row = 0) {
     const bool row_ok = m < (int) J.M;
     float * const out = J.out; __half * const out_h = J.out_h;
     const int ldo = J.ldo, ld_h = J.ld_h;
@@ -110,6 +129,13 @@ __device__ __forceinline__ void epilogue_tile(const GtJob & J, uint32_t tcol, in
         tmem_ld_32x16(tcol + c0, v);
         tmem_ld_wait();
         const int nv = T - t0 - c0;
+        if (peer) {                                                // K split: add the other half's partial sums (own + peer)
+            float pp[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) pp[i] = __ldcg(peer + (size_t) (c0 + i) * GT_BM + lane_row);
+#pragma unroll
+            for (int i = 0; i < 16; i++) v[i] = __float_as_uint(__fadd_rn(__uint_as_float(v[i]), pp[i]));
+        }
         if (row_ok) {
             // read-modify-write epilogues: all 16 operand loads go out before the first store (the compiler
             // may not move a load of `out` above a store to `out`, which made this 16 dependent round trips)
@@ -180,6 +206,11 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
     const uint32_t tmem_base = *tmem_slot_p;
 
     const int n_tiles = B.n_tiles;
+    const int ks = B.ks, krank = ks > 1 ? (int) (blockIdx.x & 1) : 0;
+    const int tile0 = ks > 1 ? (int) (blockIdx.x >> 1) : (int) blockIdx.x, tile_step = ks > 1 ? (int) (gridDim.x >> 1) : (int) gridDim.x;
+    // this CTA's share of the K steps of a job
+    auto kb_lo = [&](uint32_t kblocks) { return krank ? kblocks / 2 : 0u; };
+    auto kb_hi = [&](uint32_t kblocks) { return (ks > 1 && !krank) ? kblocks / 2 : kblocks; };
     auto locate = [&](int tile, int & j, int & mt, int & nt) {
         j = 0;
 #pragma unroll 1
@@ -193,10 +224,10 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
         if (lane == 0) {
             pdl_wait();                                          // the activations come from the preceding kernels
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < B.total_tiles; tile += gridDim.x) {
+            for (int tile = tile0; tile < B.total_tiles; tile += tile_step) {
                 int j, mt, nt; locate(tile, j, mt, nt);
                 const GtJob & J = B.job[j];
-                for (uint32_t kb = 0; kb < J.kblocks; kb++, it++) {
+                for (uint32_t kb = kb_lo(J.kblocks); kb < kb_hi(J.kblocks); kb++, it++) {
                     const uint32_t s = it % S, ph = (it / S) & 1;
                     if (QUANT) {
                         const uint32_t qs = it % GT_SQ, qph = (it / GT_SQ) & 1;
@@ -219,14 +250,15 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
         // ===== MMA issuer =====
         constexpr uint32_t idesc = umma_idesc_f16(GT_BM, BN);
         uint32_t it = 0, tl = 0;
-        for (int tile = blockIdx.x; tile < B.total_tiles; tile += gridDim.x, tl++) {
+        for (int tile = tile0; tile < B.total_tiles; tile += tile_step, tl++) {
             int j, mt, nt; locate(tile, j, mt, nt);
             const uint32_t kblocks = B.job[j].kblocks;
             const uint32_t buf = tl & 1, bph = (tl >> 1) & 1;
             mbar_wait(bar_tempty + 8 * buf, bph ^ 1);            // epilogue has drained this accumulator
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + buf * BN;
-            for (uint32_t kb = 0; kb < kblocks; kb++, it++) {
+            const uint32_t kfirst = kb_lo(kblocks), klast = kb_hi(kblocks);
+            for (uint32_t kb = kfirst; kb < klast; kb++, it++) {
                 const uint32_t s = it % S, ph = (it / S) & 1;
                 mbar_wait(bar_full + 8 * s, ph);
                 tc_fence_after();
@@ -237,9 +269,9 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
 #ifdef RB_ABL_NOMMA
                         if (kb == 0 && k == 0)
 #endif
-                        tc_mma_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | (uint32_t) k) != 0 ? 1u : 0u);
+                        tc_mma_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, ((kb - kfirst) | (uint32_t) k) != 0 ? 1u : 0u);
                     tc_commit(bar_empty + 8 * s);                 // stage free once these MMAs have read it
-                    if (kb + 1 == kblocks) tc_commit(bar_tfull + 8 * buf);
+                    if (kb + 1 == klast) tc_commit(bar_tfull + 8 * buf);
                 }
                 __syncwarp();
             }
@@ -249,7 +281,7 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
         const int q = warp & 3, half_id = (warp - 2) >> 2;
         pdl_wait();
         uint32_t tl = 0;
-        for (int tile = blockIdx.x; tile < B.total_tiles; tile += gridDim.x, tl++) {
+        for (int tile = tile0; tile < B.total_tiles; tile += tile_step, tl++) {
             int j, mt, nt; locate(tile, j, mt, nt);
             const GtJob & J = B.job[j];
             const uint32_t buf = tl & 1, bph = (tl >> 1) & 1;
@@ -257,18 +289,44 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
             tc_fence_after();
             const uint32_t tcol = tmem_base + ((uint32_t) (q * 32) << 16) + buf * BN;
             const int m = mt * GT_BM + q * 32 + lane, t0 = nt * BN;
+            const float * peer = nullptr;
+            if (ks > 1) {
+                float * scr = B.scratch + (size_t) tile * BN * GT_BM;
+                unsigned int * flag = B.flags + (size_t) tile * GT_EPI_WARPS + (warp - 2);
+                if (krank) {                                      // upper half of K: spill, publish, next tile
+                    epilogue_spill<BN>(scr, tcol, q * 32 + lane, t0, B.T, half_id);
+                    __threadfence();
+                    __syncwarp();
+                    if (lane == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(flag), "r"(1u) : "memory");
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+                    continue;
+                }
+                if (lane == 0) {
+                    unsigned int seen = 0;
+                    const long long tstart = clock64();
+                    do {
+                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
+                    } while (seen == 0 && clock64() - tstart < 4000000000LL);      // ~2 s: never hang the GPU on a lost partner
+                    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(flag), "r"(0u) : "memory");     // ready for the next launch
+                }
+                __syncwarp();
+                peer = scr;
+            }
+            const int lrow = q * 32 + lane;
             switch (J.epi) {
-                case EPI_STORE:        epilogue_tile<EPI_STORE, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_SIGMOID:      epilogue_tile<EPI_SIGMOID, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_RELU_SQ:      epilogue_tile<EPI_RELU_SQ, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_SILU:         epilogue_tile<EPI_SILU, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_TANH:         epilogue_tile<EPI_TANH, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_ADD_TO:       epilogue_tile<EPI_ADD_TO, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_MULADD_TO:    epilogue_tile<EPI_MULADD_TO, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_BIAS_SIGMOID: epilogue_tile<EPI_BIAS_SIGMOID, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_V6_DECAY:     epilogue_tile<EPI_V6_DECAY, BN>(J, tcol, m, t0, B.T, half_id); break;
-                case EPI_ADD_AUX:      epilogue_tile<EPI_ADD_AUX, BN>(J, tcol, m, t0, B.T, half_id); break;
-                default:               epilogue_tile<EPI_V7_DECAY, BN>(J, tcol, m, t0, B.T, half_id); break;
+                case EPI_STORE:        epilogue_tile<EPI_STORE, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_SIGMOID:      epilogue_tile<EPI_SIGMOID, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_RELU_SQ:      epilogue_tile<EPI_RELU_SQ, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_SILU:         epilogue_tile<EPI_SILU, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_TANH:         epilogue_tile<EPI_TANH, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_ADD_TO:       epilogue_tile<EPI_ADD_TO, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_MULADD_TO:    epilogue_tile<EPI_MULADD_TO, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_BIAS_SIGMOID: epilogue_tile<EPI_BIAS_SIGMOID, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_V6_DECAY:     epilogue_tile<EPI_V6_DECAY, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                case EPI_ADD_AUX:      epilogue_tile<EPI_ADD_AUX, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
+                default:               epilogue_tile<EPI_V7_DECAY, BN>(J, tcol, m, t0, B.T, half_id, peer, lrow); break;
             }
             tc_fence_before();
             __syncwarp();
@@ -280,10 +338,10 @@ gemm_tc_kernel(const __grid_constant__ GtBatch B) {
         const int row = d & (GT_BM - 1), blk = d >> 7;
         const int e = blk * GT_BM + row;
         uint32_t it = 0;
-        for (int tile = blockIdx.x; tile < B.total_tiles; tile += gridDim.x) {
+        for (int tile = tile0; tile < B.total_tiles; tile += tile_step) {
             int j, mt, nt; locate(tile, j, mt, nt);
             const uint32_t kblocks = B.job[j].kblocks;
-            for (uint32_t kb = 0; kb < kblocks; kb++, it++) {
+            for (uint32_t kb = kb_lo(kblocks); kb < kb_hi(kblocks); kb++, it++) {
                 const uint32_t s = it % S, ph = (it / S) & 1, qs = it % GT_SQ, qph = (it / GT_SQ) & 1;
                 mbar_wait(bar_qfull + 8 * qs, qph);
                 const uint8_t * cq = pQ + qs * CH;
@@ -382,7 +440,7 @@ bool gemm_tc_supported(const DevMat & W, int T) {
 
 template <int TYPE, int BN>
 static cudaError_t launch_gt(const GtBatch & b, cudaStream_t st) {
-    const int grid = std::min(b.total_tiles, 148);
+    const int grid = b.ks > 1 ? 2 * std::min(b.total_tiles, 74) : std::min(b.total_tiles, 148);
     return launch_pdl(gemm_tc_kernel<TYPE, BN>, dim3(grid), dim3(GT_THREADS), gt_smem_bytes<TYPE, BN>(), st, b);
 }
 template <int TYPE>
@@ -392,7 +450,7 @@ static cudaError_t launch_gt_bn(const GtBatch & b, int BN, cudaStream_t st) {
     return launch_gt<TYPE, 64>(b, st);
 }
 
-cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t st) {
+cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t st, const GemmScratch * scratch) {
     if (n_jobs <= 0) return cudaSuccess;
     if (n_jobs > GEMM_MAX_JOBS) return cudaErrorInvalidValue;
     // Tile width: wide tiles reuse the dequantised weights over more tokens, narrow tiles fill the
@@ -400,19 +458,33 @@ cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t
     // L2-bound estimates): 800 / 520 / 330 for BN = 256 / 128 / 64, times the number of tile rounds.
     int m_tiles_total = 0;
     for (int j = 0; j < n_jobs; j++) m_tiles_total += ((int) jobs[j].W.M + GT_BM - 1) / GT_BM;
-    int BN = 64; double best = 1e300;
+    int BN = 64, KS = 1; double best = 1e300;
     const int cand[3] = {256, 128, 64}; const double cost[3] = {800.0, 520.0, 330.0};
     static const int force_bn = [] { const char * e = getenv("RWKV_B200_TC_BN"); return e ? atoi(e) : 0; }();   // tests: pin the tile width
+    static const int force_ks = [] { const char * e = getenv("RWKV_B200_TC_KS"); return e ? atoi(e) : 0; }();   // tests: 1 = never split K, 2 = split whenever possible
+    uint32_t kb_max = 0, kb_min = 0xffffffffu; bool kb_even = true;
+    for (int j = 0; j < n_jobs; j++) {
+        const uint32_t kb = (jobs[j].W.K + GT_BK - 1) / GT_BK;
+        kb_max = std::max(kb_max, kb); kb_min = std::min(kb_min, kb); kb_even = kb_even && (kb % 2 == 0);
+    }
+    // K split over CTA pairs: few tiles with a long K loop leave most SMs idle (ffn value: 2048 rows x K = 7168); two CTAs
+    // then share a tile and meet in an L2-resident scratch tile (deterministic: own half + peer half).
+    const bool can_split = scratch && scratch->buf && scratch->flags && kb_even && kb_min >= 16 && force_ks != 1;
     for (int c = 0; c < 3; c++) {
         if (force_bn && cand[c] != force_bn) continue;
         if (cand[c] > 64 && cand[c] / 2 >= T) continue;           // tile would be more than half empty
         const int tiles = m_tiles_total * ((T + cand[c] - 1) / cand[c]);
-        const double t = (double) ((tiles + 147) / 148) * cost[c];
-        if (t < best) { best = t; BN = cand[c]; }
+        for (int ks = 1; ks <= 2; ks++) {
+            if (ks == 2 && !(can_split && tiles <= 74 && (size_t) tiles * cand[c] * GT_BM <= scratch->floats)) continue;
+            if (ks == 1 && force_ks == 2 && can_split && tiles <= 74 && (size_t) tiles * cand[c] * GT_BM <= scratch->floats) continue;
+            const double t = (double) ((tiles * ks + 147) / 148) * cost[c] * (double) (kb_max / ks) + (ks == 2 ? 2500.0 : 0.0);
+            if (t < best) { best = t; BN = cand[c]; KS = ks; }
+        }
     }
     GtBatch b;
     memset(&b, 0, sizeof(b));
     b.n_jobs = n_jobs; b.T = T; b.n_tiles = (T + BN - 1) / BN;
+    b.ks = KS; b.scratch = KS > 1 ? scratch->buf : nullptr; b.flags = KS > 1 ? scratch->flags : nullptr;
     const uint32_t type = jobs[0].W.type;
     int total = 0;
     for (int j = 0; j < n_jobs; j++) {

@@ -110,7 +110,11 @@ bool gemm_tc_enabled();                                // driver entry point fou
 int  gemm_tc_min_rows();                               // smallest T that takes the tensor path (default 64)
 bool gemm_tc_supported(const DevMat & W, int T);
 cudaError_t gemm_tc_init();                            // once per device, outside stream capture
-cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t st);   // all jobs share one weight type
+// Scratch of the K-split launches (per context: one GEMM at a time per stream): raw partial tiles + one flag per
+// (tile, epilogue warp), zero-initialised.  Without it every launch keeps whole K loops per CTA.
+struct GemmScratch { float * buf = nullptr; unsigned int * flags = nullptr; size_t floats = 0; };
+constexpr size_t GEMM_SCRATCH_FLOATS = (size_t) 74 * 256 * 128, GEMM_SCRATCH_FLAGS = 74 * 8;
+cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t st, const GemmScratch * scratch = nullptr);   // all jobs share one weight type
 cudaError_t launch_to_half(const float * x, uint16_t * out, size_t n, cudaStream_t st);  // n % 4 == 0
 
 // ---- codec -----------------------------------------------------------------------------

@@ -89,3 +89,18 @@ def test_gemm_tc_repeatable(raw_lib, t):
         bad = np.abs(y - ref) > 1e-3 * scale
         assert not bad.any(), (rep, int(bad.sum()))
     dm.free()
+
+
+@pytest.mark.parametrize("t", [O.TYPE_Q5_1, O.TYPE_Q8_0, O.TYPE_FP16], ids=["Q5_1", "Q8_0", "FP16"])
+@pytest.mark.parametrize("M,K,T", [(2048, 7168, 1024), (2560, 10240, 256), (160, 2048, 1024), (640, 2048, 200)])
+def test_gemm_tc_few_tiles_long_k(raw_lib, t, M, K, T):
+    """Shapes with few output tiles and a long K loop (ffn value, v6 time_maa_w1): the K-split launches (two CTAs
+    per tile meeting in a scratch tile) against the FP16 oracle, repeated (flags must re-arm between launches)."""
+    rng = np.random.default_rng(M + K + T + t)
+    _, raw = make_matrix(rng, t, M, K)
+    dm = DevMatrix(raw_lib.lib, t, raw, M, K)
+    x = rng.standard_normal((T, K)).astype(np.float32)
+    y = check(dm, t, raw, M, K, x)
+    for _ in range(3):
+        assert np.array_equal(mul_tc(dm, x), y)          # deterministic: own half + peer half, always in that order
+    dm.free()
