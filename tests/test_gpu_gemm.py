@@ -96,11 +96,18 @@ def test_gemm_tc_repeatable(raw_lib, t):
 def test_gemm_tc_few_tiles_long_k(raw_lib, t, M, K, T):
     """Shapes with few output tiles and a long K loop (ffn value, v6 time_maa_w1): the K-split launches (two CTAs
     per tile meeting in a scratch tile) against the FP16 oracle, repeated (flags must re-arm between launches)."""
+    import os
     rng = np.random.default_rng(M + K + T + t)
     _, raw = make_matrix(rng, t, M, K)
     dm = DevMatrix(raw_lib.lib, t, raw, M, K)
     x = rng.standard_normal((T, K)).astype(np.float32)
-    y = check(dm, t, raw, M, K, x)
-    for _ in range(3):
-        assert np.array_equal(mul_tc(dm, x), y)          # deterministic: own half + peer half, always in that order
+    y1 = check(dm, t, raw, M, K, x)                       # whole-K tiles (default)
+    os.environ["RWKV_B200_TC_KS"] = "2"                   # opt-in K split (read per launch)
+    try:
+        y = check(dm, t, raw, M, K, x)
+        for _ in range(3):
+            assert np.array_equal(mul_tc(dm, x), y)      # deterministic: own half + peer half, always in that order
+    finally:
+        del os.environ["RWKV_B200_TC_KS"]
+    assert np.allclose(y, y1, rtol=0, atol=float(np.abs(y1).max()) * 1e-5)
     dm.free()
