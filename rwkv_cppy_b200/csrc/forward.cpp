@@ -24,7 +24,7 @@ bool dalloc(Workspace & ws, T *& p, size_t n) {
 bool act_alloc(Workspace & ws, Act & a, int rows, int K) {
     a.K = K;
     if (!dalloc(ws, a.f, (size_t) rows * K)) return false;
-    if (gemm_tc_enabled() && rows >= gemm_tc_min_rows() && !dalloc(ws, a.h, (size_t) rows * K)) return false;
+    if (gemm_tc_enabled() && rows >= gemm_tc_min_rows(true) && !dalloc(ws, a.h, (size_t) rows * K)) return false;
     if (K % 32 == 0) {
         const size_t nb = (size_t) rows * (K / 32);
         if (!dalloc(ws, a.q, (size_t) rows * K) || !dalloc(ws, a.d, nb) || !dalloc(ws, a.s, nb) || !dalloc(ws, a.isum, nb)) return false;
@@ -50,7 +50,7 @@ bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows
     if (m.arch_major == 6) ok = ok && dalloc(ws, ws.m5, 5 * n);
     if (m.arch_major >= 5 && rows >= WKV_SEQ_MIN_ROWS) ok = ok && dalloc(ws, ws.yraw, n);
     ws.gemm_scratch = GemmScratch();
-    if (gemm_tc_enabled() && rows >= gemm_tc_min_rows()) {
+    if (gemm_tc_enabled() && rows >= gemm_tc_min_rows(true)) {
         ok = ok && dalloc(ws, ws.gemm_scratch.buf, GEMM_SCRATCH_FLOATS) && dalloc(ws, ws.gemm_scratch.flags, GEMM_SCRATCH_FLAGS);
         ok = ok && cudaMemset(ws.gemm_scratch.flags, 0, GEMM_SCRATCH_FLAGS * sizeof(unsigned int)) == cudaSuccess;
         if (ok) ws.gemm_scratch.floats = GEMM_SCRATCH_FLOATS;
@@ -144,14 +144,14 @@ struct Pass {
     }
     std::vector<const float *> to_half_marks;
     bool tc_job(const GemvJob & j, int rows) const {
-        return j.x.h != nullptr && (j.x_off % 8) == 0 && (j.x.K % 8) == 0 && gemm_tc_supported(j.W, rows);
+        return j.x.h != nullptr && (j.x_off % 8) == 0 && (j.x.K % 8) == 0 && gemm_tc_supported(j.W, rows, fa.batch != 0);
     }
     // The form a producer should emit `a` in: when every consumer is a tensor-core GEMM the rows are
     // written once as FP16 (no FP32 rows, no q8 blocks, no conversion launch); otherwise FP32 + q8.
     Act produced(const Act & a, std::initializer_list<const DevMat *> consumers, int rows = -1) {
         if (rows < 0) rows = R;
         bool all_tc = a.h != nullptr && (a.K % 8) == 0 && consumers.size() > 0;
-        for (const DevMat * W : consumers) all_tc = all_tc && gemm_tc_supported(*W, rows);
+        for (const DevMat * W : consumers) all_tc = all_tc && gemm_tc_supported(*W, rows, fa.batch != 0);
         Act o = a;
         if (all_tc) { o.f = nullptr; o.q = nullptr; o.d = nullptr; o.s = nullptr; o.isum = nullptr; tc_written[a.f] = true; }
         else        { o.h = nullptr; tc_written.erase(a.f); }
@@ -382,7 +382,7 @@ struct Pass {
         // low-rank pairs (never quantised).  Wide row counts chain the two stages on the tensor cores: the first
         // stage then also leaves an FP16 copy of its rows for the second (no q8 form: the second stage is FP16 / FP32).
         auto lora_tc = [&](const DevMat & W1, const DevMat & W2) {
-            return ws.lora[0].h != nullptr && W1.M % 8 == 0 && gemm_tc_supported(W1, R) && gemm_tc_supported(W2, R);
+            return ws.lora[0].h != nullptr && W1.M % 8 == 0 && gemm_tc_supported(W1, R, fa.batch != 0) && gemm_tc_supported(W2, R, fa.batch != 0);
         };
         const DevMat * second[4] = {&l.w2, &l.a2, &l.g2, &l.v2};
         auto lora_in = [&](int slot, const DevMat & W, int epi) {

@@ -426,13 +426,13 @@ bool gemm_tc_enabled() {
     return on;
 }
 
-int gemm_tc_min_rows() {
-    static const int v = [] { const char * e = getenv("RWKV_B200_TC_MIN_ROWS"); const int n = e ? atoi(e) : 0; return n > 0 ? n : 64; }();
-    return v;
+int gemm_tc_min_rows(bool batch) {
+    static const int v = [] { const char * e = getenv("RWKV_B200_TC_MIN_ROWS"); const int n = e ? atoi(e) : 0; return n > 0 ? n : 0; }();
+    return v > 0 ? v : (batch ? 32 : 64);
 }
 
-bool gemm_tc_supported(const DevMat & W, int T) {
-    if (!gemm_tc_enabled() || T < gemm_tc_min_rows()) return false;
+bool gemm_tc_supported(const DevMat & W, int T, bool batch) {
+    if (!gemm_tc_enabled() || T < gemm_tc_min_rows(batch)) return false;
     if (W.K < 64 || W.K % 8 != 0) return false;
     if (W.type == T_F16) return true;
     return type_quantized(W.type) && W.tc != nullptr;

@@ -107,8 +107,10 @@ struct GemmJob {
     uint16_t *       out_h = nullptr; int ld_h = 0;   // optional FP16 copy of the result (input of a chained GEMM)
 };
 bool gemm_tc_enabled();                                // driver entry point found and RWKV_B200_NO_TC != 1
-int  gemm_tc_min_rows();                               // smallest T that takes the tensor path (default 64)
-bool gemm_tc_supported(const DevMat & W, int T);
+// smallest row count that takes the tensor path: 64 tokens of a sequence, 32 streams of a batch (a batch step re-reads every
+// weight whatever its width, so the tensor path pays earlier: 32 v7-2.9B streams 7.74 -> 5.99 ms); RWKV_B200_TC_MIN_ROWS sets both
+int  gemm_tc_min_rows(bool batch = false);
+bool gemm_tc_supported(const DevMat & W, int T, bool batch = false);
 cudaError_t gemm_tc_init();                            // once per device, outside stream capture
 // Scratch of the K-split launches (per context: one GEMM at a time per stream): raw partial tiles + one flag per
 // (tile, epilogue warp), zero-initialised.  Without it every launch keeps whole K loops per CTA.

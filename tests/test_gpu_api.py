@@ -142,20 +142,21 @@ def test_batch_streams_equal_individual_streams(shared_library, raw_lib, arch, f
     batch.free(); m.free()
 
 
+@pytest.mark.parametrize("B", [40, 96])
 @pytest.mark.parametrize("shape,fmt", [("v7-mini", "FP16-to-Q8_0"), ("v6-mini", "FP16-to-Q5_1"), ("v4-mini", "FP16")])
-def test_wide_batch_matches_individual_streams(shared_library, shape, fmt):
-    """96 streams step together on the tensor-core path (FP16 operands, warp-per-row layer norm, coalesced
+def test_wide_batch_matches_individual_streams(shared_library, shape, fmt, B):
+    """B >= 32 streams step together on the tensor-core path (FP16 operands, warp-per-row layer norm, coalesced
     state staging); every stream must agree with its own serial rwkv_eval loop within the FP16 tolerance."""
     from rwkv_cppy_b200 import RWKVModel, synth
     m = RWKVModel(shared_library, synth.ensure_model(shared_library, shape, fmt))
-    B, steps = 96, 5
+    steps = 5
     rng = np.random.default_rng(5)
     toks = rng.integers(0, 512, size=(steps, B)).astype(np.uint32)
     batch = m.create_batch(B)
     logits = None
     for s in range(steps):
         logits = batch.eval(toks[s])
-    for b in (0, 1, 47, 95):
+    for b in (0, 1, B // 2, B - 1):
         st, l1 = None, None
         for s in range(steps):
             l1, st = m.eval(int(toks[s, b]), st, use_numpy=True)
