@@ -21,13 +21,15 @@ void ctx_fail(rwkv_context * ctx, int flags, const char * file, int line, const 
 }
 thread_local int t_device = -1;
 
+// -1: no CUDA device; -2: LOCAL_RANK names a device that does not exist (several ranks silently sharing GPU 0 would
+// "work" and, under tensor parallelism, deadlock on each other).
 int pick_device() {
-    if (t_device >= 0) return t_device;
-    const char * lr = getenv("LOCAL_RANK");
     int n = 0;
-    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) return -1;
-    int d = lr ? atoi(lr) : 0;
-    if (d < 0 || d >= n) d = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) { cudaGetLastError(); return -1; }
+    if (t_device >= 0) return t_device < n ? t_device : -2;
+    const char * lr = getenv("LOCAL_RANK");
+    const int d = lr ? atoi(lr) : 0;
+    if (d < 0 || d >= n) return -2;
     return d;
 }
 
@@ -160,6 +162,7 @@ struct rwkv_context * rwkv_init_from_file(const char * model_file_path, const ui
     g_last_error = RWKV_ERROR_NONE;
     RB_CHECK(model_file_path != nullptr, RWKV_ERROR_ARGS, nullptr, "model_file_path is NULL");
     const int dev = pick_device();
+    RB_CHECK(dev != -2, RWKV_ERROR_ARGS | RWKV_ERROR_CTX, nullptr, "LOCAL_RANK / rwkv_b200_set_device names a CUDA device that does not exist");
     RB_CHECK(dev >= 0, RWKV_ERROR_CTX | RWKV_ERROR_UNSUPPORTED, nullptr, "No CUDA device: this engine has no CPU path");
     RB_CUDA(cudaSetDevice(dev), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, nullptr);
     Model * model = model_load(model_file_path);

@@ -28,7 +28,7 @@ struct rwkv_b200_matrix {
     float * y = nullptr; size_t y_cap = 0;
     cudaStream_t stream = nullptr;
     size_t next = 0;
-    GemmScratch scratch;              // K-split partial tiles (tensor-core hook)
+    MatmulScratch scratch;              // K-split partial tiles (tensor-core hook)
 };
 
 namespace {
@@ -58,7 +58,7 @@ bool upload_matrix(int type, const void * raw, size_t M, size_t K, cudaStream_t 
     ok = ok && cudaMemcpyAsync(scratch, raw, nbytes, cudaMemcpyHostToDevice, st) == cudaSuccess;
     ok = ok && launch_repack(type, (const uint8_t *) scratch, M, K, tiled, st) == cudaSuccess;
     void * tc = nullptr;
-    if (ok && gemm_tc_enabled() && K >= TC_KB) {
+    if (ok && matmul_tc_enabled() && K >= TC_KB) {
         tc = alloc(tc_bytes(type, M, K));
         ok = tc != nullptr && launch_repack_tc(type, (const uint8_t *) scratch, M, K, tc, st) == cudaSuccess;
     }
@@ -75,7 +75,7 @@ bool act_dev_alloc(std::vector<void *> & allocs, Act & a, int rows, int K) {
     a.K = K;
     a.f = (float *) alloc((size_t) rows * K * 4);
     if (!a.f) return false;
-    if (gemm_tc_enabled()) { a.h = (uint16_t *) alloc((size_t) rows * K * 2); if (!a.h) return false; }
+    if (matmul_tc_enabled()) { a.h = (uint16_t *) alloc((size_t) rows * K * 2); if (!a.h) return false; }
     if (K % 32 == 0) {
         const size_t nb = (size_t) rows * (K / 32);
         a.q = (int8_t *) alloc((size_t) rows * K); a.d = (float *) alloc(nb * 4); a.s = (float *) alloc(nb * 4); a.isum = (int *) alloc(nb * 4);
@@ -317,6 +317,7 @@ struct rwkv_context * rwkv_b200_tp_init_from_file(const char * model_file_path, 
     RB_CHECK(world_size >= 2 && rank >= 0 && rank < world_size, RWKV_ERROR_ARGS, nullptr, "Bad rank %d / world size %d", rank, world_size);
     RB_CHECK(tp_available(), RWKV_ERROR_CTX | RWKV_ERROR_UNSUPPORTED, nullptr, "NCCL (libnccl.so.2) not found");
     const int dev = pick_device();
+    RB_CHECK(dev != -2, RWKV_ERROR_ARGS | RWKV_ERROR_CTX, nullptr, "LOCAL_RANK / rwkv_b200_set_device names a CUDA device that does not exist");
     RB_CHECK(dev >= 0, RWKV_ERROR_CTX | RWKV_ERROR_UNSUPPORTED, nullptr, "No CUDA device: this engine has no CPU path");
     RB_CUDA(cudaSetDevice(dev), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, nullptr);
     TpInfo tp; tp.rank = rank; tp.world = world_size;
@@ -375,8 +376,8 @@ struct rwkv_b200_matrix * rwkv_b200_matrix_create(int type, const void * raw, si
     rwkv_b200_matrix * m = new (std::nothrow) rwkv_b200_matrix();
     RB_CHECK(m != nullptr, RWKV_ERROR_ALLOC, nullptr, "alloc failed");
     m->device = dev;
-    bool ok = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) == cudaSuccess && gemv_async_init() == cudaSuccess
-              && (!gemm_tc_enabled() || gemm_tc_init() == cudaSuccess);
+    bool ok = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) == cudaSuccess && matvec_async_init() == cudaSuccess
+              && (!matmul_tc_enabled() || matmul_tc_init() == cudaSuccess);
     m->copies.resize(copies);
     for (size_t c = 0; c < copies && ok; c++) ok = upload_matrix(type, raw, n_rows, n_cols, m->stream, m->allocations, m->copies[c]);
     if (!ok) { rwkv_b200_matrix_free(m); return nullptr; }
@@ -396,14 +397,14 @@ size_t rwkv_b200_matrix_bytes(const struct rwkv_b200_matrix * m) { return m && !
 
 static bool matrix_prepare(rwkv_b200_matrix * m, size_t n_vec) {
     const DevMat & W = m->copies[0];
-    if (!m->scratch.buf && gemm_tc_enabled()) {
+    if (!m->scratch.buf && matmul_tc_enabled()) {
         void * p = nullptr, * f = nullptr;
-        RB_CUDA(cudaMalloc(&p, GEMM_SCRATCH_FLOATS * sizeof(float)), RWKV_ERROR_ALLOC, false);
+        RB_CUDA(cudaMalloc(&p, MATMUL_SCRATCH_FLOATS * sizeof(float)), RWKV_ERROR_ALLOC, false);
         m->allocations.push_back(p);
-        RB_CUDA(cudaMalloc(&f, GEMM_SCRATCH_FLAGS * sizeof(unsigned int)), RWKV_ERROR_ALLOC, false);
+        RB_CUDA(cudaMalloc(&f, MATMUL_SCRATCH_FLAGS * sizeof(unsigned int)), RWKV_ERROR_ALLOC, false);
         m->allocations.push_back(f);
-        RB_CUDA(cudaMemset(f, 0, GEMM_SCRATCH_FLAGS * sizeof(unsigned int)), RWKV_ERROR_ALLOC, false);
-        m->scratch.buf = (float *) p; m->scratch.flags = (unsigned int *) f; m->scratch.floats = GEMM_SCRATCH_FLOATS;
+        RB_CUDA(cudaMemset(f, 0, MATMUL_SCRATCH_FLAGS * sizeof(unsigned int)), RWKV_ERROR_ALLOC, false);
+        m->scratch.buf = (float *) p; m->scratch.flags = (unsigned int *) f; m->scratch.floats = MATMUL_SCRATCH_FLOATS;
     }
     if ((int) n_vec > m->x_rows) {
         RB_CHECK(act_dev_alloc(m->allocations, m->x, (int) n_vec, (int) W.K), RWKV_ERROR_ALLOC, false, "alloc failed");
@@ -426,9 +427,9 @@ bool rwkv_b200_matrix_mul(struct rwkv_b200_matrix * m, const float * x, size_t n
     if (!matrix_prepare(m, n_vec)) return false;
     RB_CUDA(cudaMemcpyAsync(m->x.f, x, n_vec * W.K * sizeof(float), cudaMemcpyHostToDevice, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(launch_quantize_act(m->x, (int) n_vec, m->stream), RWKV_ERROR_GRAPH, false);
-    GemvBatch b; b.T = (int) n_vec; b.n_jobs = 1;
+    MatvecBatch b; b.T = (int) n_vec; b.n_jobs = 1;
     b.job[0].W = W; b.job[0].x = m->x; b.job[0].out = m->y; b.job[0].ldo = (int) W.M; b.job[0].epi = EPI_STORE;
-    RB_CUDA(launch_gemv(b, m->stream), RWKV_ERROR_GRAPH, false);
+    RB_CUDA(launch_matvec(b, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(cudaMemcpyAsync(y, m->y, n_vec * W.M * sizeof(float), cudaMemcpyDeviceToHost, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(cudaStreamSynchronize(m->stream), RWKV_ERROR_GRAPH, false);
     return true;
@@ -439,13 +440,13 @@ bool rwkv_b200_matrix_mul_tc(struct rwkv_b200_matrix * m, const float * x, size_
     RB_CUDA(cudaSetDevice(m->device), RWKV_ERROR_CTX, false);
     const DevMat & W = m->copies[m->next % m->copies.size()];
     m->next++;
-    RB_CHECK(gemm_tc_enabled() && (W.type == T_F16 || W.tc != nullptr) && W.K >= 64 && W.K % 8 == 0, RWKV_ERROR_ARGS | RWKV_ERROR_UNSUPPORTED, false,
+    RB_CHECK(matmul_tc_enabled() && (W.type == T_F16 || W.tc != nullptr) && W.K >= 64 && W.K % 8 == 0, RWKV_ERROR_ARGS | RWKV_ERROR_UNSUPPORTED, false,
              "Matrix not eligible for the tensor-core path");
     if (!matrix_prepare(m, n_vec)) return false;
     RB_CUDA(cudaMemcpyAsync(m->x.f, x, n_vec * W.K * sizeof(float), cudaMemcpyHostToDevice, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(launch_to_half(m->x.f, m->x.h, n_vec * W.K, m->stream), RWKV_ERROR_GRAPH, false);
-    GemmJob g; g.W = W; g.x16 = m->x.h; g.ldx = (int) W.K; g.out = m->y; g.ldo = (int) W.M; g.epi = EPI_STORE;
-    RB_CUDA(launch_gemm_tc(&g, 1, (int) n_vec, m->stream, &m->scratch), RWKV_ERROR_GRAPH, false);
+    MatmulJob g; g.W = W; g.x16 = m->x.h; g.ldx = (int) W.K; g.out = m->y; g.ldo = (int) W.M; g.epi = EPI_STORE;
+    RB_CUDA(launch_matmul_tc(&g, 1, (int) n_vec, m->stream, &m->scratch), RWKV_ERROR_GRAPH, false);
     RB_CUDA(cudaMemcpyAsync(y, m->y, n_vec * W.M * sizeof(float), cudaMemcpyDeviceToHost, m->stream), RWKV_ERROR_GRAPH, false);
     RB_CUDA(cudaStreamSynchronize(m->stream), RWKV_ERROR_GRAPH, false);
     return true;
@@ -455,7 +456,7 @@ bool rwkv_b200_matrix_bench_tc(struct rwkv_b200_matrix * m, size_t n_vec, int it
     RB_CHECK(m && n_vec > 0 && iters > 0 && ms_per_launch, RWKV_ERROR_ARGS, false, "Bad arguments");
     RB_CUDA(cudaSetDevice(m->device), RWKV_ERROR_CTX, false);
     const DevMat & W0 = m->copies[0];
-    RB_CHECK(gemm_tc_enabled() && (W0.type == T_F16 || W0.tc != nullptr) && W0.K >= 64 && W0.K % 8 == 0, RWKV_ERROR_ARGS | RWKV_ERROR_UNSUPPORTED, false,
+    RB_CHECK(matmul_tc_enabled() && (W0.type == T_F16 || W0.tc != nullptr) && W0.K >= 64 && W0.K % 8 == 0, RWKV_ERROR_ARGS | RWKV_ERROR_UNSUPPORTED, false,
              "Matrix not eligible for the tensor-core path");
     if (!matrix_prepare(m, n_vec)) return false;
     RB_CUDA(cudaMemsetAsync(m->x.h, 0, n_vec * W0.K * 2, m->stream), RWKV_ERROR_GRAPH, false);
@@ -463,8 +464,8 @@ bool rwkv_b200_matrix_bench_tc(struct rwkv_b200_matrix * m, size_t n_vec, int it
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaError_t err = cudaSuccess;
     auto one = [&](size_t c) {
-        GemmJob g; g.W = m->copies[c % m->copies.size()]; g.x16 = m->x.h; g.ldx = (int) W0.K; g.out = m->y; g.ldo = (int) W0.M; g.epi = EPI_STORE;
-        return launch_gemm_tc(&g, 1, (int) n_vec, m->stream, &m->scratch);
+        MatmulJob g; g.W = m->copies[c % m->copies.size()]; g.x16 = m->x.h; g.ldx = (int) W0.K; g.out = m->y; g.ldo = (int) W0.M; g.epi = EPI_STORE;
+        return launch_matmul_tc(&g, 1, (int) n_vec, m->stream, &m->scratch);
     };
     for (size_t c = 0; c < m->copies.size() && err == cudaSuccess; c++) err = one(c);
     cudaEventRecord(e0, m->stream);
@@ -490,9 +491,9 @@ bool rwkv_b200_matrix_bench(struct rwkv_b200_matrix * m, size_t n_vec, int iters
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaError_t err = cudaSuccess;
     auto one = [&](size_t c) {
-        GemvBatch b; b.T = (int) n_vec; b.n_jobs = 1;
+        MatvecBatch b; b.T = (int) n_vec; b.n_jobs = 1;
         b.job[0].W = m->copies[c % m->copies.size()]; b.job[0].x = m->x; b.job[0].out = m->y; b.job[0].ldo = (int) W0.M; b.job[0].epi = EPI_STORE;
-        return launch_gemv(b, m->stream);
+        return launch_matvec(b, m->stream);
     };
     for (size_t c = 0; c < m->copies.size() && err == cudaSuccess; c++) err = one(c);     // warm-up, touches every copy
     cudaEventRecord(e0, m->stream);

@@ -162,7 +162,7 @@ __global__ void dequant_kernel(DevMat W, OutT * __restrict__ out) {
 cudaError_t launch_dequant(const DevMat & W, float * out, cudaStream_t st) {
     const size_t n = (size_t) W.M * W.K;
     if (n == 0) return cudaSuccess;
-    const unsigned grid = (unsigned) std::min<size_t>((n + 255) / 256, 148 * 16);
+    const unsigned grid = (unsigned) std::min<size_t>((n + 255) / 256, (size_t) device_sm_count() * 16);
     dequant_kernel<float><<<grid, 256, 0, st>>>(W, out);
     return cudaGetLastError();
 }
@@ -170,7 +170,7 @@ cudaError_t launch_dequant(const DevMat & W, float * out, cudaStream_t st) {
 cudaError_t launch_dequant_f16(const DevMat & W, void * out_half, cudaStream_t st) {
     const size_t n = (size_t) W.M * W.K;
     if (n == 0) return cudaSuccess;
-    const unsigned grid = (unsigned) std::min<size_t>((n + 255) / 256, 148 * 16);
+    const unsigned grid = (unsigned) std::min<size_t>((n + 255) / 256, (size_t) device_sm_count() * 16);
     dequant_kernel<__half><<<grid, 256, 0, st>>>(W, (__half *) out_half);
     return cudaGetLastError();
 }

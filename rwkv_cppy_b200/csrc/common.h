@@ -98,7 +98,7 @@ struct DevMat {
     const void * qs = nullptr;
     uint32_t rg_stride = 0;                // bytes between row groups (quantised only)
     size_t bytes = 0;                      // algorithmic bytes of the matrix (file bytes)
-    // Second copy for the tensor-core GEMM (quantised only; null when not built): chunks of
+    // Second copy for the tensor-core MATMUL (quantised only; null when not built): chunks of
     // 128 rows x 64 weights (2 blocks), chunk (mt, kb) at (mt * tc_kblocks + kb) * 256 * block
     // bytes.  Inside a chunk, entry e = blk * 128 + row and three planes like the warp tile:
     // nibbles [256] x 16 B (Q8_0 32 B) | qh [256] x u32 (Q5, permuted) | scales [256] x half or half2.
@@ -109,6 +109,19 @@ struct DevMat {
 constexpr int TC_ROWS = 128, TC_KB = 64;
 inline size_t tc_chunk_bytes(uint32_t t) { return (size_t) 2 * TC_ROWS * type_block_bytes(t); }
 inline size_t tc_bytes(uint32_t t, size_t M, size_t K) { return ((M + TC_ROWS - 1) / TC_ROWS) * ((K + TC_KB - 1) / TC_KB) * tc_chunk_bytes(t); }
+
+// SM count of the current device (cudaDevAttrMultiProcessorCount, cached per device): grids and
+// split rules are sized against it instead of a literal 148.
+inline int device_sm_count() {
+    static std::atomic<int> cache[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int n = cache[dev].load(std::memory_order_relaxed);
+    if (n > 0) return n;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev].store(n, std::memory_order_relaxed);
+    return n;
+}
 
 #if defined(__CUDACC__)
 #define RB_HD __host__ __device__

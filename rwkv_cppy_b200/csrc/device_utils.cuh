@@ -117,7 +117,7 @@ __device__ __forceinline__ int q8_block(float v, bool valid, float & d16, float 
 // x86 quantize_row_q8_0/q8_1 produce it (ggml-cpu-quants.c:783-850, 1083-1150):
 //   d = amax/127 (stored as fp16), id = 127/amax, q = rint(v*id) (ties to even),
 //   s = fp16(d * sum q) with the unrounded d.
-// An Act may carry any subset of its forms: f (FP32), h (FP16 rows for the tensor-core GEMM),
+// An Act may carry any subset of its forms: f (FP32), h (FP16 rows for the tensor-core MATMUL),
 // q/d/s/isum (q8 blocks for the exact mat-vec); the producer writes the ones that are present.
 __device__ __forceinline__ void act_store_block(const Act & a, size_t row, int e, bool valid, float v) {
     if (valid && a.f) a.f[row * a.K + e] = v;

@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
     }
 }
 
-// Sequence rows whose consumers are all tensor-core GEMMs (FP16 outputs only: the tolerance-mode path).
+// Sequence rows whose consumers are all tensor-core MATMULs (FP16 outputs only: the tolerance-mode path).
 // CTA = RPC (4 or 8) consecutive rows, one warp per row with the row in registers (two-pass statistics in FP32, no
 // block-wide synchronisation), plus one more warp that normalises the row before the tile (or fetches the
 // shift state for the first row of the sequence).  The normalised rows meet in shared memory, so every
@@ -186,13 +186,26 @@ static cudaError_t launch_ln_mix_seq_n(const LnMixArgs & a, cudaStream_t st) {
     // 4 rows per CTA fill the SMs better for sequences up to a few thousand rows (25 % halo work instead of 12.5 %)
     constexpr int RPC = 4;
     const size_t smem = (size_t) (RPC + 1) * a.D * sizeof(float);
-    static bool attr_set = false;                             // per template instance; > 48 KB needs the opt-in
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(ln_mix_seq_kernel<N4, RPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (RPC + 1) * N4 * 128 * (int) sizeof(float));
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    // rows wider than 2400 floats need > 48 KB: opted in per device by elementwise_init() (called from model_load)
     return launch_pdl(ln_mix_seq_kernel<N4, RPC>, dim3((a.R + RPC - 1) / RPC), dim3((RPC + 1) * 32), smem, st, a);
+}
+
+template <int N4>
+static cudaError_t ln_mix_seq_attr() {
+    constexpr int RPC = 4;
+    return cudaFuncSetAttribute(ln_mix_seq_kernel<N4, RPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (RPC + 1) * N4 * 128 * (int) sizeof(float));
+}
+
+// Function attributes are per device: called once per model load on the model's device (outside stream capture).
+cudaError_t elementwise_init() {
+    cudaError_t e = ln_mix_seq_attr<2>();
+    if (e == cudaSuccess) e = ln_mix_seq_attr<4>();
+    if (e == cudaSuccess) e = ln_mix_seq_attr<6>();
+    if (e == cudaSuccess) e = ln_mix_seq_attr<8>();
+    if (e == cudaSuccess) e = ln_mix_seq_attr<12>();
+    if (e == cudaSuccess) e = ln_mix_seq_attr<16>();
+    if (e == cudaSuccess) e = ln_mix_seq_attr<20>();
+    return e;
 }
 
 static bool ln_mix_seq_ok(const LnMixArgs & a) {
@@ -231,7 +244,7 @@ cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
     }
     if (a.D <= LN_SMALL_D) {
         // Rows up to 2048 wide: 256 threads, element it*256 + tid.  The decode mat-vecs rebuild these
-        // rows in their prologue (gemv_async.cu) with the same thread shape, hence the same sums.
+        // rows in their prologue (matvec_q.cu) with the same thread shape, hence the same sums.
         const int items = (a.D + 255) / 256;
         if (items <= 1) return launch_ln_mix_i<1, 256>(a, 256, st);
         if (items <= 2) return launch_ln_mix_i<2, 256>(a, 256, st);

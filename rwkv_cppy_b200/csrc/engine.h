@@ -60,7 +60,7 @@ struct Workspace {
     float * r = nullptr, * k = nullptr, * v = nullptr, * g = nullptr, * w = nullptr, * a = nullptr, * vgate = nullptr;
     float * ffn_r = nullptr, * m5 = nullptr /* [5][rows][D] */, * v_first = nullptr;
     float * yraw = nullptr;       // [rows][D] raw WKV scan outputs (sequence kernels)
-    GemmScratch gemm_scratch;     // K-split partial tiles of the tensor-core GEMM
+    MatmulScratch matmul_scratch;     // K-split partial tiles of the tensor-core MATMUL
     float * wkv_ds = nullptr, * wkv_pc = nullptr;   // chunk-parallel WKV5/6 scratch (head size 64, rows on the tensor-core path)
     float * tp_send = nullptr, * tp_recv = nullptr;   // tensor parallel: [rows][2*D] all-reduce buffers of the ffn ([partial Wv k | r shards])
     float * tp_att = nullptr;                         // [rows][D] partial att output

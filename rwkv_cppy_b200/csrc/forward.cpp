@@ -24,7 +24,7 @@ bool dalloc(Workspace & ws, T *& p, size_t n) {
 bool act_alloc(Workspace & ws, Act & a, int rows, int K) {
     a.K = K;
     if (!dalloc(ws, a.f, (size_t) rows * K)) return false;
-    if (gemm_tc_enabled() && rows >= gemm_tc_min_rows(true) && !dalloc(ws, a.h, (size_t) rows * K)) return false;
+    if (matmul_tc_enabled() && rows >= matmul_tc_min_rows(true) && !dalloc(ws, a.h, (size_t) rows * K)) return false;
     if (K % 32 == 0) {
         const size_t nb = (size_t) rows * (K / 32);
         if (!dalloc(ws, a.q, (size_t) rows * K) || !dalloc(ws, a.d, nb) || !dalloc(ws, a.s, nb) || !dalloc(ws, a.isum, nb)) return false;
@@ -49,13 +49,13 @@ bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows
             && dalloc(ws, ws.a, n) && dalloc(ws, ws.vgate, n) && dalloc(ws, ws.ffn_r, n) && dalloc(ws, ws.v_first, n);
     if (m.arch_major == 6) ok = ok && dalloc(ws, ws.m5, 5 * n);
     if (m.arch_major >= 5 && rows >= WKV_SEQ_MIN_ROWS) ok = ok && dalloc(ws, ws.yraw, n);
-    ws.gemm_scratch = GemmScratch();
-    if (gemm_tc_enabled() && rows >= gemm_tc_min_rows(true)) {
-        ok = ok && dalloc(ws, ws.gemm_scratch.buf, GEMM_SCRATCH_FLOATS) && dalloc(ws, ws.gemm_scratch.flags, GEMM_SCRATCH_FLAGS);
-        ok = ok && cudaMemset(ws.gemm_scratch.flags, 0, GEMM_SCRATCH_FLAGS * sizeof(unsigned int)) == cudaSuccess;
-        if (ok) ws.gemm_scratch.floats = GEMM_SCRATCH_FLOATS;
+    ws.matmul_scratch = MatmulScratch();
+    if (matmul_tc_enabled() && rows >= matmul_tc_min_rows(true)) {
+        ok = ok && dalloc(ws, ws.matmul_scratch.buf, MATMUL_SCRATCH_FLOATS) && dalloc(ws, ws.matmul_scratch.flags, MATMUL_SCRATCH_FLAGS);
+        ok = ok && cudaMemset(ws.matmul_scratch.flags, 0, MATMUL_SCRATCH_FLAGS * sizeof(unsigned int)) == cudaSuccess;
+        if (ok) ws.matmul_scratch.floats = MATMUL_SCRATCH_FLOATS;
     }
-    if ((m.arch_major == 5 || m.arch_major == 6) && m.head_size == 64 && gemm_tc_enabled() && rows >= gemm_tc_min_rows()) {
+    if ((m.arch_major == 5 || m.arch_major == 6) && m.head_size == 64 && matmul_tc_enabled() && rows >= matmul_tc_min_rows()) {
         const size_t chunks = ((size_t) rows + WKV_CHUNK_TOKENS - 1) / WKV_CHUNK_TOKENS;
         ok = ok && dalloc(ws, ws.wkv_ds, chunks * D * 64) && dalloc(ws, ws.wkv_pc, chunks * D);
     }
@@ -84,31 +84,31 @@ struct Pass {
 
     void chk(cudaError_t e) { if (err == cudaSuccess && e != cudaSuccess) err = e; }
 
-    static GemvJob job(const DevMat & W, const Act & x, float * out, int ldo, int epi) {
-        GemvJob j; j.W = W; j.x = x; j.out = out; j.ldo = ldo; j.epi = epi; return j;
+    static MatvecJob job(const DevMat & W, const Act & x, float * out, int ldo, int epi) {
+        MatvecJob j; j.W = W; j.x = x; j.out = out; j.ldo = ldo; j.epi = epi; return j;
     }
-    // Acts last written by a tensor-core GEMM: their FP16 copy is current (value true) but their
+    // Acts last written by a tensor-core MATMUL: their FP16 copy is current (value true) but their
     // q8 blocks are stale.  Every other producer writes FP32 + q8.
     std::unordered_map<const float *, bool> tc_written;
 
     // launches the jobs grouped by weight type, `rows` rows each; wide row counts go to the
-    // tensor-core GEMM (FP16 operands), everything else to the exact mat-vec kernels
-    void gemv(std::vector<GemvJob> jobs, int rows, const GemvPrologue * pro = nullptr) {
+    // tensor-core MATMUL (FP16 operands), everything else to the exact mat-vec kernels
+    void matvec(std::vector<MatvecJob> jobs, int rows, const MatvecPrologue * pro = nullptr) {
         std::vector<bool> done(jobs.size(), false);
         // ---- tensor-core path ----
         for (size_t i = 0; i < jobs.size(); i++) {
             if (done[i] || !tc_job(jobs[i], rows)) continue;
-            GemmJob g[GEMM_MAX_JOBS]; int n = 0;
-            for (size_t k = i; k < jobs.size() && n < GEMM_MAX_JOBS; k++) {
+            MatmulJob g[MATMUL_MAX_JOBS]; int n = 0;
+            for (size_t k = i; k < jobs.size() && n < MATMUL_MAX_JOBS; k++) {
                 if (done[k] || jobs[k].W.type != jobs[i].W.type || !tc_job(jobs[k], rows)) continue;
-                const GemvJob & j = jobs[k];
+                const MatvecJob & j = jobs[k];
                 auto it = tc_written.find(j.x.f);
                 if (it == tc_written.end() || !it->second) {            // FP16 copy of the input rows
                     chk(launch_to_half(j.x.f, j.x.h, (size_t) rows * j.x.K, st));
                     tc_written[j.x.f] = true;                           // (q8 state of x is irrelevant from here on within this call)
                     to_half_marks.push_back(j.x.f);
                 }
-                GemmJob & o = g[n++];
+                MatmulJob & o = g[n++];
                 o.W = j.W; o.x16 = j.x.h + j.x_off; o.ldx = j.x.K;
                 o.out = j.out; o.ldo = j.ldo; o.epi = j.epi; o.aux = j.aux; o.ld_aux = j.ld_aux; o.vec = j.vec;
                 if (j.out_act.f) {
@@ -117,8 +117,8 @@ struct Pass {
                 }
                 done[k] = true;
             }
-            chk(launch_gemm_tc(g, n, rows, st, &ws.gemm_scratch));
-            // inputs converted for this launch keep a valid q8 form: only the marks of GEMM outputs persist
+            chk(launch_matmul_tc(g, n, rows, st, &ws.matmul_scratch));
+            // inputs converted for this launch keep a valid q8 form: only the marks of MATMUL outputs persist
             for (const float * p : to_half_marks) tc_written.erase(p);
             to_half_marks.clear();
             for (size_t k = i; k < jobs.size(); k++)
@@ -127,31 +127,31 @@ struct Pass {
         // ---- exact path ----
         for (size_t i = 0; i < jobs.size(); i++) {
             if (done[i]) continue;
-            GemvBatch b; b.T = rows;
+            MatvecBatch b; b.T = rows;
             if (pro) b.pro = *pro;
-            for (size_t k = i; k < jobs.size() && b.n_jobs < GEMV_MAX_JOBS; k++)
+            for (size_t k = i; k < jobs.size() && b.n_jobs < MATVEC_MAX_JOBS; k++)
                 if (!done[k] && jobs[k].W.type == jobs[i].W.type &&
-                    (!type_quantized(jobs[i].W.type) || gemv_ksplit(jobs[k].W.M, jobs[k].W.K) == gemv_ksplit(jobs[i].W.M, jobs[i].W.K))) {
-                    const GemvJob & j = jobs[k];
-                    if (type_quantized(j.W.type) && tc_written.count(j.x.f)) {   // produced by a GEMM: q8 blocks are stale
+                    (!type_quantized(jobs[i].W.type) || matvec_ksplit(jobs[k].W.M, jobs[k].W.K) == matvec_ksplit(jobs[i].W.M, jobs[i].W.K))) {
+                    const MatvecJob & j = jobs[k];
+                    if (type_quantized(j.W.type) && tc_written.count(j.x.f)) {   // produced by a MATMUL: q8 blocks are stale
                         Act a = j.x; a.h = nullptr; chk(launch_quantize_act(a, rows, st)); tc_written.erase(j.x.f);
                     }
                     if (j.out_act.f) tc_written.erase(j.out_act.f);
                     b.job[b.n_jobs] = j; b.job[b.n_jobs].out_act.h = nullptr; b.n_jobs++; done[k] = true;
                 }
-            chk(launch_gemv(b, st));
+            chk(launch_matvec(b, st));
         }
     }
     std::vector<const float *> to_half_marks;
-    bool tc_job(const GemvJob & j, int rows) const {
-        return j.x.h != nullptr && (j.x_off % 8) == 0 && (j.x.K % 8) == 0 && gemm_tc_supported(j.W, rows, fa.batch != 0);
+    bool tc_job(const MatvecJob & j, int rows) const {
+        return j.x.h != nullptr && (j.x_off % 8) == 0 && (j.x.K % 8) == 0 && matmul_tc_supported(j.W, rows, fa.batch != 0);
     }
-    // The form a producer should emit `a` in: when every consumer is a tensor-core GEMM the rows are
+    // The form a producer should emit `a` in: when every consumer is a tensor-core MATMUL the rows are
     // written once as FP16 (no FP32 rows, no q8 blocks, no conversion launch); otherwise FP32 + q8.
     Act produced(const Act & a, std::initializer_list<const DevMat *> consumers, int rows = -1) {
         if (rows < 0) rows = R;
         bool all_tc = a.h != nullptr && (a.K % 8) == 0 && consumers.size() > 0;
-        for (const DevMat * W : consumers) all_tc = all_tc && gemm_tc_supported(*W, rows, fa.batch != 0);
+        for (const DevMat * W : consumers) all_tc = all_tc && matmul_tc_supported(*W, rows, fa.batch != 0);
         Act o = a;
         if (all_tc) { o.f = nullptr; o.q = nullptr; o.d = nullptr; o.s = nullptr; o.isum = nullptr; tc_written[a.f] = true; }
         else        { o.h = nullptr; tc_written.erase(a.f); }
@@ -170,9 +170,9 @@ struct Pass {
         for (const DevMat * W : mats) if (!type_quantized(W->type) || W->K != D) return false;
         return true;
     }
-    GemvPrologue ln_prologue(uint32_t layer, bool att, int kind) const {
+    MatvecPrologue ln_prologue(uint32_t layer, bool att, int kind) const {
         const LayerW & l = m.layers[layer];
-        GemvPrologue P;
+        MatvecPrologue P;
         P.kind = PRO_LNMIX; P.D = (int) D; P.mix_kind = kind;
         P.x = ws.x; P.ln_w = att ? l.ln1_w : l.ln2_w; P.ln_b = att ? l.ln1_b : l.ln2_b;
         const size_t slot = att ? D : 0;
@@ -206,7 +206,7 @@ struct Pass {
         a.r = ws.r; a.k = ws.k; a.v = ws.v; a.y = produced(ws.y, {&m.layers[layer].att_output}); a.layer = (int) layer; a.yraw = ws.yraw;
         // rows whose projections run on the tensor cores (FP16 operands) are in tolerance mode anyway:
         // their v5 / v6 recurrence takes the chunk-parallel form; exact-path rows keep the serial order
-        if (!fa.batch && ws.wkv_ds && gemm_tc_supported(m.layers[layer].att_output, R)) { a.chunk_ds = ws.wkv_ds; a.chunk_pc = ws.wkv_pc; }
+        if (!fa.batch && ws.wkv_ds && matmul_tc_supported(m.layers[layer].att_output, R)) { a.chunk_ds = ws.wkv_ds; a.chunk_pc = ws.wkv_pc; }
         return a;
     }
 
@@ -218,7 +218,7 @@ struct Pass {
         const LayerW & l = m.layers[layer];
         const int Dl = (int) l.att_key.M;
         ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false);
-        gemv({job(l.att_key, ws.mix[0], ws.k, Dl, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, Dl, EPI_STORE),
+        matvec({job(l.att_key, ws.mix[0], ws.k, Dl, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, Dl, EPI_STORE),
               job(l.att_receptance, ws.mix[2], ws.r, Dl, EPI_SIGMOID)}, R);
         WkvArgs a = wkv_base(layer);
         a.D = Dl; a.state_D = (int) D; a.chan0 = m.tp.rank * Dl;
@@ -226,9 +226,9 @@ struct Pass {
         a.u = l.time_first; a.decay = l.time_decay;
         chk(launch_wkv4(a, st));
         Act yl = ws.y; yl.K = Dl;
-        GemvJob o = job(l.att_output, yl, ws.tp_att, (int) D, m.tp.rank == 0 ? EPI_ADD_AUX : EPI_STORE);   // rank 0 carries the residual
+        MatvecJob o = job(l.att_output, yl, ws.tp_att, (int) D, m.tp.rank == 0 ? EPI_ADD_AUX : EPI_STORE);   // rank 0 carries the residual
         o.aux = ws.x; o.ld_aux = (int) D;
-        gemv({o}, R);
+        matvec({o}, R);
         tp_all_reduce(ws.tp_att, ws.x, (size_t) R * D);
     }
 
@@ -236,12 +236,12 @@ struct Pass {
         const LayerW & l = m.layers[layer];
         const int Fl = (int) l.ffn_key.M, Dl = (int) l.ffn_receptance.M;
         ln_mix(layer, false, MIX_LERP, 2, l.ffn_mu, false);
-        GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = Fl;
+        MatvecJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = Fl;
         // this rank's slice of r goes straight into the second half of the send buffer (zero elsewhere)
-        GemvJob r = job(l.ffn_receptance, ws.mix[1], ws.tp_send + D + (size_t) m.tp.rank * Dl, 2 * (int) D, EPI_SIGMOID);
-        gemv({k, r}, R);
+        MatvecJob r = job(l.ffn_receptance, ws.mix[1], ws.tp_send + D + (size_t) m.tp.rank * Dl, 2 * (int) D, EPI_SIGMOID);
+        matvec({k, r}, R);
         Act kin = ws.ffn_k; kin.K = Fl;
-        gemv({job(l.ffn_value, kin, ws.tp_send, 2 * (int) D, EPI_STORE)}, R);
+        matvec({job(l.ffn_value, kin, ws.tp_send, 2 * (int) D, EPI_STORE)}, R);
         tp_all_reduce(ws.tp_send, ws.tp_recv, (size_t) R * 2 * D);
         chk(launch_tp_ffn_combine(ws.x, ws.tp_recv, R, (int) D, st));
     }
@@ -250,86 +250,86 @@ struct Pass {
         const LayerW & l = m.layers[layer];
         if (m.tp.world > 1) { ffn_v4_tp(layer); return; }
         if (m.arch_major == 7) {
-            GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
+            MatvecJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
             if (can_fuse({&l.ffn_key})) {
-                const GemvPrologue P = ln_prologue(layer, false, MIX_SX);
+                const MatvecPrologue P = ln_prologue(layer, false, MIX_SX);
                 k.pro_mu = l.ffn_mu[0];
-                gemv({k}, R, &P);
+                matvec({k}, R, &P);
             } else {
                 const Act outs[1] = {produced(ws.mix[0], {&l.ffn_key})};
                 ln_mix(layer, false, MIX_SX, 1, l.ffn_mu, false, outs);
-                gemv({k}, R);
+                matvec({k}, R);
             }
             Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
-            gemv({job(l.ffn_value, kin, ws.x, (int) D, EPI_ADD_TO)}, R);
+            matvec({job(l.ffn_value, kin, ws.x, (int) D, EPI_ADD_TO)}, R);
             return;
         }
         const int kind = m.arch_major == 6 ? MIX_SX : MIX_LERP;
-        GemvJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
-        GemvJob r = job(l.ffn_receptance, ws.mix[1], ws.ffn_r, (int) D, EPI_SIGMOID);
+        MatvecJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
+        MatvecJob r = job(l.ffn_receptance, ws.mix[1], ws.ffn_r, (int) D, EPI_SIGMOID);
         if (can_fuse({&l.ffn_key, &l.ffn_receptance})) {
-            const GemvPrologue P = ln_prologue(layer, false, kind);
+            const MatvecPrologue P = ln_prologue(layer, false, kind);
             k.pro_mu = l.ffn_mu[0]; r.pro_mu = l.ffn_mu[1];
-            gemv({k, r}, R, &P);
+            matvec({k, r}, R, &P);
         } else {
             const Act outs[2] = {produced(ws.mix[0], {&l.ffn_key}), produced(ws.mix[1], {&l.ffn_receptance})};
             ln_mix(layer, false, kind, 2, l.ffn_mu, false, outs);
-            gemv({k, r}, R);
+            matvec({k, r}, R);
         }
         Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
-        GemvJob v = job(l.ffn_value, kin, ws.x, (int) D, EPI_MULADD_TO); v.aux = ws.ffn_r; v.ld_aux = (int) D;
-        gemv({v}, R);
+        MatvecJob v = job(l.ffn_value, kin, ws.x, (int) D, EPI_MULADD_TO); v.aux = ws.ffn_r; v.ld_aux = (int) D;
+        matvec({v}, R);
     }
 
     void att_v4(uint32_t layer) {
         const LayerW & l = m.layers[layer];
-        std::vector<GemvJob> kvr = {job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
+        std::vector<MatvecJob> kvr = {job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
                                     job(l.att_receptance, ws.mix[2], ws.r, (int) D, EPI_SIGMOID)};
         if (can_fuse({&l.att_key, &l.att_value, &l.att_receptance})) {
-            const GemvPrologue P = ln_prologue(layer, true, MIX_LERP);
+            const MatvecPrologue P = ln_prologue(layer, true, MIX_LERP);
             for (int i = 0; i < 3; i++) kvr[i].pro_mu = l.att_mu[i];
-            gemv(kvr, R, &P);
+            matvec(kvr, R, &P);
         } else {
             const Act outs[3] = {produced(ws.mix[0], {&l.att_key}), produced(ws.mix[1], {&l.att_value}), produced(ws.mix[2], {&l.att_receptance})};
             ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false, outs);
-            gemv(kvr, R);
+            matvec(kvr, R);
         }
         WkvArgs a = wkv_base(layer);
         a.u = l.time_first; a.decay = l.time_decay;
-        GemvJob o = job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO);
+        MatvecJob o = job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO);
         if (can_fuse({&l.att_output})) {
-            GemvPrologue P;
+            MatvecPrologue P;
             P.kind = PRO_WKV4; P.D = (int) D;
             P.k = ws.k; P.v = ws.v; P.r = ws.r; P.u = a.u; P.decay = a.decay;
             P.state_in = a.state_in; P.state_out = a.state_out;
-            gemv({o}, R, &P);
+            matvec({o}, R, &P);
         } else {
             chk(launch_wkv4(a, st));
-            gemv({o}, R);
+            matvec({o}, R);
         }
     }
 
     void att_v5(uint32_t layer) {
         const LayerW & l = m.layers[layer];
         const bool gate = m.arch_minor >= 2;
-        std::vector<GemvJob> jobs = {job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
+        std::vector<MatvecJob> jobs = {job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
                                      job(l.att_receptance, ws.mix[2], ws.r, (int) D, EPI_STORE)};
         if (gate) jobs.push_back(job(l.att_gate, ws.mix[3], ws.g, (int) D, EPI_SILU));
         if (gate ? can_fuse({&l.att_key, &l.att_value, &l.att_receptance, &l.att_gate}) : can_fuse({&l.att_key, &l.att_value, &l.att_receptance})) {
-            const GemvPrologue P = ln_prologue(layer, true, MIX_LERP);
+            const MatvecPrologue P = ln_prologue(layer, true, MIX_LERP);
             for (size_t i = 0; i < jobs.size(); i++) jobs[i].pro_mu = l.att_mu[i];
-            gemv(jobs, R, &P);
+            matvec(jobs, R, &P);
         } else {
             const Act outs[4] = {produced(ws.mix[0], {&l.att_key}), produced(ws.mix[1], {&l.att_value}), produced(ws.mix[2], {&l.att_receptance}),
                                  gate ? produced(ws.mix[3], {&l.att_gate}) : Act()};
             ln_mix(layer, true, MIX_LERP, gate ? 4 : 3, l.att_mu, false, outs);
-            gemv(jobs, R);
+            matvec(jobs, R);
         }
         WkvArgs a = wkv_base(layer);
         a.u = l.time_first; a.decay = l.time_decay; a.per_head_scalar = gate ? 0 : 1;
         a.g = gate ? ws.g : nullptr; a.lnx_w = l.lnx_w; a.lnx_b = l.lnx_b; a.gn_eps = 1e-5f;
         chk(launch_wkv5(a, st));
-        gemv({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
+        matvec({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
     }
 
     void att_v6(uint32_t layer) {
@@ -337,14 +337,14 @@ struct Pass {
         const Act xxx[1] = {produced(ws.mix[0], {&l.maa_w1})};
         ln_mix(layer, true, MIX_SX, 1, l.att_mu, true, xxx);                 // xxx = x + sx*maa_x
         const int E5 = (int) l.maa_w1.M, E = E5 / 5;
-        GemvJob j1 = job(l.maa_w1, ws.mix[0], nullptr, 0, EPI_TANH);
+        MatvecJob j1 = job(l.maa_w1, ws.mix[0], nullptr, 0, EPI_TANH);
         j1.out_act = ws.lora[0]; j1.out_act.K = E5;
         if (E5 % 32 != 0) { j1.out = ws.lora[0].f; j1.ldo = E5; j1.out_act = Act(); }
-        gemv({j1}, R);
+        matvec({j1}, R);
         Act t5 = ws.lora[0]; t5.K = E5; if (E5 % 32 != 0) t5.q = nullptr;
         V6Mix2Args mx; mx.x0 = ws.x0; mx.sx = ws.sx; mx.R = R; mx.D = (int) D;
         const DevMat * cons5[5] = {&l.decay_w1, &l.att_key, &l.att_value, &l.att_receptance, &l.att_gate};
-        bool fold = E == 32 && D % 2 == 0 && ws.lora[0].f != nullptr;          // all five mixes feed tensor-core GEMMs: fold the rank-32 stage in
+        bool fold = E == 32 && D % 2 == 0 && ws.lora[0].f != nullptr;          // all five mixes feed tensor-core MATMULs: fold the rank-32 stage in
         for (int n = 0; n < 5; n++) {
             mx.m[n] = ws.m5 + (size_t) n * R * D; mx.maa[n] = l.att_mu[1 + n]; mx.out[n] = produced(ws.mix[1 + n], {cons5[n]});
             fold = fold && mx.out[n].f == nullptr && mx.out[n].h != nullptr && l.maa_w2[n].type == T_F32 && l.maa_w2[n].K == 32;
@@ -354,23 +354,23 @@ struct Pass {
             for (int n = 0; n < 5; n++) { ml.w2[n] = (const float *) l.maa_w2[n].qs; ml.maa[n] = l.att_mu[1 + n]; ml.out_h[n] = mx.out[n].h; }
             chk(launch_v6_mix_lora(ml, st));
         } else {
-            std::vector<GemvJob> jobs;
-            for (int n = 0; n < 5; n++) { GemvJob j = job(l.maa_w2[n], t5, ws.m5 + (size_t) n * R * D, (int) D, EPI_STORE); j.x_off = n * E; jobs.push_back(j); }
-            gemv(jobs, R);
+            std::vector<MatvecJob> jobs;
+            for (int n = 0; n < 5; n++) { MatvecJob j = job(l.maa_w2[n], t5, ws.m5 + (size_t) n * R * D, (int) D, EPI_STORE); j.x_off = n * E; jobs.push_back(j); }
+            matvec(jobs, R);
             chk(launch_v6_mix2(mx, st));                                      // mix[1..5] = xw, xk, xv, xr, xg
         }
         const int DW = (int) l.decay_w1.M;
-        GemvJob jd = job(l.decay_w1, ws.mix[1], nullptr, 0, EPI_TANH); jd.out_act = ws.lora[1]; jd.out_act.K = DW;
+        MatvecJob jd = job(l.decay_w1, ws.mix[1], nullptr, 0, EPI_TANH); jd.out_act = ws.lora[1]; jd.out_act.K = DW;
         if (DW % 32 != 0) { jd.out = ws.lora[1].f; jd.ldo = DW; jd.out_act = Act(); }
-        gemv({job(l.att_key, ws.mix[2], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[3], ws.v, (int) D, EPI_STORE),
+        matvec({job(l.att_key, ws.mix[2], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[3], ws.v, (int) D, EPI_STORE),
               job(l.att_receptance, ws.mix[4], ws.r, (int) D, EPI_STORE), job(l.att_gate, ws.mix[5], ws.g, (int) D, EPI_SILU), jd}, R);
         Act td = ws.lora[1]; td.K = DW; if (DW % 32 != 0) td.q = nullptr;
-        GemvJob jw = job(l.decay_w2, td, ws.w, (int) D, EPI_V6_DECAY); jw.vec = l.time_decay;
-        gemv({jw}, R);
+        MatvecJob jw = job(l.decay_w2, td, ws.w, (int) D, EPI_V6_DECAY); jw.vec = l.time_decay;
+        matvec({jw}, R);
         WkvArgs a = wkv_base(layer);
         a.u = l.time_first; a.w = ws.w; a.g = ws.g; a.lnx_w = l.lnx_w; a.lnx_b = l.lnx_b; a.gn_eps = 64e-5f;
         chk(launch_wkv5(a, st));
-        gemv({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
+        matvec({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
     }
 
     void att_v7(uint32_t layer) {
@@ -382,34 +382,34 @@ struct Pass {
         // low-rank pairs (never quantised).  Wide row counts chain the two stages on the tensor cores: the first
         // stage then also leaves an FP16 copy of its rows for the second (no q8 form: the second stage is FP16 / FP32).
         auto lora_tc = [&](const DevMat & W1, const DevMat & W2) {
-            return ws.lora[0].h != nullptr && W1.M % 8 == 0 && gemm_tc_supported(W1, R, fa.batch != 0) && gemm_tc_supported(W2, R, fa.batch != 0);
+            return ws.lora[0].h != nullptr && W1.M % 8 == 0 && matmul_tc_supported(W1, R, fa.batch != 0) && matmul_tc_supported(W2, R, fa.batch != 0);
         };
         const DevMat * second[4] = {&l.w2, &l.a2, &l.g2, &l.v2};
         auto lora_in = [&](int slot, const DevMat & W, int epi) {
-            GemvJob j = job(W, ws.mix[slot == 0 ? 1 : slot == 1 ? 4 : slot == 2 ? 5 : 3], nullptr, 0, epi);
+            MatvecJob j = job(W, ws.mix[slot == 0 ? 1 : slot == 1 ? 4 : slot == 2 ? 5 : 3], nullptr, 0, epi);
             if (lora_tc(W, *second[slot])) { j.out_act.f = ws.lora[slot].f; j.out_act.h = ws.lora[slot].h; j.out_act.K = (int) W.M; }
             else { j.out = ws.lora[slot].f; j.ldo = (int) W.M; tc_written.erase(ws.lora[slot].f); }
             return j;
         };
-        std::vector<GemvJob> jobs = {job(l.att_receptance, ws.mix[0], ws.r, (int) D, EPI_STORE), job(l.att_key, ws.mix[2], ws.k, (int) D, EPI_STORE),
+        std::vector<MatvecJob> jobs = {job(l.att_receptance, ws.mix[0], ws.r, (int) D, EPI_STORE), job(l.att_key, ws.mix[2], ws.k, (int) D, EPI_STORE),
                                      job(l.att_value, ws.mix[3], ws.v, (int) D, EPI_STORE),
                                      lora_in(0, l.w1, EPI_TANH), lora_in(1, l.a1, EPI_STORE), lora_in(2, l.g1, EPI_SIGMOID)};
         if (layer != 0) jobs.push_back(lora_in(3, l.v1, EPI_STORE));
-        gemv(jobs, R);
+        matvec(jobs, R);
         auto lora_out = [&](int slot, const DevMat & W, float * out, int epi, const float * vec) {
             Act x; x.f = ws.lora[slot].f; x.K = (int) W.K;
             if (tc_written.count(ws.lora[slot].f)) x.h = ws.lora[slot].h;     // first stage ran on the tensor cores and left FP16 rows
-            GemvJob j = job(W, x, out, (int) D, epi); j.vec = vec;
+            MatvecJob j = job(W, x, out, (int) D, epi); j.vec = vec;
             return j;
         };
         jobs = {lora_out(0, l.w2, ws.w, EPI_V7_DECAY, l.w0), lora_out(1, l.a2, ws.a, EPI_BIAS_SIGMOID, l.a0), lora_out(2, l.g2, ws.g, EPI_STORE, nullptr)};
         if (layer != 0) jobs.push_back(lora_out(3, l.v2, ws.vgate, EPI_BIAS_SIGMOID, l.v0));
-        gemv(jobs, R);
+        matvec(jobs, R);
         WkvArgs a = wkv_base(layer);
         a.w = ws.w; a.a = ws.a; a.g = ws.g; a.vgate = ws.vgate; a.v_first = ws.v_first;
         a.k_k = l.k_k; a.k_a = l.k_a; a.r_k = l.r_k; a.lnx_w = l.lnx_w; a.lnx_b = l.lnx_b; a.gn_eps = 64e-5f;
         chk(launch_wkv7(a, st));
-        gemv({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
+        matvec({job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO)}, R);
     }
 
     void run() {
@@ -429,11 +429,11 @@ struct Pass {
             chk(launch_ln_act(x, (int) D, rows, (int) D, m.ln_out_w, m.ln_out_b, produced(ws.head_in, {&m.head}, rows), st));
             if (m.tp.world > 1) {      // vocabulary rows are sharded: gather the slices (equal-sized, zero-padded at the end)
                 const int Vl = (int) ((m.n_vocab + m.tp.world - 1) / m.tp.world);
-                gemv({job(m.head, ws.head_in, ws.logits_part, Vl, EPI_STORE)}, rows);
+                matvec({job(m.head, ws.head_in, ws.logits_part, Vl, EPI_STORE)}, rows);
                 if (rows == 1) chk(tp_allgather(m.tp, ws.logits_part, ws.logits, (size_t) Vl, st));
                 else err = err == cudaSuccess ? cudaErrorNotSupported : err;     // batched logits under TP: not needed by any caller yet
             } else
-            gemv({job(m.head, ws.head_in, ws.logits, (int) m.n_vocab, EPI_STORE)}, rows);
+            matvec({job(m.head, ws.head_in, ws.logits, (int) m.n_vocab, EPI_STORE)}, rows);
         }
     }
 };

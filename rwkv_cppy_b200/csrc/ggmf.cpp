@@ -91,6 +91,14 @@ bool ggmf_open(const char * path, GgmfFile & f) {
         RB_CHECK(c.left >= key_len, RWKV_ERROR_MODEL_PARAMS | RWKV_ERROR_KEY, false, "Failed to read a parameter name");
         t.name.assign((const char *) c.p, key_len);
         c.skip(key_len);
+        // three unchecked 32-bit dimensions: their product must not wrap (a crafted header would otherwise
+        // pass the size check below with a small nbytes while the loader copies ne[1]*ne[2] rows)
+        {
+            const unsigned __int128 n128 = (unsigned __int128) t.ne[0] * t.ne[1] * t.ne[2];
+            RB_CHECK(t.ne[0] > 0 && t.ne[1] > 0 && t.ne[2] > 0 && n128 <= (unsigned __int128) f.map_size * 32, RWKV_ERROR_MODEL_PARAMS | RWKV_ERROR_SHAPE, false,
+                     "Tensor %s: dimensions (%llu, %llu, %llu) do not fit the file", t.name.c_str(), (unsigned long long) t.ne[0],
+                     (unsigned long long) t.ne[1], (unsigned long long) t.ne[2]);
+        }
         // rwkv_utilities.inc:1-4: nbytes = type_size * n / block
         RB_CHECK(t.ne[0] % type_block(t.type) == 0, RWKV_ERROR_MODEL_PARAMS | RWKV_ERROR_SHAPE, false,
                  "Tensor %s: row length %llu is not a multiple of the block size", t.name.c_str(), (unsigned long long) t.ne[0]);

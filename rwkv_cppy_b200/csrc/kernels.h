@@ -11,7 +11,7 @@ namespace rb {
 //   d    fp16-rounded scale per block   } (quantize_row_q8_0 / q8_1 as compiled for x86,
 //   s    fp16-rounded d*sum(q) (q8_1)   }  ggml-cpu-quants.c:783-850,1083-1150), split into
 //   isum sum(q) per block (int)         }  planes.  q == nullptr when K % 32 != 0.
-//   h    FP16 copy [T][K] for the tensor-core GEMM (optional; filled on demand)
+//   h    FP16 copy [T][K] for the tensor-core MATMUL (optional; filled on demand)
 struct Act {
     float *  f = nullptr;
     int8_t * q = nullptr;
@@ -36,7 +36,7 @@ enum Epilogue : int {
     EPI_ADD_AUX,         // out = aux[t][m] + y                 (tensor parallel: rank 0 folds the residual into its partial sum)
 };
 
-struct GemvJob {
+struct MatvecJob {
     DevMat        W;
     Act           x;                  // input rows, T of them (x.K == W.K)
     int           x_off = 0;          // element offset into each input row (slices of a wider row)
@@ -60,18 +60,18 @@ struct GemvJob {
 // reduction order, same q8 blocks).
 constexpr int LN_SMALL_D = 2048;
 enum PrologueKind : int { PRO_NONE = 0, PRO_LNMIX = 1, PRO_WKV4 = 2 };
-struct GemvPrologue {
+struct MatvecPrologue {
     int kind = PRO_NONE, D = 0, mix_kind = 0;
     const float * x = nullptr, * ln_w = nullptr, * ln_b = nullptr;          // PRO_LNMIX
     const float * k = nullptr, * v = nullptr, * r = nullptr, * u = nullptr, * decay = nullptr;   // PRO_WKV4
     const float * state_in = nullptr; float * state_out = nullptr;          // shift slot (LNMIX) / aa slot (WKV4; bb, pp follow at +D, +2D)
 };
 
-constexpr int GEMV_MAX_JOBS = 8;
-struct GemvBatch {
-    GemvPrologue pro;
-    GemvJob job[GEMV_MAX_JOBS];
-    int     cta_begin[GEMV_MAX_JOBS + 1];   // prefix sum of CTAs per job (filled by launch_gemv)
+constexpr int MATVEC_MAX_JOBS = 8;
+struct MatvecBatch {
+    MatvecPrologue pro;
+    MatvecJob job[MATVEC_MAX_JOBS];
+    int     cta_begin[MATVEC_MAX_JOBS + 1];   // prefix sum of CTAs per job (filled by launch_matvec)
     int     n_jobs = 0;
     int     T = 1;
     int     ks = 1;                         // K split (cluster size along x) of the quantised kernel; all jobs of a batch share it
@@ -80,23 +80,25 @@ struct GemvBatch {
 // of the same matrix adds its partial sums in the same order.  Splits while the row blocks alone
 // would leave most SMs idle and every CTA keeps at least five 1024-weight chunks (below that the
 // fixed cost of a CTA outweighs the extra parallelism: measured on 5120x5120 vs 5120x20480).
-inline int gemv_ksplit(uint32_t M, uint32_t K) {
+inline int matvec_ksplit(uint32_t M, uint32_t K) {
     const int row_blocks = (int) ((M + 31) / 32), nch = (int) ((K / 32 + TILE_BLOCKS - 1) / TILE_BLOCKS);
     int ks = 1;
-    while (row_blocks * ks < 3 * 148 && ks < 4 && nch / (ks * 2) >= 5) ks *= 2;
+    while (row_blocks * ks < 3 * device_sm_count() && ks < 4 && nch / (ks * 2) >= 5) ks *= 2;
     return ks;
 }
 
 // All jobs of a batch must have the same weight type.
-cudaError_t launch_gemv(const GemvBatch & b, cudaStream_t st);
+cudaError_t launch_matvec(const MatvecBatch & b, cudaStream_t st);
 // once per device, outside stream capture (opts the bulk-async kernel in to > 48 KB shared memory)
-cudaError_t gemv_async_init();
+cudaError_t matvec_async_init();
+cudaError_t wkv_init();            // same for the WKV scan kernels
+cudaError_t elementwise_init();    // and the sequence layer-norm kernel
 
-// ---- tensor-core GEMM (sequence mode / wide batches; gemm_tc.cu) ----------------------------
+// ---- tensor-core MATMUL (sequence mode / wide batches; matmul_tc.cu) ----------------------------
 // out[T][M] = epi(X[T][K] * W[M][K]^T) with FP16 operands (quantised weights dequantised to FP16
 // on the fly) and FP32 accumulation on tcgen05 / TMEM.  Same epilogues as the mat-vec jobs.
-constexpr int GEMM_MAX_JOBS = 6;
-struct GemmJob {
+constexpr int MATMUL_MAX_JOBS = 6;
+struct MatmulJob {
     DevMat           W;                 // quantised (needs W.tc) or T_F16
     const uint16_t * x16 = nullptr;     // FP16 activations, T rows of W.K values, row stride ldx
     int              ldx = 0;
@@ -104,19 +106,19 @@ struct GemmJob {
     int              epi = EPI_STORE;
     const float *    aux = nullptr; int ld_aux = 0;
     const float *    vec = nullptr;
-    uint16_t *       out_h = nullptr; int ld_h = 0;   // optional FP16 copy of the result (input of a chained GEMM)
+    uint16_t *       out_h = nullptr; int ld_h = 0;   // optional FP16 copy of the result (input of a chained MATMUL)
 };
-bool gemm_tc_enabled();                                // driver entry point found and RWKV_B200_NO_TC != 1
+bool matmul_tc_enabled();                                // driver entry point found and RWKV_B200_NO_TC != 1
 // smallest row count that takes the tensor path: 64 tokens of a sequence, 32 streams of a batch (a batch step re-reads every
 // weight whatever its width, so the tensor path pays earlier: 32 v7-2.9B streams 7.74 -> 5.99 ms); RWKV_B200_TC_MIN_ROWS sets both
-int  gemm_tc_min_rows(bool batch = false);
-bool gemm_tc_supported(const DevMat & W, int T, bool batch = false);
-cudaError_t gemm_tc_init();                            // once per device, outside stream capture
-// Scratch of the K-split launches (per context: one GEMM at a time per stream): raw partial tiles + one flag per
+int  matmul_tc_min_rows(bool batch = false);
+bool matmul_tc_supported(const DevMat & W, int T, bool batch = false);
+cudaError_t matmul_tc_init();                            // once per device, outside stream capture
+// Scratch of the K-split launches (per context: one MATMUL at a time per stream): raw partial tiles + one flag per
 // (tile, epilogue warp), zero-initialised.  Without it every launch keeps whole K loops per CTA.
-struct GemmScratch { float * buf = nullptr; unsigned int * flags = nullptr; size_t floats = 0; };
-constexpr size_t GEMM_SCRATCH_FLOATS = (size_t) 74 * 256 * 128, GEMM_SCRATCH_FLAGS = 74 * 8;
-cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t st, const GemmScratch * scratch = nullptr);   // all jobs share one weight type
+struct MatmulScratch { float * buf = nullptr; unsigned int * flags = nullptr; size_t floats = 0; };
+constexpr size_t MATMUL_SCRATCH_FLOATS = (size_t) 74 * 256 * 128, MATMUL_SCRATCH_FLAGS = 74 * 8;
+cudaError_t launch_matmul_tc(const MatmulJob * jobs, int n_jobs, int T, cudaStream_t st, const MatmulScratch * scratch = nullptr);   // all jobs share one weight type
 cudaError_t launch_to_half(const float * x, uint16_t * out, size_t n, cudaStream_t st);  // n % 4 == 0
 
 // ---- codec -----------------------------------------------------------------------------
@@ -126,7 +128,7 @@ cudaError_t launch_repack(uint32_t type, const uint8_t * raw, size_t M, size_t K
 cudaError_t launch_repack_tc(uint32_t type, const uint8_t * raw, size_t M, size_t K, void * out, cudaStream_t st);
 // device layout -> FP32 [M][K]; bit-exact dequantize_row_* (ggml-quants.c:255-363)
 cudaError_t launch_dequant(const DevMat & W, float * out, cudaStream_t st);
-// device layout -> FP16 [M][K] (operand of the tensor-core sequence GEMM)
+// device layout -> FP16 [M][K] (operand of the tensor-core sequence MATMUL)
 cudaError_t launch_dequant_f16(const DevMat & W, void * out_half, cudaStream_t st);
 
 // ---- embedding + ln0 --------------------------------------------------------------------
@@ -187,7 +189,7 @@ struct WkvArgs {
     Act   y;                              // output rows
     float * yraw = nullptr;               // [R][D] scratch: raw scan outputs of the sequence kernels (before the head norm)
     // chunk-parallel form (wkv_chunk.cu): scratch for ceil(R/16) chunks, [H][chunks][S][S] and [H][chunks][S];
-    // both set => long sequences of head-size-64 models take it (tolerance mode, like the tensor-core GEMM)
+    // both set => long sequences of head-size-64 models take it (tolerance mode, like the tensor-core MATMUL)
     float * chunk_ds = nullptr, * chunk_pc = nullptr;
 };
 constexpr int WKV_SEQ_MIN_ROWS = 8;       // sequences at least this long use the scan kernels (same arithmetic, different work split)

@@ -1,10 +1,10 @@
-// Tensor-core GEMM for sequence mode and wide batches: out[T][M] = epi(X[T][K] * W[M][K]^T).
+// Tensor-core MATMUL for sequence mode and wide batches: out[T][M] = epi(X[T][K] * W[M][K]^T).
 //
 // Replaces the same ggml_mul_mat nodes as the mat-vec kernels (rwkv_graph.inc block builders),
 // for T >= 64 rows where the product is a dense contraction.  Arithmetic: weights dequantised
 // to FP16 with ONE rounding (w16 = fp16(q*d + m), HFMA2 / HMUL2), activations rounded to FP16,
 // products exact, FP32 accumulation in tensor memory -- the numerics of the reference's own
-// GPU offload path (dequantise-to-FP16 + FP16 GEMM), not of its CPU path; FP32 files never
+// GPU offload path (dequantise-to-FP16 + FP16 MATMUL), not of its CPU path; FP32 files never
 // take this path.
 //
 // Structure (one persistent CTA per SM, 18 warps, tiles of 128 weight rows x BN tokens):
@@ -17,9 +17,9 @@
 //               stage, accumulator in TMEM (double buffered: 2 x BN columns), and commits the
 //               stage / the accumulator to mbarriers;
 //   warps 2-9   epilogue: tcgen05.ld 32 lanes x 32 columns, the same fused epilogues as the
-//               mat-vec kernels, coalesced FP32 stores (+ optional FP16 copy for a chained GEMM).
+//               mat-vec kernels, coalesced FP32 stores (+ optional FP16 copy for a chained MATMUL).
 // FP16 weight matrices (FP16 files, head) skip the dequantisers: the A tile is a second TMA load.
-#include "gemv_common.cuh"
+#include "matvec_common.cuh"
 #include "launch.cuh"
 #include "ptx.cuh"
 
@@ -47,7 +47,7 @@ struct GtJob {
     int tile_begin, m_tiles;
 };
 struct GtBatch {
-    GtJob job[GEMM_MAX_JOBS];
+    GtJob job[MATMUL_MAX_JOBS];
     int n_jobs, T, n_tiles, total_tiles;
     // K split (ks = 2): CTAs 2c and 2c+1 share output tile(s) c, c + gridDim/2, ...; the odd CTA takes the upper half of
     // K, leaves its raw accumulators in `scratch` ([tile][BN tokens][128 rows] FP32) and raises one flag per epilogue
@@ -169,7 +169,7 @@ __device__ __forceinline__ void epilogue_tile(const GtJob & J, uint32_t tcol, in
 
 template <int TYPE, int BN>
 __global__ void __launch_bounds__(GT_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ GtBatch B) {
+matmul_tc_kernel(const __grid_constant__ GtBatch B) {
     constexpr bool QUANT = (TYPE != T_F16);
     constexpr int S = gt_stages<BN>();
     constexpr int B_BYTES = BN * GT_BK * 2;
@@ -394,7 +394,7 @@ cudaError_t launch_to_half(const float * x, uint16_t * out, size_t n, cudaStream
     if (n == 0) return cudaSuccess;
     if (n % 4 != 0) return cudaErrorInvalidValue;
     const size_t n4 = n / 4;
-    const unsigned grid = (unsigned) std::min<size_t>((n4 + 255) / 256, 148 * 8);
+    const unsigned grid = (unsigned) std::min<size_t>((n4 + 255) / 256, (size_t) device_sm_count() * 8);
     return launch_pdl(to_half_kernel, dim3(grid), dim3(256), 0, st, x, reinterpret_cast<__half *>(out), n4);
 }
 
@@ -421,18 +421,18 @@ static bool make_map(CUtensorMap * map, const void * base, uint64_t cols, uint64
               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-bool gemm_tc_enabled() {
+bool matmul_tc_enabled() {
     static const bool on = [] { const char * e = getenv("RWKV_B200_NO_TC"); return !(e && e[0] == '1') && encode_fn() != nullptr; }();
     return on;
 }
 
-int gemm_tc_min_rows(bool batch) {
+int matmul_tc_min_rows(bool batch) {
     static const int v = [] { const char * e = getenv("RWKV_B200_TC_MIN_ROWS"); const int n = e ? atoi(e) : 0; return n > 0 ? n : 0; }();
     return v > 0 ? v : (batch ? 32 : 64);
 }
 
-bool gemm_tc_supported(const DevMat & W, int T, bool batch) {
-    if (!gemm_tc_enabled() || T < gemm_tc_min_rows(batch)) return false;
+bool matmul_tc_supported(const DevMat & W, int T, bool batch) {
+    if (!matmul_tc_enabled() || T < matmul_tc_min_rows(batch)) return false;
     if (W.K < 64 || W.K % 8 != 0) return false;
     if (W.type == T_F16) return true;
     return type_quantized(W.type) && W.tc != nullptr;
@@ -440,8 +440,9 @@ bool gemm_tc_supported(const DevMat & W, int T, bool batch) {
 
 template <int TYPE, int BN>
 static cudaError_t launch_gt(const GtBatch & b, cudaStream_t st) {
-    const int grid = b.ks > 1 ? 2 * std::min(b.total_tiles, 74) : std::min(b.total_tiles, 148);
-    return launch_pdl(gemm_tc_kernel<TYPE, BN>, dim3(grid), dim3(GT_THREADS), gt_smem_bytes<TYPE, BN>(), st, b);
+    const int nsm = device_sm_count();
+    const int grid = b.ks > 1 ? 2 * std::min(b.total_tiles, nsm / 2) : std::min(b.total_tiles, nsm);
+    return launch_pdl(matmul_tc_kernel<TYPE, BN>, dim3(grid), dim3(GT_THREADS), gt_smem_bytes<TYPE, BN>(), st, b);
 }
 template <int TYPE>
 static cudaError_t launch_gt_bn(const GtBatch & b, int BN, cudaStream_t st) {
@@ -450,15 +451,16 @@ static cudaError_t launch_gt_bn(const GtBatch & b, int BN, cudaStream_t st) {
     return launch_gt<TYPE, 64>(b, st);
 }
 
-cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t st, const GemmScratch * scratch) {
+cudaError_t launch_matmul_tc(const MatmulJob * jobs, int n_jobs, int T, cudaStream_t st, const MatmulScratch * scratch) {
     if (n_jobs <= 0) return cudaSuccess;
-    if (n_jobs > GEMM_MAX_JOBS) return cudaErrorInvalidValue;
+    if (n_jobs > MATMUL_MAX_JOBS) return cudaErrorInvalidValue;
     // Tile width: wide tiles reuse the dequantised weights over more tokens, narrow tiles fill the
     // 148 SMs when there are few weight rows.  Cost model (cycles per 64-wide K step of one CTA,
     // L2-bound estimates): 800 / 520 / 330 for BN = 256 / 128 / 64, times the number of tile rounds.
     int m_tiles_total = 0;
     for (int j = 0; j < n_jobs; j++) m_tiles_total += ((int) jobs[j].W.M + GT_BM - 1) / GT_BM;
     int BN = 64, KS = 1; double best = 1e300;
+    const int nsm = device_sm_count();
     const int cand[3] = {256, 128, 64}; const double cost[3] = {800.0, 520.0, 330.0};
     static const int force_bn = [] { const char * e = getenv("RWKV_B200_TC_BN"); return e ? atoi(e) : 0; }();   // tests: pin the tile width
     // K split: measured slower than whole-K tiles on every model shape of this round (the single-round launches it
@@ -478,9 +480,9 @@ cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t
         if (cand[c] > 64 && cand[c] / 2 >= T) continue;           // tile would be more than half empty
         const int tiles = m_tiles_total * ((T + cand[c] - 1) / cand[c]);
         for (int ks = 1; ks <= 2; ks++) {
-            if (ks == 2 && !(can_split && tiles <= 74 && (size_t) tiles * cand[c] * GT_BM <= scratch->floats)) continue;
-            if (ks == 1 && force_ks == 2 && can_split && tiles <= 74 && (size_t) tiles * cand[c] * GT_BM <= scratch->floats) continue;
-            const double t = (double) ((tiles * ks + 147) / 148) * cost[c] * (double) (kb_max / ks) + (ks == 2 ? 2500.0 : 0.0);
+            if (ks == 2 && !(can_split && tiles <= nsm / 2 && (size_t) tiles * cand[c] * GT_BM <= scratch->floats)) continue;
+            if (ks == 1 && force_ks == 2 && can_split && tiles <= nsm / 2 && (size_t) tiles * cand[c] * GT_BM <= scratch->floats) continue;
+            const double t = (double) ((tiles * ks + nsm - 1) / nsm) * cost[c] * (double) (kb_max / ks) + (ks == 2 ? 2500.0 : 0.0);
             if (t < best) { best = t; BN = cand[c]; KS = ks; }
         }
     }
@@ -491,7 +493,7 @@ cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t
     const uint32_t type = jobs[0].W.type;
     int total = 0;
     for (int j = 0; j < n_jobs; j++) {
-        const GemmJob & g = jobs[j];
+        const MatmulJob & g = jobs[j];
         if (g.W.type != type) return cudaErrorInvalidValue;
         GtJob & o = b.job[j];
         if (!make_map(&o.xmap, g.x16, g.W.K, (uint64_t) T, (uint64_t) g.ldx, (uint32_t) BN)) return cudaErrorInvalidValue;
@@ -516,14 +518,14 @@ cudaError_t launch_gemm_tc(const GemmJob * jobs, int n_jobs, int T, cudaStream_t
 
 template <int TYPE>
 static cudaError_t gt_attr() {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<TYPE, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, gt_smem_bytes<TYPE, 256>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<TYPE, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, gt_smem_bytes<TYPE, 128>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<TYPE, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, gt_smem_bytes<TYPE, 64>());
+    cudaError_t e = cudaFuncSetAttribute(matmul_tc_kernel<TYPE, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, gt_smem_bytes<TYPE, 256>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matmul_tc_kernel<TYPE, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, gt_smem_bytes<TYPE, 128>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matmul_tc_kernel<TYPE, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, gt_smem_bytes<TYPE, 64>());
     return e;
 }
 
 // once per device, outside stream capture
-cudaError_t gemm_tc_init() {
+cudaError_t matmul_tc_init() {
     cudaError_t e = gt_attr<T_F16>();
     if (e == cudaSuccess) e = gt_attr<T_Q4_0>();
     if (e == cudaSuccess) e = gt_attr<T_Q4_1>();

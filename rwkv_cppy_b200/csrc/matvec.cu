@@ -17,37 +17,37 @@
 // the roofline is bytes(W)/t against the measured copy bandwidth.
 // A CTA owning 32 consecutive outputs can quantise them for the next mat-vec in its
 // epilogue (one q8 block per column), so chained products need no extra launch.
-#include "gemv_common.cuh"
+#include "matvec_common.cuh"
 #include "launch.cuh"
 #include <cstdlib>
 
 namespace rb {
 
-cudaError_t launch_gemv_async(const GemvBatch & b, int total_ctas, cudaStream_t st);
+cudaError_t launch_matvec_async(const MatvecBatch & b, int total_ctas, cudaStream_t st);
 
-constexpr int GEMV_WARPS = 8;
-constexpr int GEMV_R     = 4;                       // rows per warp
-constexpr int GEMV_ROWS  = GEMV_WARPS * GEMV_R;     // 32 rows per CTA = one q8 block of outputs
+constexpr int MATVEC_WARPS = 8;
+constexpr int MATVEC_R     = 4;                       // rows per warp
+constexpr int MATVEC_ROWS  = MATVEC_WARPS * MATVEC_R;     // 32 rows per CTA = one q8 block of outputs
 
 template <int TYPE, int NCOL>
-__global__ void __launch_bounds__(GEMV_WARPS * 32)
-gemv_kernel(const __grid_constant__ GemvBatch B) {
+__global__ void __launch_bounds__(MATVEC_WARPS * 32)
+matvec_kernel(const __grid_constant__ MatvecBatch B) {
     pdl_trigger();
     // which job / row block
     int j = 0;
 #pragma unroll 1
     while (j + 1 < B.n_jobs && (int) blockIdx.x >= B.cta_begin[j + 1]) j++;
-    const GemvJob & J = B.job[j];
+    const MatvecJob & J = B.job[j];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int M = J.W.M, K = J.W.K, T = B.T;
-    const int row0 = ((int) blockIdx.x - B.cta_begin[j]) * GEMV_ROWS + warp * GEMV_R;
+    const int row0 = ((int) blockIdx.x - B.cta_begin[j]) * MATVEC_ROWS + warp * MATVEC_R;
     const int col0 = blockIdx.y * NCOL;
 
-    float res[GEMV_R][NCOL];
+    float res[MATVEC_R][NCOL];
     {   // pull the head of this warp's rows towards L2 while the producer of x is still running
         const size_t esz = (TYPE == T_F32) ? 4 : 2;
 #pragma unroll
-        for (int r = 0; r < GEMV_R; r++) {
+        for (int r = 0; r < MATVEC_R; r++) {
             const char * p = reinterpret_cast<const char *>(J.W.qs) + (size_t) min(row0 + r, M - 1) * K * esz + (size_t) lane * 128;
             if ((size_t) lane * 128 < (size_t) K * esz) asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
         }
@@ -55,11 +55,11 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
     pdl_wait();
 
     {
-        static_assert(TYPE == T_F32 || TYPE == T_F16, "quantised types use gemv_async.cu");
+        static_assert(TYPE == T_F32 || TYPE == T_F16, "quantised types use matvec_q.cu");
         constexpr int VEC = (TYPE == T_F32) ? 4 : 8;
-        float acc[GEMV_R][NCOL];
+        float acc[MATVEC_R][NCOL];
 #pragma unroll
-        for (int r = 0; r < GEMV_R; r++)
+        for (int r = 0; r < MATVEC_R; r++)
 #pragma unroll
             for (int c = 0; c < NCOL; c++) acc[r][c] = 0.0f;
         const int nchunk = (K % VEC == 0 && J.x_off % VEC == 0 && J.x.K % 4 == 0) ? K / VEC : 0;   // else rows are not 16-byte aligned
@@ -79,15 +79,15 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
                     for (int i = 0; i < VEC; i++) xv[c][i] = round_f16(xv[c][i]);
                 }
             }
-            uint4 wq[GEMV_R];
+            uint4 wq[MATVEC_R];
 #pragma unroll
-            for (int r = 0; r < GEMV_R; r++) {
+            for (int r = 0; r < MATVEC_R; r++) {
                 const int row = min(row0 + r, M - 1);
                 if (TYPE == T_F32) wq[r] = *reinterpret_cast<const uint4 *>(reinterpret_cast<const float *>(J.W.qs) + (size_t) row * K + (size_t) ch * 4);
                 else               wq[r] = *reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(J.W.qs) + (size_t) row * K + (size_t) ch * 8);
             }
 #pragma unroll
-            for (int r = 0; r < GEMV_R; r++) {
+            for (int r = 0; r < MATVEC_R; r++) {
                 float wf[VEC];
                 if (TYPE == T_F32) {
                     wf[0] = __uint_as_float(wq[r].x); wf[1] = __uint_as_float(wq[r].y); wf[2] = __uint_as_float(wq[r].z); wf[3] = __uint_as_float(wq[r].w);
@@ -108,7 +108,7 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
         // scalar tail when K is not a multiple of the vector width
         for (int k = nchunk * VEC + lane; k < K; k += 32) {
 #pragma unroll
-            for (int r = 0; r < GEMV_R; r++) {
+            for (int r = 0; r < MATVEC_R; r++) {
                 const int row = min(row0 + r, M - 1);
                 const float wv = (TYPE == T_F32) ? reinterpret_cast<const float *>(J.W.qs)[(size_t) row * K + k]
                                                  : __half2float(reinterpret_cast<const __half *>(J.W.qs)[(size_t) row * K + k]);
@@ -122,20 +122,20 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
             }
         }
 #pragma unroll
-        for (int r = 0; r < GEMV_R; r++)
+        for (int r = 0; r < MATVEC_R; r++)
 #pragma unroll
             for (int c = 0; c < NCOL; c++) res[r][c] = warp_sum(acc[r][c]);
     }
 
     // ---- epilogue: lane (r*NCOL + c) finishes output (row0 + r, col0 + c) ------------------
-    __shared__ float tile[NCOL][GEMV_ROWS];
+    __shared__ float tile[NCOL][MATVEC_ROWS];
     float mine = 0.0f;
 #pragma unroll
-    for (int r = 0; r < GEMV_R; r++)
+    for (int r = 0; r < MATVEC_R; r++)
 #pragma unroll
         for (int c = 0; c < NCOL; c++) if (lane == r * NCOL + c) mine = res[r][c];
     const bool want_q = (J.out_act.f != nullptr);
-    if (lane < GEMV_R * NCOL) {
+    if (lane < MATVEC_R * NCOL) {
         const int r = lane / NCOL, c = lane % NCOL;
         const int m = row0 + r, t = col0 + c;
         float v = 0.0f;
@@ -143,12 +143,12 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
             v = apply_epilogue(J, mine, t, m);
             if (J.out) J.out[(size_t) t * J.ldo + m] = v;
         }
-        if (want_q) tile[c][warp * GEMV_R + r] = v;
+        if (want_q) tile[c][warp * MATVEC_R + r] = v;
     }
     if (want_q) {                                   // uniform per CTA
         __syncthreads();
         if (warp < NCOL && col0 + warp < T) {
-            const int m = ((int) blockIdx.x - B.cta_begin[j]) * GEMV_ROWS + lane;
+            const int m = ((int) blockIdx.x - B.cta_begin[j]) * MATVEC_ROWS + lane;
             act_store_block(J.out_act, (size_t) (col0 + warp), m, m < M, tile[warp][lane]);
         }
     }
@@ -157,15 +157,15 @@ gemv_kernel(const __grid_constant__ GemvBatch B) {
 // ---- FP32 weights with a very short K (v6 time_maa_w2: K = 32) over many rows ---------------
 // The mat-vec kernel re-reads such a matrix once per 8 columns; here a thread keeps its weight
 // row in registers and walks 32 activation rows staged in shared memory.  The result is
-// bit-identical to gemv_kernel<T_F32>: lane c of that kernel accumulates chunk c (4 weights,
+// bit-identical to matvec_kernel<T_F32>: lane c of that kernel accumulates chunk c (4 weights,
 // FMA chain), lanes >= K/4 hold 0, and the xor-butterfly (16, 8, 4, 2, 1) combines them; the
 // same tree is evaluated here in one thread (x + 0 is exact, so the empty lanes drop out).
 template <int NCH>   // K / 4: 8 or 16
-__global__ void __launch_bounds__(256) smallk_kernel(const __grid_constant__ GemvBatch B) {
+__global__ void __launch_bounds__(256) smallk_kernel(const __grid_constant__ MatvecBatch B) {
     constexpr int K = NCH * 4, TT = 32;
     __shared__ __align__(16) float xs[TT][K];
     pdl_trigger();
-    const GemvJob & J = B.job[blockIdx.z];
+    const MatvecJob & J = B.job[blockIdx.z];
     const int m = blockIdx.x * 256 + threadIdx.x, t0 = blockIdx.y * TT, M = J.W.M, T = B.T;
     float w[K];
     {
@@ -200,56 +200,56 @@ __global__ void __launch_bounds__(256) smallk_kernel(const __grid_constant__ Gem
     }
 }
 
-static bool smallk_ok(const GemvBatch & b) {
+static bool smallk_ok(const MatvecBatch & b) {
     if (b.T < 16 || b.n_jobs < 1) return false;
     const uint32_t K = b.job[0].W.K;
     if (K != 32 && K != 64) return false;
     for (int j = 0; j < b.n_jobs; j++) {
-        const GemvJob & g = b.job[j];
+        const MatvecJob & g = b.job[j];
         if (g.W.type != T_F32 || g.W.K != K || g.W.M != b.job[0].W.M || g.out == nullptr || g.out_act.f != nullptr) return false;
         if (g.x_off % 4 != 0 || g.x.K % 4 != 0) return false;
     }
     return true;
 }
 
-static cudaError_t launch_smallk(const GemvBatch & b, cudaStream_t st) {
+static cudaError_t launch_smallk(const MatvecBatch & b, cudaStream_t st) {
     const dim3 grid((b.job[0].W.M + 255) / 256, (b.T + 31) / 32, b.n_jobs);
     if (b.job[0].W.K == 32) return launch_pdl(smallk_kernel<8>, grid, dim3(256), 0, st, b);
     return launch_pdl(smallk_kernel<16>, grid, dim3(256), 0, st, b);
 }
 
 template <int TYPE>
-static cudaError_t launch_typed(const GemvBatch & b, int total_ctas, cudaStream_t st) {
-    const dim3 block(GEMV_WARPS * 32);
-    if (b.T == 1)      return launch_pdl(gemv_kernel<TYPE, 1>, dim3(total_ctas, 1), block, 0, st, b);
-    else if (b.T == 2) return launch_pdl(gemv_kernel<TYPE, 2>, dim3(total_ctas, 1), block, 0, st, b);
-    else if (b.T <= 4) return launch_pdl(gemv_kernel<TYPE, 4>, dim3(total_ctas, 1), block, 0, st, b);
-    else               return launch_pdl(gemv_kernel<TYPE, 8>, dim3(total_ctas, (b.T + 7) / 8), block, 0, st, b);
+static cudaError_t launch_typed(const MatvecBatch & b, int total_ctas, cudaStream_t st) {
+    const dim3 block(MATVEC_WARPS * 32);
+    if (b.T == 1)      return launch_pdl(matvec_kernel<TYPE, 1>, dim3(total_ctas, 1), block, 0, st, b);
+    else if (b.T == 2) return launch_pdl(matvec_kernel<TYPE, 2>, dim3(total_ctas, 1), block, 0, st, b);
+    else if (b.T <= 4) return launch_pdl(matvec_kernel<TYPE, 4>, dim3(total_ctas, 1), block, 0, st, b);
+    else               return launch_pdl(matvec_kernel<TYPE, 8>, dim3(total_ctas, (b.T + 7) / 8), block, 0, st, b);
 }
 
-static bool gemv_ksplit_disabled() {
+static bool matvec_ksplit_disabled() {
     static const bool off = [] { const char * e = getenv("RWKV_B200_NO_KSPLIT"); return e && e[0] == '1'; }();
     return off;
 }
 
-cudaError_t launch_gemv(const GemvBatch & b_in, cudaStream_t st) {
+cudaError_t launch_matvec(const MatvecBatch & b_in, cudaStream_t st) {
     if (b_in.n_jobs == 0) return cudaSuccess;
-    GemvBatch b = b_in;
+    MatvecBatch b = b_in;
     const uint32_t type = b.job[0].W.type;
     int total = 0;
     b.ks = 1;
     if (type_quantized(type)) {
-        b.ks = gemv_ksplit(b.job[0].W.M, b.job[0].W.K);
-        for (int j = 1; j < b.n_jobs; j++) if (gemv_ksplit(b.job[j].W.M, b.job[j].W.K) != b.ks) return cudaErrorInvalidValue;   // callers group by split
-        if (gemv_ksplit_disabled()) b.ks = 1;
+        b.ks = matvec_ksplit(b.job[0].W.M, b.job[0].W.K);
+        for (int j = 1; j < b.n_jobs; j++) if (matvec_ksplit(b.job[j].W.M, b.job[j].W.K) != b.ks) return cudaErrorInvalidValue;   // callers group by split
+        if (matvec_ksplit_disabled()) b.ks = 1;
     }
     for (int j = 0; j < b.n_jobs; j++) {
         if (b.job[j].W.type != type) return cudaErrorInvalidValue;
         b.cta_begin[j] = total;
-        total += (((int) b.job[j].W.M + GEMV_ROWS - 1) / GEMV_ROWS) * b.ks;
+        total += (((int) b.job[j].W.M + MATVEC_ROWS - 1) / MATVEC_ROWS) * b.ks;
     }
     b.cta_begin[b.n_jobs] = total;
-    if (type_quantized(type)) return launch_gemv_async(b, total, st);
+    if (type_quantized(type)) return launch_matvec_async(b, total, st);
     if (b.pro.kind != PRO_NONE) return cudaErrorInvalidValue;      // prologues exist in the quantised kernel only
     if (type == T_F32 && smallk_ok(b)) return launch_smallk(b, st);
     if (type == T_F32) return launch_typed<T_F32>(b, total, st);

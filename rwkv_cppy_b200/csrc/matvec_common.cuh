@@ -1,5 +1,5 @@
-// Inner products and epilogues shared by the two mat-vec kernels (gemv.cu: register-staged,
-// any shape / FP16 / FP32; gemv_async.cu: bulk-async staged, quantised).  See gemv.cu for the
+// Inner products and epilogues shared by the two mat-vec kernels (matvec.cu: register-staged,
+// any shape / FP16 / FP32; matvec_q.cu: bulk-async staged, quantised).  See matvec.cu for the
 // reference arithmetic these restate.
 #pragma once
 #include "device_utils.cuh"

@@ -15,7 +15,7 @@
 // One CTA = 8 warps = 32 consecutive rows, so the epilogue can also emit the q8 activation
 // block of its 32 outputs for a chained mat-vec.  Per output the FP32 summation order is
 // lane-strided over K + butterfly: it depends on K only, never on T or the grid.
-#include "gemv_common.cuh"
+#include "matvec_common.cuh"
 #include "launch.cuh"
 #include "ptx.cuh"
 #include <cstdlib>
@@ -103,7 +103,7 @@ __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; a
 #define TRACE_PASS
 #endif
 
-// ---- decode prologues (kernels.h GemvPrologue) ---------------------------------------------------
+// ---- decode prologues (kernels.h MatvecPrologue) ---------------------------------------------------
 // The input vector of the launch as q8 blocks in shared memory (what the chunk loop otherwise
 // reads from the Act planes in global memory).
 template <bool ON>
@@ -154,7 +154,7 @@ __device__ __forceinline__ void pro_store_all(ProX & px, const float (&v)[ITEMS]
 // part 1 (before pdl_wait): constants and the read-only input state
 template <int ITEMS> struct ProLnRegs { float xs[ITEMS], w[ITEMS], b[ITEMS], mu[ITEMS]; };
 template <int ITEMS>
-__device__ __forceinline__ void pro_lnmix_pre(const GemvPrologue & P, const float * __restrict__ mu, ProLnRegs<ITEMS> & r) {
+__device__ __forceinline__ void pro_lnmix_pre(const MatvecPrologue & P, const float * __restrict__ mu, ProLnRegs<ITEMS> & r) {
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
         const int e = it * PRO_NT + threadIdx.x;
@@ -166,7 +166,7 @@ __device__ __forceinline__ void pro_lnmix_pre(const GemvPrologue & P, const floa
 }
 // part 2 (after pdl_wait): the row itself; same arithmetic as ln_mix_kernel<., ., 256> (elementwise.cu)
 template <int ITEMS>
-__device__ __forceinline__ void pro_lnmix_post(const GemvPrologue & P, const ProLnRegs<ITEMS> & r, ProX & px, double (*red)[32] TRACE_ARG) {
+__device__ __forceinline__ void pro_lnmix_post(const MatvecPrologue & P, const ProLnRegs<ITEMS> & r, ProX & px, double (*red)[32] TRACE_ARG) {
     float x[1][ITEMS];
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
@@ -192,7 +192,7 @@ __device__ __forceinline__ void pro_lnmix_post(const GemvPrologue & P, const Pro
 
 template <int ITEMS> struct ProWkvRegs { float aa[ITEMS], bb[ITEMS], pp[ITEMS], u[ITEMS], w[ITEMS]; };
 template <int ITEMS>
-__device__ __forceinline__ void pro_wkv4_pre(const GemvPrologue & P, ProWkvRegs<ITEMS> & r) {
+__device__ __forceinline__ void pro_wkv4_pre(const MatvecPrologue & P, ProWkvRegs<ITEMS> & r) {
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
         const int e = it * PRO_NT + threadIdx.x;
@@ -203,7 +203,7 @@ __device__ __forceinline__ void pro_wkv4_pre(const GemvPrologue & P, ProWkvRegs<
 }
 // same arithmetic as wkv4_kernel (wkv.cu; rwkv_operators.inc / rwkv_graph.inc v4 att)
 template <int ITEMS>
-__device__ __forceinline__ void pro_wkv4_post(const GemvPrologue & P, const ProWkvRegs<ITEMS> & g, ProX & px) {
+__device__ __forceinline__ void pro_wkv4_post(const MatvecPrologue & P, const ProWkvRegs<ITEMS> & g, ProX & px) {
     float k[ITEMS], v[ITEMS], r[ITEMS], out[ITEMS];
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
@@ -234,7 +234,7 @@ __device__ __forceinline__ void pro_wkv4_post(const GemvPrologue & P, const ProW
 
 template <int TYPE, int NCOL, int S, int PRO = PRO_NONE, int PIT = 4>
 __global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? (QFmt<TYPE>::QB == 32 ? 2 : 3) : (NCOL == 2 ? 2 : 1))
-gemv_async_kernel(const __grid_constant__ GemvBatch B) {
+matvec_async_kernel(const __grid_constant__ MatvecBatch B) {
     static_assert(PRO == PRO_NONE || NCOL == 1, "prologues are single-row");
     using F = QFmt<TYPE>;
     constexpr int BB = F::QB + F::HB + F::DB;              // bytes per block
@@ -251,7 +251,7 @@ gemv_async_kernel(const __grid_constant__ GemvBatch B) {
     int j = 0;
 #pragma unroll 1
     while (j + 1 < B.n_jobs && (int) blockIdx.x >= B.cta_begin[j + 1]) j++;
-    const GemvJob & J = B.job[j];
+    const MatvecJob & J = B.job[j];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int M = J.W.M, nb = J.W.K >> 5, T = B.T;
     // K split: the `ks` CTAs of a cluster share one block of 32 rows, CTA kr takes a contiguous range
@@ -448,28 +448,28 @@ static int ga_stage_override() {
 }
 
 template <int TYPE, int NCOL>
-static cudaError_t launch_async_n(const GemvBatch & b, int total_ctas, int ygrid, cudaStream_t st) {
+static cudaError_t launch_async_n(const MatvecBatch & b, int total_ctas, int ygrid, cudaStream_t st) {
     // Ring depth: 3 stages let three CTAs share an SM (24 warps hide the unpack latency) and win
     // once the grid fills them (>= 3 x 148 CTAs); smaller grids run one or two CTAs per SM and
     // want the deeper ring for bytes in flight.  Q8_0 tiles are 4.25 KB: 3 stages either way.
     // The depth never changes the arithmetic.
-    int S = (QFmt<TYPE>::QB == 32 || total_ctas * ygrid >= 3 * 148) ? 3 : 4;
+    int S = (QFmt<TYPE>::QB == 32 || total_ctas * ygrid >= 3 * device_sm_count()) ? 3 : 4;
     if (ga_stage_override() == 3 || ga_stage_override() == 4) S = ga_stage_override();
     const int cl = b.ks > 1 ? b.ks : 0;
-    if (S == 3) return launch_pdl_cluster(gemv_async_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, cl, b);
-    return launch_pdl_cluster(gemv_async_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, cl, b);
+    if (S == 3) return launch_pdl_cluster(matvec_async_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, cl, b);
+    return launch_pdl_cluster(matvec_async_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, cl, b);
 }
 
 template <int TYPE, int PRO>
-static cudaError_t launch_async_pro(const GemvBatch & b, int total, cudaStream_t st) {
+static cudaError_t launch_async_pro(const MatvecBatch & b, int total, cudaStream_t st) {
     constexpr int S = QFmt<TYPE>::QB == 32 ? 3 : 4;          // small models: grids well below 3 x 148 CTAs
     if (b.pro.D <= 4 * PRO_NT)
-        return launch_pdl(gemv_async_kernel<TYPE, 1, S, PRO, 4>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
-    return launch_pdl(gemv_async_kernel<TYPE, 1, S, PRO, 8>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
+        return launch_pdl(matvec_async_kernel<TYPE, 1, S, PRO, 4>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
+    return launch_pdl(matvec_async_kernel<TYPE, 1, S, PRO, 8>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
 }
 
 template <int TYPE>
-static cudaError_t launch_async_t(const GemvBatch & b, int total, cudaStream_t st) {
+static cudaError_t launch_async_t(const MatvecBatch & b, int total, cudaStream_t st) {
     if (b.pro.kind != PRO_NONE) {
         if (b.T != 1 || b.ks != 1 || b.pro.D > LN_SMALL_D || b.pro.D % 32 != 0) return cudaErrorInvalidValue;
         for (int j = 0; j < b.n_jobs; j++)
@@ -482,8 +482,8 @@ static cudaError_t launch_async_t(const GemvBatch & b, int total, cudaStream_t s
     else               return launch_async_n<TYPE, 8>(b, total, (b.T + 7) / 8, st);
 }
 
-// b.cta_begin already filled by launch_gemv (32 rows per CTA)
-cudaError_t launch_gemv_async(const GemvBatch & b, int total_ctas, cudaStream_t st) {
+// b.cta_begin already filled by launch_matvec (32 rows per CTA)
+cudaError_t launch_matvec_async(const MatvecBatch & b, int total_ctas, cudaStream_t st) {
     switch (b.job[0].W.type) {
         case T_Q4_0: return launch_async_t<T_Q4_0>(b, total_ctas, st);
         case T_Q4_1: return launch_async_t<T_Q4_1>(b, total_ctas, st);
@@ -496,7 +496,7 @@ cudaError_t launch_gemv_async(const GemvBatch & b, int total_ctas, cudaStream_t 
 
 template <int TYPE, int NCOL, int S>
 static cudaError_t set_smem_one() {
-    return cudaFuncSetAttribute(gemv_async_kernel<TYPE, NCOL, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, S>());
+    return cudaFuncSetAttribute(matvec_async_kernel<TYPE, NCOL, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, S>());
 }
 
 template <int TYPE>
@@ -511,16 +511,16 @@ static cudaError_t set_smem_attr() {
     if (e == cudaSuccess) e = set_smem_one<TYPE, 4, 4>();
     if (e == cudaSuccess) e = set_smem_one<TYPE, 8, 4>();
     constexpr int SP = QFmt<TYPE>::QB == 32 ? 3 : 4;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1, SP, PRO_LNMIX, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1, SP, PRO_LNMIX, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemv_async_kernel<TYPE, 1, SP, PRO_WKV4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_async_kernel<TYPE, 1, SP, PRO_LNMIX, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_async_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_async_kernel<TYPE, 1, SP, PRO_LNMIX, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_async_kernel<TYPE, 1, SP, PRO_WKV4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     return e;
 }
 
 // Opt in to > 48 KB dynamic shared memory; call once per device before the first launch
 // (and outside stream capture).
-cudaError_t gemv_async_init() {
+cudaError_t matvec_async_init() {
     cudaError_t e = set_smem_attr<T_Q4_0>();
     if (e == cudaSuccess) e = set_smem_attr<T_Q4_1>();
     if (e == cudaSuccess) e = set_smem_attr<T_Q5_0>();

@@ -11,9 +11,12 @@
 namespace rb {
 
 Model::~Model() {
+    int prev = -1;
+    cudaGetDevice(&prev);                                 // leave the calling thread's current device as it was
     cudaSetDevice(device);
     tp_comm_destroy(tp);
     for (void * p : allocations) cudaFree(p);
+    if (prev >= 0 && prev != device) cudaSetDevice(prev);
 }
 
 static float half_bits_to_float(uint16_t h) {
@@ -87,6 +90,10 @@ struct Loader {
                                     t->name.c_str(), (unsigned long long) K, (unsigned long long) blk);
             return false;
         }
+        if ((elem_off + M * K) / blk * bb > t->nbytes) {      // the view must stay inside the tensor's bytes in the mapping
+            ok = false; global_fail(RWKV_ERROR_MODEL_PARAMS | RWKV_ERROR_SHAPE, __FILE__, __LINE__, "Parameter %s: matrix view runs past the tensor data", t->name.c_str());
+            return false;
+        }
         return upload(t->type, t->data + elem_off / blk * bb, M, K, out);
     }
 
@@ -124,7 +131,7 @@ struct Loader {
         if (launch_repack(type, scratch, M, K, tiled, st) != cudaSuccess) { ok = false; return false; }
         if (cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
         out.qs = tiled; out.rg_stride = (uint32_t) tiled_rg_stride(type, K);
-        if (gemm_tc_enabled() && K >= TC_KB) {                 // second copy in the tensor-core chunk layout (scratch still holds the raw rows)
+        if (matmul_tc_enabled() && K >= TC_KB) {                 // second copy in the tensor-core chunk layout (scratch still holds the raw rows)
             void * tc = bump(tc_bytes(type, M, K));
             if (!tc) return false;
             if (launch_repack_tc(type, scratch, M, K, tc, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
@@ -220,7 +227,7 @@ Model * model_load(const char * path, const TpInfo & tp) {
         const size_t as_vec = t.n_elements() * 4;
         arena += std::max(t.nbytes, t.n_dims == 2 ? t.nbytes : as_vec) + 4 * 256;
         if (type_quantized(t.type)) arena += TILE_ROWS * (t.ne[0] / 32) * type_block_bytes(t.type) + 64;   // row padding of the tiled layout
-        if (type_quantized(t.type) && t.n_dims == 2 && gemm_tc_enabled()) arena += tc_bytes(t.type, t.ne[1] * t.ne[2], t.ne[0]) + 256;
+        if (type_quantized(t.type) && t.n_dims == 2 && matmul_tc_enabled()) arena += tc_bytes(t.type, t.ne[1] * t.ne[2], t.ne[0]) + 256;
         if (type_quantized(t.type)) scratch = std::max(scratch, t.nbytes);
     }
     RB_CUDA(cudaMalloc((void **) &L.arena, arena), RWKV_ERROR_MODEL | RWKV_ERROR_ALLOC, nullptr);
@@ -231,8 +238,10 @@ Model * model_load(const char * path, const TpInfo & tp) {
         L.scratch_size = scratch;
     }
     RB_CUDA(cudaStreamCreate(&L.st), RWKV_ERROR_MODEL | RWKV_ERROR_ALLOC, nullptr);
-    RB_CUDA(gemv_async_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
-    if (gemm_tc_enabled()) RB_CUDA(gemm_tc_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
+    RB_CUDA(matvec_async_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
+    RB_CUDA(wkv_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
+    RB_CUDA(elementwise_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
+    if (matmul_tc_enabled()) RB_CUDA(matmul_tc_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
 
     const size_t D = m.n_embed, V = m.n_vocab;
     L.mat("emb.weight", D, V, m.emb);

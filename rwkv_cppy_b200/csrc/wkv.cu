@@ -326,12 +326,7 @@ static cudaError_t launch_wkv5_t(const WkvArgs & a, cudaStream_t st) {
     if (!a.batch && a.R >= WKV_SEQ_MIN_ROWS && a.yraw != nullptr) {
         constexpr size_t smem = 2 * WKV_TCH * (3 * S + 8) * sizeof(float);
         constexpr int LC = S >= 32 ? WKV_SEQ_LC : (S >= 16 ? 2 : 1);   // 8*LC lanes per state column
-        static bool attr_set = false;                     // per template instance; > 48 KB needs the opt-in
-        if (!attr_set && smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute(wkv5_seq_kernel<S, LC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-            if (e != cudaSuccess) return e;
-            attr_set = true;
-        }
+        // > 48 KB of dynamic shared memory: opted in per device by wkv_init() (called from model_load)
         cudaError_t e = launch_pdl(wkv5_seq_kernel<S, LC>, dim3(a.H, S / 8), dim3(64 * LC), smem, st, a, a.yraw);
         if (e != cudaSuccess) return e;
         return launch_pdl(wkv5_norm_kernel<S>, dim3((a.D + 255) / 256, a.R), dim3(256), 0, st, a, (const float *) a.yraw);
@@ -340,6 +335,23 @@ static cudaError_t launch_wkv5_t(const WkvArgs & a, cudaStream_t st) {
     const int threads = ((hpb * S + 31) / 32) * 32;
     dim3 grid((a.H + hpb - 1) / hpb, a.batch ? a.R : 1);
     return launch_pdl(wkv5_kernel<S>, grid, dim3(threads), 5 * threads * sizeof(float), st, a);
+}
+
+template <int S>
+static cudaError_t wkv5_seq_attr() {
+    constexpr size_t smem = 2 * WKV_TCH * (3 * S + 8) * sizeof(float);
+    constexpr int LC = S >= 32 ? WKV_SEQ_LC : (S >= 16 ? 2 : 1);
+    if (smem <= 48 * 1024) return cudaSuccess;
+    return cudaFuncSetAttribute(wkv5_seq_kernel<S, LC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+}
+
+// Function attributes are per device: called once per model load on the model's device (outside stream capture).
+cudaError_t wkv_init() {
+    cudaError_t e = wkv5_seq_attr<8>();
+    if (e == cudaSuccess) e = wkv5_seq_attr<16>();
+    if (e == cudaSuccess) e = wkv5_seq_attr<32>();
+    if (e == cudaSuccess) e = wkv5_seq_attr<64>();
+    return e;
 }
 
 cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st) {

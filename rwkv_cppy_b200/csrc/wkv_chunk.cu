@@ -1,5 +1,5 @@
 // v5 / v6 WKV over long sequences, chunk-parallel form (head size 64, rows >= 64 of FP16 /
-// quantised models -- the rows that also take the tensor-core GEMM, i.e. the tolerance-mode
+// quantised models -- the rows that also take the tensor-core MATMUL, i.e. the tolerance-mode
 // sequence path; everything else keeps the exact scan of wkv.cu).
 //
 // Reference recurrence (ggml_compute_forward_rwkv_wkv6_f32, ggml-cpu.c:11945-11980), per head,
