@@ -32,8 +32,9 @@ class RWKVSharedLibrary:
 
     def __init__(self, shared_library_path: str) -> None:
         self.path = shared_library_path
-        # the same flags the reference uses for the CUDA build: resolve symbols globally
-        self.library = lib = ctypes.CDLL(shared_library_path, mode=ctypes.RTLD_GLOBAL)
+        # RTLD_LOCAL (ctypes' default): a process may also hold the reference's own librwkv.so (tests, the
+        # bench's cpu_baseline leg); with RTLD_GLOBAL that library's internal rwkv_* calls would bind here
+        self.library = lib = ctypes.CDLL(shared_library_path)
         vp, u32, sz, b = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_size_t, ctypes.c_bool
 
         def sig(name, args, res):
