@@ -2,6 +2,7 @@
 // runs for bench.py, and the codec / mat-vec hooks the parity tests drive.
 #include "context.h"
 #include "../../include/rwkv_b200.h"
+#include "matrix_handle.h"
 
 #include <cstring>
 #include <new>
@@ -18,17 +19,6 @@ struct rwkv_b200_batch {
     int * h_tokens = nullptr;                    // pinned [n]
     cudaGraphExec_t graph[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};   // [state parity][logits]
     size_t graph_nodes[2] = {0, 0};
-};
-
-struct rwkv_b200_matrix {
-    int device = 0;
-    std::vector<DevMat> copies;
-    std::vector<void *> allocations;
-    Act x; int x_rows = 0;
-    float * y = nullptr; size_t y_cap = 0;
-    cudaStream_t stream = nullptr;
-    size_t next = 0;
-    MatmulScratch scratch;              // K-split partial tiles (tensor-core hook)
 };
 
 namespace {

@@ -140,7 +140,7 @@ __device__ __forceinline__ void act_store_block(const Act & a, size_t row, int e
 // ggml_compute_forward_norm_f32 (ggml-cpu.c:6880-6930): mean and variance accumulated in
 // double, y = (x-mean) * 1/sqrt(var+eps); then rwkv_layer_norm (rwkv_operators.inc:93):
 // y*w + b as two roundings.  `buf` (shared, D floats) receives the result.
-__device__ __forceinline__ void block_layer_norm(const float * __restrict__ x, int D, const float * __restrict__ w,
+__device__ __forceinline__ void block_layer_norm(const float * x, int D, const float * __restrict__ w,
                                                  const float * __restrict__ b, float eps, float * buf, double * red) {
     double s = 0.0;
     for (int i = threadIdx.x; i < D; i += blockDim.x) { const float v = x[i]; buf[i] = v; s += (double) v; }

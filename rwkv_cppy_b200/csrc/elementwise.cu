@@ -257,7 +257,7 @@ cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
     return launch_ln_mix_i<8, 1024>(a, threads, st);
 }
 
-__global__ void __launch_bounds__(256) ln_act_kernel(const float * __restrict__ x, int ldx, int D, const float * __restrict__ w,
+__global__ void __launch_bounds__(256) ln_act_kernel(const float * x /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */, int ldx, int D, const float * __restrict__ w,
                                                      const float * __restrict__ b, Act out) {
     extern __shared__ float smem[];
     __shared__ double red[32];
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(256) ln_act_kernel(const float * __restrict__ 
 
 // Register-resident variant (rows up to 256 * ITEMS wide), same structure as ln_mix_kernel.
 template <int ITEMS>
-__global__ void __launch_bounds__(256) ln_act_reg_kernel(const float * __restrict__ x, int ldx, int D, const float * __restrict__ w,
+__global__ void __launch_bounds__(256) ln_act_reg_kernel(const float * x /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */, int ldx, int D, const float * __restrict__ w,
                                                          const float * __restrict__ b, Act out) {
     __shared__ double red[2][32];
     const int r = blockIdx.x;

@@ -4,6 +4,7 @@
 // (R = T tokens of one stream) and batched decode (R independent streams): the kernels take
 // the row count and the "rows are streams" flag.
 #include "engine.h"
+#include "launch.cuh"
 #include <cstdlib>
 #include <initializer_list>
 #include <unordered_map>
@@ -248,6 +249,7 @@ struct Pass {
 
     void ffn(uint32_t layer) {
         const LayerW & l = m.layers[layer];
+        pdl_site() = 8;
         if (m.tp.world > 1) { ffn_v4_tp(layer); return; }
         if (m.arch_major == 7) {
             MatvecJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
@@ -261,6 +263,7 @@ struct Pass {
                 matvec({k}, R);
             }
             Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
+            pdl_site() = 16;
             matvec({job(l.ffn_value, kin, ws.x, (int) D, EPI_ADD_TO)}, R);
             return;
         }
@@ -278,6 +281,7 @@ struct Pass {
         }
         Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
         MatvecJob v = job(l.ffn_value, kin, ws.x, (int) D, EPI_MULADD_TO); v.aux = ws.ffn_r; v.ld_aux = (int) D;
+        pdl_site() = 16;
         matvec({v}, R);
     }
 
@@ -415,6 +419,7 @@ struct Pass {
     void run() {
         chk(launch_embed_ln0(m.emb, ws.tokens, R, m.ln0_w, m.ln0_b, ws.x, st));
         for (uint32_t i = 0; i < m.n_layer; i++) {
+            pdl_site() = 1;
             switch (m.arch_major) {
                 case 4: if (m.tp.world > 1) att_v4_tp(i); else att_v4(i); break;
                 case 5: att_v5(i); break;
@@ -423,17 +428,21 @@ struct Pass {
             }
             ffn(i);
         }
+        pdl_site() = 0;
         if (fa.logits) {
             const int rows = fa.batch ? R : 1;
             const float * x = fa.batch ? ws.x : ws.x + (size_t) (R - 1) * D;
+            pdl_site() = 32;
             chk(launch_ln_act(x, (int) D, rows, (int) D, m.ln_out_w, m.ln_out_b, produced(ws.head_in, {&m.head}, rows), st));
             if (m.tp.world > 1) {      // vocabulary rows are sharded: gather the slices (equal-sized, zero-padded at the end)
                 const int Vl = (int) ((m.n_vocab + m.tp.world - 1) / m.tp.world);
                 matvec({job(m.head, ws.head_in, ws.logits_part, Vl, EPI_STORE)}, rows);
                 if (rows == 1) chk(tp_allgather(m.tp, ws.logits_part, ws.logits, (size_t) Vl, st));
                 else err = err == cudaSuccess ? cudaErrorNotSupported : err;     // batched logits under TP: not needed by any caller yet
-            } else
-            matvec({job(m.head, ws.head_in, ws.logits, (int) m.n_vocab, EPI_STORE)}, rows);
+            } else {
+                pdl_site() = 64;
+                matvec({job(m.head, ws.head_in, ws.logits, (int) m.n_vocab, EPI_STORE)}, rows);
+            }
         }
     }
 };

@@ -7,6 +7,9 @@
 //       input state: bulk-copy / prefetch them ...
 //   pdl_wait()     before the first access to anything a preceding kernel writes, and before
 //                  the first global write.
+// RULE: a pointer to anything a preceding kernel writes must not be `const T * __restrict__` (nor read with __ldg): nvcc
+// marks such loads invariant (LDG.E.CONSTANT) and may hoist them above griddepcontrol.wait -- seen in ln_act_reg_kernel<8>,
+// which read the residual row before the last ffn mat-vec had added to it (caught by tests/test_gpu_fast_paths.py).
 // So a mat-vec streams its first weight tiles while the producer of its activations is
 // still running, and the tail of one kernel overlaps the fill of the next.  pdl_wait()
 // returns when the preceding kernel has completed and flushed; since every kernel waits
@@ -22,9 +25,13 @@ namespace rb {
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// Debug aid: forward.cpp tags the launches of a pass with a site bit (1 att input, 2 wkv, 4 att output, 8 ffn key / receptance,
+// 16 ffn value, 32 ln_out, 64 head); RWKV_B200_PDL_OFF_SITES=<mask> launches those sites in plain stream order.
+inline int & pdl_site() { static thread_local int s = 0; return s; }
 inline bool pdl_enabled() {
     static const bool on = [] { const char * e = getenv("RWKV_B200_NO_PDL"); return !(e && e[0] == '1'); }();
-    return on;
+    static const int off_sites = [] { const char * e = getenv("RWKV_B200_PDL_OFF_SITES"); return e ? atoi(e) : 0; }();
+    return on && !(off_sites & pdl_site());
 }
 
 template <typename... KArgs, typename... Args>

@@ -379,7 +379,7 @@ matmul_tc_kernel(const __grid_constant__ GtBatch B) {
 }
 
 // ---- FP32 -> FP16 activation rows ---------------------------------------------------------
-__global__ void to_half_kernel(const float * __restrict__ x, __half * __restrict__ out, size_t n4) {
+__global__ void to_half_kernel(const float * x /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */, __half * out, size_t n4) {
     pdl_trigger();
     pdl_wait();
     for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t) gridDim.x * blockDim.x) {

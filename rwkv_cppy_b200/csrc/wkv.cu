@@ -192,7 +192,7 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 // L = S/(8*LC) consecutive key rows each.  With LC = 2 the second lane of a chain continues the
 // first lane's partial sum (one shuffle), so the chain is still summed key by key in order.
 template <int S, int LC>
-__global__ void __launch_bounds__(64 * LC) wkv5_seq_kernel(const __grid_constant__ WkvArgs a, float * __restrict__ yraw) {
+__global__ void __launch_bounds__(64 * LC) wkv5_seq_kernel(const __grid_constant__ WkvArgs a, float * yraw) {
     constexpr int P = WKV_CHAINS * LC;                 // lanes per column
     constexpr int L = S / P;                           // key rows per lane
     constexpr int NT = 8 * P;                          // threads: 8 columns per CTA
@@ -304,7 +304,7 @@ __global__ void __launch_bounds__(64 * LC) wkv5_seq_kernel(const __grid_constant
 
 // per-head norm + ln_x + gate of raw scan outputs: CTA = 256 consecutive channels of one token
 template <int S>
-__global__ void __launch_bounds__(256) wkv5_norm_kernel(const __grid_constant__ WkvArgs a, const float * __restrict__ yraw) {
+__global__ void __launch_bounds__(256) wkv5_norm_kernel(const __grid_constant__ WkvArgs a, const float * yraw /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */) {
     __shared__ __align__(8) float sy[256];
     pdl_trigger();
     pdl_wait();
@@ -483,7 +483,7 @@ cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st) {
 }
 
 // ---- tensor parallel: x += r * (Wv k) after the all-reduce of [partial Wv k | r shards] ----
-__global__ void __launch_bounds__(256) tp_ffn_combine_kernel(float * __restrict__ x, const float * __restrict__ recv, int D) {
+__global__ void __launch_bounds__(256) tp_ffn_combine_kernel(float * x, const float * recv /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */, int D) {
     pdl_trigger();
     pdl_wait();
     const int e = blockIdx.x * 256 + threadIdx.x;

@@ -59,7 +59,7 @@ __device__ __forceinline__ float4 load_row4(const float * p, const WkvArgs & a, 
 }
 
 // ---- 1: chunk-local state increment -------------------------------------------------------------
-__global__ void __launch_bounds__(256) wkv_chunk_state_kernel(const __grid_constant__ WkvArgs a, float * __restrict__ ds, float * __restrict__ pc, int nchunks) {
+__global__ void __launch_bounds__(256) wkv_chunk_state_kernel(const __grid_constant__ WkvArgs a, float * ds, float * pc, int nchunks) {
     __shared__ __align__(16) float sw[CC][CS];
     __shared__ __align__(16) float kd[CC][CS];
     __shared__ __align__(16) float sv[CC][CS];
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(256) wkv_chunk_state_kernel(const __grid_const
 // ---- 2: state entering every chunk ----------------------------------------------------------------
 // grid (H, 4): CTA = 16 key rows of a head, thread = one float4 of the state.  The loads of the
 // next 8 chunks are in flight while the current 8 are chained.
-__global__ void __launch_bounds__(256) wkv_chunk_scan_kernel(const __grid_constant__ WkvArgs a, float * __restrict__ ds, const float * __restrict__ pc, int nchunks) {
+__global__ void __launch_bounds__(256) wkv_chunk_scan_kernel(const __grid_constant__ WkvArgs a, float * ds, const float * pc /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */, int nchunks) {
     pdl_trigger();
     const int tid = threadIdx.x, h = blockIdx.x;
     const int i = blockIdx.y * 16 + (tid >> 4), j0 = (tid & 15) * 4;
@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(256) wkv_chunk_scan_kernel(const __grid_consta
 }
 
 // ---- 3: outputs of a chunk ----------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) wkv_chunk_out_kernel(const __grid_constant__ WkvArgs a, const float * __restrict__ ds, int nchunks) {
+__global__ void __launch_bounds__(256) wkv_chunk_out_kernel(const __grid_constant__ WkvArgs a, const float * ds /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */, int nchunks) {
     __shared__ __align__(16) float sst[CS * CS];          // S_start of the chunk; later the 4 partial y tiles, then y
     __shared__ __align__(16) float sw[CC][CS];
     __shared__ __align__(16) float sr[CC][CS];

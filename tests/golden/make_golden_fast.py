@@ -14,7 +14,7 @@ BASELINE.json model shapes.  Run in the build container (the GPU box only reads 
                                         file, so a test can tell "different file" from "different result"
 
 Synthetic files are regenerated on the GPU box by the same deterministic writer (numpy PCG64
-streams + the product's byte-identical quantiser).  `--only tiny,mini,169m,v6,v7,14b` limits the
+streams + the product's byte-identical quantiser).  `--only tiny,mini,169m,v6,v7,14b,l2` limits the
 sections (existing entries of the .npz are kept).
 """
 import hashlib
@@ -83,7 +83,7 @@ def section_mini(L, ours, synth, out):
     for shape, fmt in MINI:
         p = synth.ensure_model(ours, shape, fmt)
         out[f"files/{shape}-{fmt}"] = file_tag(p)
-        c = L.load(p, N_THREADS, 0)
+        c = L.load(p, 2, 0)      # <= head count (4): ggml's wkv6 op returns threads >= HEADS before its barrier (ggml-cpu.c:11822) and hangs otherwise
         for T in MINI_T:
             s, lg = c.eval_sequence(mini_tokens(T), c.init_state())
             out[f"mini/{shape}-{fmt}/T{T}/logits"] = lg.copy()
@@ -151,6 +151,40 @@ def section_v7(L, ours, synth, out):
     c.free()
 
 
+def section_l2(L, ours, synth, out):
+    # two-layer cuts of the v6 1.6B / v7 2.9B shapes: 6 decode tokens + a 64-token sequence; and the reference's own movement
+    # under a +-1 ulp perturbation of its input state on the full-depth files (the noise floor of "same arithmetic, other sum order")
+    for shape, fmt in (("v6-1b6-L2", "Q5_1"), ("v7-2b9-L2", "Q8_0")):
+        p = synth.ensure_model(ours, shape, fmt)
+        out[f"files/{shape}-{fmt}"] = file_tag(p)
+        c = L.load(p, N_THREADS, 0)
+        toks = big_tokens(15, 64, c.n_vocab)
+        s = c.init_state()
+        for i, t in enumerate(toks[:6]):
+            s, lg = c.eval(t, s)
+            out[f"big/{shape}-{fmt}/logits_t{i + 1}"] = lg.copy()
+        out[f"big/{shape}-{fmt}/state_t6"] = state_sample(s)
+        s, lg = c.eval_sequence(toks, c.init_state())
+        out[f"big/{shape}-{fmt}/logits_T64"] = lg.copy()
+        out[f"big/{shape}-{fmt}/state_T64"] = state_sample(s)
+        c.free()
+        print("l2", shape, "done", flush=True)
+    for shape, fmt in (("v6-1b6", "Q5_1"), ("v7-2b9", "Q8_0"), ("v4-14b", "Q4_1")):
+        c = L.load(synth.ensure_model(ours, shape, fmt), N_THREADS, 0)
+        toks = big_tokens(100, 4, c.n_vocab)
+        s = c.init_state()
+        for t in toks[:3]:
+            s, lg = c.eval(t, s)
+        _, l1 = c.eval(toks[3], s.copy())
+        sp = s.copy()
+        bits = sp.view(np.int32)
+        bits += np.random.default_rng(0).integers(-1, 2, size=bits.shape, dtype=np.int32) * ((np.abs(s) < 1e29) & (s != 0))
+        _, l2 = c.eval(toks[3], sp)
+        out[f"sensitivity/{shape}-{fmt}"] = np.float32([np.abs(l2 - l1).max() / max(1.0, float(np.abs(l1).max())), np.sqrt(np.mean((l2 - l1) ** 2))])
+        print("sensitivity", shape, out[f"sensitivity/{shape}-{fmt}"], flush=True)
+        c.free()
+
+
 def section_14b(L, ours, synth, out):
     # configs[4]: v4 14B Q4_1, 4 decode tokens
     p = synth.ensure_model(ours, "v4-14b", "Q4_1")
@@ -177,7 +211,8 @@ def main():
     out = dict(np.load(OUT)) if os.path.exists(OUT) else {}
     sections = [("tiny", lambda: section_tiny(L, out)), ("mini", lambda: section_mini(L, ours, synth, out)),
                 ("169m", lambda: section_169m(L, ours, synth, out)), ("v6", lambda: section_v6(L, ours, synth, out)),
-                ("v7", lambda: section_v7(L, ours, synth, out)), ("14b", lambda: section_14b(L, ours, synth, out))]
+                ("v7", lambda: section_v7(L, ours, synth, out)), ("14b", lambda: section_14b(L, ours, synth, out)),
+                ("l2", lambda: section_l2(L, ours, synth, out))]
     for name, fn in sections:
         if only and name not in only:
             continue
