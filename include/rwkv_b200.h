@@ -96,6 +96,19 @@ RWKV_API bool   rwkv_b200_matrix_bench(struct rwkv_b200_matrix * m, size_t n_vec
  * batches use for n_vec >= 64 rows (replaces ggml_mul_mat at T > 1, rwkv_graph.inc:744-870). */
 RWKV_API bool   rwkv_b200_matrix_mul_tc(struct rwkv_b200_matrix * m, const float * x, size_t n_vec, float * y);
 RWKV_API bool   rwkv_b200_matrix_bench_tc(struct rwkv_b200_matrix * m, size_t n_vec, int iters, double * ms_per_launch);
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it).  Same product and same arithmetic as rwkv_b200_matrix_mul for a QUANTISED matrix, but this call
+ * allocates nothing: x and y are DEVICE buffers of the handle's GPU supplied by the caller
+ * (x[n_vec][n_cols], y[n_vec][n_rows], FP32), and the q8 activation blocks the kernel reads live in a
+ * static __device__ array inside the library (352 KiB per GPU that loads it, held until exit).
+ * Limit: n_vec * n_cols <= RWKV_B200_NO_ALLOC_MAX_ELEMS, larger calls fail with RWKV_ERROR_ARGS |
+ * RWKV_ERROR_SHAPE.  All calls share that array (it keeps the last call's contents; every byte a
+ * call reads it has rewritten first): calls that overlap on the GPU race, serialise them.
+ * Synchronises the handle's stream before returning. */
+#define RWKV_B200_NO_ALLOC_MAX_ELEMS 262144
+RWKV_API bool   rwkv_b200_matrix_mul_no_alloc(struct rwkv_b200_matrix * m, const float * x_dev, size_t n_vec, float * y_dev);
+RWKV_API size_t rwkv_b200_no_alloc_max_elements(void);
 /* Algorithmic bytes of one copy (the file bytes of the matrix). */
 RWKV_API size_t rwkv_b200_matrix_bytes(const struct rwkv_b200_matrix * m);
 
