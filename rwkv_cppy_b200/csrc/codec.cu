@@ -177,11 +177,12 @@ cudaError_t launch_dequant_f16(const DevMat & W, void * out_half, cudaStream_t s
 
 // ---- embedding row gather + ln0 (rwkv_graph.inc:655-658: ggml_get_rows then rwkv_layer_norm) ----
 __global__ void embed_ln0_kernel(DevMat emb, const int * __restrict__ tokens, const float * __restrict__ w,
-                                 const float * __restrict__ b, float * __restrict__ x) {
+                                 const float * __restrict__ b, float * __restrict__ x, unsigned int * step) {
     extern __shared__ float smem[];
     __shared__ double red[32];
     pdl_trigger();
     pdl_wait();
+    if (step && blockIdx.x == 0 && threadIdx.x == 0) *step = *step + 1;
     const int t = blockIdx.x, D = emb.K;
     const int tok = tokens[t];
     float * raw = smem + D;          // second half: gathered row
@@ -195,9 +196,10 @@ __global__ void embed_ln0_kernel(DevMat emb, const int * __restrict__ tokens, co
 // statistics use the shared row reduction (device_utils.cuh ln_rows_stats).
 template <int ITEMS>
 __global__ void __launch_bounds__(256) embed_ln0_reg_kernel(DevMat emb, const int * __restrict__ tokens, const float * __restrict__ w,
-                                                            const float * __restrict__ b, float * __restrict__ x) {
+                                                            const float * __restrict__ b, float * __restrict__ x, unsigned int * step) {
     __shared__ double red[2][32];
     pdl_trigger();
+    if (step && blockIdx.x == 0 && threadIdx.x == 0) *step = *step + 1;     // plain stream-ordered launch: nothing of the previous pass is running
     const int t = blockIdx.x, D = emb.K;
     const int tok = tokens[t];
     float v[1][ITEMS], lw[ITEMS], lb[ITEMS];
@@ -217,14 +219,14 @@ __global__ void __launch_bounds__(256) embed_ln0_reg_kernel(DevMat emb, const in
     }
 }
 
-cudaError_t launch_embed_ln0(const DevMat & emb, const int * tokens, int T, const float * w, const float * b, float * x, cudaStream_t st) {
+cudaError_t launch_embed_ln0(const DevMat & emb, const int * tokens, int T, const float * w, const float * b, float * x, cudaStream_t st, unsigned int * step) {
     // Plain stream-ordered launch on purpose: the first kernel of a pass is a full fence, so nothing of
     // this pass (which may prefetch the input state before its pdl_wait) overlaps the previous pass.
-    if (emb.K <= 1024)      embed_ln0_reg_kernel<4><<<T, 256, 0, st>>>(emb, tokens, w, b, x);
-    else if (emb.K <= 2048) embed_ln0_reg_kernel<8><<<T, 256, 0, st>>>(emb, tokens, w, b, x);
-    else if (emb.K <= 4096) embed_ln0_reg_kernel<16><<<T, 256, 0, st>>>(emb, tokens, w, b, x);
-    else if (emb.K <= 8192) embed_ln0_reg_kernel<32><<<T, 256, 0, st>>>(emb, tokens, w, b, x);
-    else embed_ln0_kernel<<<T, 256, 2 * emb.K * sizeof(float), st>>>(emb, tokens, w, b, x);
+    if (emb.K <= 1024)      embed_ln0_reg_kernel<4><<<T, 256, 0, st>>>(emb, tokens, w, b, x, step);
+    else if (emb.K <= 2048) embed_ln0_reg_kernel<8><<<T, 256, 0, st>>>(emb, tokens, w, b, x, step);
+    else if (emb.K <= 4096) embed_ln0_reg_kernel<16><<<T, 256, 0, st>>>(emb, tokens, w, b, x, step);
+    else if (emb.K <= 8192) embed_ln0_reg_kernel<32><<<T, 256, 0, st>>>(emb, tokens, w, b, x, step);
+    else embed_ln0_kernel<<<T, 256, 2 * emb.K * sizeof(float), st>>>(emb, tokens, w, b, x, step);
     return cudaGetLastError();
 }
 

@@ -34,6 +34,8 @@ enum Epilogue : int {
     EPI_V6_DECAY,        // out = exp(-exp(y + vec[m]))         (rwkv_graph.inc:349-356)
     EPI_V7_DECAY,        // out = exp(-0.606531 * sigmoid(y + vec[m]))   (rwkv_graph.inc:418-426)
     EPI_ADD_AUX,         // out = aux[t][m] + y                 (tensor parallel: rank 0 folds the residual into its partial sum)
+    EPI_TP_PUSH,         // y          -> slot [tp_off + m] of this rank in every peer's low-latency inbox (fused all-reduce, tp.h)
+    EPI_TP_PUSH_SIGMOID, // sigmoid(y) -> same                  (the ffn receptance slice travels with the partial sums)
 };
 
 struct MatvecJob {
@@ -48,6 +50,7 @@ struct MatvecJob {
     const float * vec = nullptr;      // [M] per-row constant (bias / decay base)
     Act           out_act;            // optional quantised copy of `out` (out_act.q may be null)
     const float * pro_mu = nullptr;   // PRO_LNMIX launches: this job's token-shift mix vector [K]
+    int           tp_off = 0;         // EPI_TP_PUSH*: entry offset inside this rank's inbox slot
 };
 
 // Optional prologue of a single-row quantised mat-vec launch (decode of models up to LN_SMALL_D
@@ -58,18 +61,43 @@ struct MatvecJob {
 //   PRO_WKV4   k, v, r, state -> r * wkv  (what wkv4_kernel does; CTA 0 stores the new state)
 // Both reproduce the standalone kernels bit for bit (same per-element arithmetic, same
 // reduction order, same q8 blocks).
-constexpr int LN_SMALL_D = 2048;
+constexpr int LN_SMALL_D = 2048;      // rows up to here keep their prologue operands in registers across the dependency wait
+constexpr int LN_PRO_MAX_D = 8192;    // widest row a prologue (and the 256-thread layer-norm shape) handles
 enum PrologueKind : int { PRO_NONE = 0, PRO_LNMIX = 1, PRO_WKV4 = 2 };
+
+// Tensor-parallel decode, all-reduce fused into the mat-vecs (tp.h "low-latency inbox"): the
+// epilogue of a row-split mat-vec stores {value, flag} pairs straight into every peer's inbox
+// (EPI_TP_PUSH), and the prologue of the next mat-vec waits for the flags of its site and rebuilds
+// the replicated residual row itself -- no collective launch.
+constexpr int TP_LL_WORLD = 8;
+struct TpFused {
+    unsigned char * ll[TP_LL_WORLD] = {};   // low-latency inbox of every rank (ll[rank] is local memory), null = off
+    int rank = 0, world = 1;
+    const unsigned int * step = nullptr;    // pass counter (local; bumped by the first kernel of every pass)
+    unsigned int * err = nullptr;           // host-mapped error word: set when a peer did not deliver within ~2 s
+    unsigned int slot_entries = 0;          // entries per source slot
+    int site_push = -1;                     // site id the EPI_TP_PUSH* jobs of this launch publish (flag = step << 8 | site)
+};
+struct TpWait {
+    int site = -1;                          // >= 0: the prologue first gathers x = base (+ | + r *) sum of the ranks' partials of that site
+    int gated = 0;                          // 1: x = base + r * (p0 + p1 + ...) with r from the slots' second section (ffn); 0: x = ((base + p0) + p1) + ...
+    int n = 0, n_slice = 0;                 // D and D / world
+    float * x_out = nullptr;                // CTA 0 stores the gathered row here (the other buffer of the residual ping-pong)
+};
+
 struct MatvecPrologue {
     int kind = PRO_NONE, D = 0, mix_kind = 0;
     const float * x = nullptr, * ln_w = nullptr, * ln_b = nullptr;          // PRO_LNMIX
     const float * k = nullptr, * v = nullptr, * r = nullptr, * u = nullptr, * decay = nullptr;   // PRO_WKV4
-    const float * state_in = nullptr; float * state_out = nullptr;          // shift slot (LNMIX) / aa slot (WKV4; bb, pp follow at +D, +2D)
+    const float * state_in = nullptr; float * state_out = nullptr;          // shift slot (LNMIX) / aa slot (WKV4; bb, pp follow at +state_D, +2*state_D)
+    int state_D = 0;                                                         // PRO_WKV4: floats between the aa / bb / pp slots (0: D)
+    TpWait wait;                                                             // PRO_LNMIX under fused tensor parallelism
 };
 
 constexpr int MATVEC_MAX_JOBS = 8;
 struct MatvecBatch {
     MatvecPrologue pro;
+    TpFused tp;                             // fused tensor-parallel collectives (ll[0] == nullptr: none)
     MatvecJob job[MATVEC_MAX_JOBS];
     int     cta_begin[MATVEC_MAX_JOBS + 1];   // prefix sum of CTAs per job (filled by launch_matvec)
     int     n_jobs = 0;
@@ -132,7 +160,8 @@ cudaError_t launch_dequant(const DevMat & W, float * out, cudaStream_t st);
 cudaError_t launch_dequant_f16(const DevMat & W, void * out_half, cudaStream_t st);
 
 // ---- embedding + ln0 --------------------------------------------------------------------
-cudaError_t launch_embed_ln0(const DevMat & emb, const int * tokens, int T, const float * w, const float * b, float * x, cudaStream_t st);
+// step != nullptr: thread 0 also bumps the tensor-parallel pass counter
+cudaError_t launch_embed_ln0(const DevMat & emb, const int * tokens, int T, const float * w, const float * b, float * x, cudaStream_t st, unsigned int * step = nullptr);
 
 // ---- layer norm + token shift + mixes ---------------------------------------------------
 enum MixKind : int { MIX_LERP = 0 /* v4/v5: x*mu + (xp - xp*mu) */, MIX_SX = 1 /* v6/v7: x + (xp-x)*mu */ };
@@ -202,5 +231,7 @@ constexpr int WKV_CHUNK_TOKENS = 16;
 
 // tensor parallel ffn tail: x[t][m] += recv[t][D + m] * recv[t][m]  (recv = all-reduced [partial Wv k | r shards], 2*D per row)
 cudaError_t launch_tp_ffn_combine(float * x, const float * recv, int R, int D, cudaStream_t st);
+// fused tensor parallelism: materialise the residual row of a site outside a mat-vec prologue (before ln_out)
+cudaError_t launch_tp_gather_row(const TpFused & tp, const TpWait & w, const float * base, cudaStream_t st);
 
 } // namespace rb

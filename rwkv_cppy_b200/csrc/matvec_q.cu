@@ -234,7 +234,7 @@ __device__ __forceinline__ void pro_wkv4_post(const MatvecPrologue & P, const Pr
 
 template <int TYPE, int NCOL, int S, int PRO = PRO_NONE, int PIT = 4>
 __global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? (QFmt<TYPE>::QB == 32 ? 2 : 3) : (NCOL == 2 ? 2 : 1))
-matvec_async_kernel(const __grid_constant__ MatvecBatch B) {
+matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     static_assert(PRO == PRO_NONE || NCOL == 1, "prologues are single-row");
     using F = QFmt<TYPE>;
     constexpr int BB = F::QB + F::HB + F::DB;              // bytes per block
@@ -456,16 +456,16 @@ static cudaError_t launch_async_n(const MatvecBatch & b, int total_ctas, int ygr
     int S = (QFmt<TYPE>::QB == 32 || total_ctas * ygrid >= 3 * device_sm_count()) ? 3 : 4;
     if (ga_stage_override() == 3 || ga_stage_override() == 4) S = ga_stage_override();
     const int cl = b.ks > 1 ? b.ks : 0;
-    if (S == 3) return launch_pdl_cluster(matvec_async_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, cl, b);
-    return launch_pdl_cluster(matvec_async_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, cl, b);
+    if (S == 3) return launch_pdl_cluster(matvec_q_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, cl, b);
+    return launch_pdl_cluster(matvec_q_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, cl, b);
 }
 
 template <int TYPE, int PRO>
 static cudaError_t launch_async_pro(const MatvecBatch & b, int total, cudaStream_t st) {
     constexpr int S = QFmt<TYPE>::QB == 32 ? 3 : 4;          // small models: grids well below 3 x 148 CTAs
     if (b.pro.D <= 4 * PRO_NT)
-        return launch_pdl(matvec_async_kernel<TYPE, 1, S, PRO, 4>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
-    return launch_pdl(matvec_async_kernel<TYPE, 1, S, PRO, 8>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
+        return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 4>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
+    return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 8>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
 }
 
 template <int TYPE>
@@ -496,7 +496,7 @@ cudaError_t launch_matvec_async(const MatvecBatch & b, int total_ctas, cudaStrea
 
 template <int TYPE, int NCOL, int S>
 static cudaError_t set_smem_one() {
-    return cudaFuncSetAttribute(matvec_async_kernel<TYPE, NCOL, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, S>());
+    return cudaFuncSetAttribute(matvec_q_kernel<TYPE, NCOL, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, S>());
 }
 
 template <int TYPE>
@@ -511,10 +511,10 @@ static cudaError_t set_smem_attr() {
     if (e == cudaSuccess) e = set_smem_one<TYPE, 4, 4>();
     if (e == cudaSuccess) e = set_smem_one<TYPE, 8, 4>();
     constexpr int SP = QFmt<TYPE>::QB == 32 ? 3 : 4;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_async_kernel<TYPE, 1, SP, PRO_LNMIX, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_async_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_async_kernel<TYPE, 1, SP, PRO_LNMIX, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_async_kernel<TYPE, 1, SP, PRO_WKV4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     return e;
 }
 
