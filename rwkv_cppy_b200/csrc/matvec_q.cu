@@ -18,6 +18,7 @@
 #include "matvec_common.cuh"
 #include "launch.cuh"
 #include "ptx.cuh"
+#include "tp_ll.cuh"
 #include <cstdlib>
 
 namespace rb {
@@ -106,134 +107,173 @@ __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; a
 // ---- decode prologues (kernels.h MatvecPrologue) ---------------------------------------------------
 // The input vector of the launch as q8 blocks in shared memory (what the chunk loop otherwise
 // reads from the Act planes in global memory).
-template <bool ON>
+template <bool ON, int PIT = 8>
 struct ProXT {
-    static constexpr int N = ON ? LN_SMALL_D : 32;           // kernels without a prologue carry a stub
+    static constexpr int N = ON ? PIT * 256 : 32;            // kernels without a prologue carry a stub
     __align__(16) int8_t q[N];
     float d[N / 32], s[N / 32];
     int   isum[N / 32];
 };
-using ProX = ProXT<true>;
 constexpr int PRO_NT = GA_WARPS * 32;                        // thread `tid` holds elements it * 256 + tid, it < ITEMS
 
-// values of elements it*256 + tid -> q8 blocks (it*8 + warp) in shared memory; the blocks of all
-// items are reduced together so their shuffle chains overlap (same values as act_store_block)
-template <int ITEMS>
-__device__ __forceinline__ void pro_store_all(ProX & px, const float (&v)[ITEMS], int D) {
+// values of elements (it0 + g)*256 + tid, g < G -> q8 blocks ((it0 + g)*8 + warp) in shared memory; the blocks of a
+// group are reduced together so their shuffle chains overlap (same values as act_store_block)
+template <int G, typename PX>
+__device__ __forceinline__ void pro_store_group(PX & px, const float (&v)[G], int it0, int D) {
     const int tid = threadIdx.x;
-    float amax[ITEMS]; int q[ITEMS], sum[ITEMS];
+    float amax[G]; int q[G], sum[G];
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) amax[it] = it * PRO_NT + tid < D ? fabsf(v[it]) : 0.0f;
+    for (int g = 0; g < G; g++) amax[g] = (it0 + g) * PRO_NT + tid < D ? fabsf(v[g]) : 0.0f;
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1)
 #pragma unroll
-        for (int it = 0; it < ITEMS; it++) amax[it] = fmaxf(amax[it], __shfl_xor_sync(FULL, amax[it], off));
+        for (int g = 0; g < G; g++) amax[g] = fmaxf(amax[g], __shfl_xor_sync(FULL, amax[g], off));
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-        const float id = amax[it] != 0.0f ? __fdiv_rn(127.0f, amax[it]) : 0.0f;
-        q[it] = it * PRO_NT + tid < D ? __float2int_rn(__fmul_rn(v[it], id)) : 0;
-        sum[it] = q[it];
+    for (int g = 0; g < G; g++) {
+        const float id = amax[g] != 0.0f ? __fdiv_rn(127.0f, amax[g]) : 0.0f;
+        q[g] = (it0 + g) * PRO_NT + tid < D ? __float2int_rn(__fmul_rn(v[g], id)) : 0;
+        sum[g] = q[g];
     }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1)
 #pragma unroll
-        for (int it = 0; it < ITEMS; it++) sum[it] += __shfl_xor_sync(FULL, sum[it], off);
+        for (int g = 0; g < G; g++) sum[g] += __shfl_xor_sync(FULL, sum[g], off);
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-        const int e = it * PRO_NT + tid;
+    for (int g = 0; g < G; g++) {
+        const int e = (it0 + g) * PRO_NT + tid;
         if (e - (tid & 31) < D) {                            // warps past the row own no block (uniform)
-            px.q[e] = (int8_t) q[it];
+            px.q[e] = (int8_t) q[g];
             if ((tid & 31) == 0) {
-                const float d = __fdiv_rn(amax[it], 127.0f);
-                px.d[e >> 5] = round_f16(d); px.s[e >> 5] = round_f16(__fmul_rn(d, (float) sum[it])); px.isum[e >> 5] = sum[it];
+                const float d = __fdiv_rn(amax[g], 127.0f);
+                px.d[e >> 5] = round_f16(d); px.s[e >> 5] = round_f16(__fmul_rn(d, (float) sum[g])); px.isum[e >> 5] = sum[g];
             }
         }
     }
 }
 
-// part 1 (before pdl_wait): constants and the read-only input state
-template <int ITEMS> struct ProLnRegs { float xs[ITEMS], w[ITEMS], b[ITEMS], mu[ITEMS]; };
+// part 1 (before pdl_wait): constants and the read-only input state.  Rows wider than LN_SMALL_D fetch
+// them after the wait instead (they come from L2 and the registers are needed for the row itself).
+template <int ITEMS> struct ProLnRegs { float xs[ITEMS <= 8 ? ITEMS : 1], w[ITEMS <= 8 ? ITEMS : 1], b[ITEMS <= 8 ? ITEMS : 1], mu[ITEMS <= 8 ? ITEMS : 1]; };
 template <int ITEMS>
 __device__ __forceinline__ void pro_lnmix_pre(const MatvecPrologue & P, const float * __restrict__ mu, ProLnRegs<ITEMS> & r) {
+    if constexpr (ITEMS <= 8) {
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-        const int e = it * PRO_NT + threadIdx.x;
-        const bool valid = e < P.D;
-        r.xs[it] = valid ? P.state_in[e] : 0.0f;
-        r.w[it] = valid ? P.ln_w[e] : 0.0f; r.b[it] = valid ? P.ln_b[e] : 0.0f;
-        r.mu[it] = valid ? mu[e] : 0.0f;
+        for (int it = 0; it < ITEMS; it++) {
+            const int e = it * PRO_NT + threadIdx.x;
+            const bool valid = e < P.D;
+            r.xs[it] = valid ? P.state_in[e] : 0.0f;
+            r.w[it] = valid ? P.ln_w[e] : 0.0f; r.b[it] = valid ? P.ln_b[e] : 0.0f;
+            r.mu[it] = valid ? mu[e] : 0.0f;
+        }
     }
 }
 // part 2 (after pdl_wait): the row itself; same arithmetic as ln_mix_kernel<., ., 256> (elementwise.cu)
-template <int ITEMS>
-__device__ __forceinline__ void pro_lnmix_post(const MatvecPrologue & P, const ProLnRegs<ITEMS> & r, ProX & px, double (*red)[32] TRACE_ARG) {
+template <int ITEMS, typename PX>
+__device__ __forceinline__ void pro_lnmix_post(const MatvecBatch & B, const float * __restrict__ mu, const ProLnRegs<ITEMS> & r, PX & px, double (*red)[32] TRACE_ARG) {
+    const MatvecPrologue & P = B.pro;
     float x[1][ITEMS];
+    if (P.wait.site >= 0) {                                  // fused tensor parallelism: the row is still in flight from the peers
+        const uint2 * inbox = tp_inbox(B.tp, P.wait.site);
+        const unsigned want = tp_flag(B.tp, P.wait.site);
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-        const int e = it * PRO_NT + threadIdx.x;
-        x[0][it] = e < P.D ? P.x[e] : 0.0f;
+        for (int it = 0; it < ITEMS; it++) {
+            const int e = it * PRO_NT + threadIdx.x;
+            x[0][it] = 0.0f;
+            if (e < P.D) {
+                x[0][it] = tp_gather_element(B.tp, P.wait, inbox, want, P.x[e], e);
+                if (blockIdx.x == 0) P.wait.x_out[e] = x[0][it];
+            }
+        }
+    } else {
+#pragma unroll
+        for (int it = 0; it < ITEMS; it++) {
+            const int e = it * PRO_NT + threadIdx.x;
+            x[0][it] = e < P.D ? P.x[e] : 0.0f;
+        }
     }
     float scale[1];
     ln_rows_stats<ITEMS, 1>(x, P.D, PRO_NT, red, scale, 1e-5f);
     TRACE(7);
-    float v[ITEMS];
+    constexpr int G = 4;
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-        const int e = it * PRO_NT + threadIdx.x;
-        const float x0 = __fadd_rn(__fmul_rn(__fmul_rn(x[0][it], scale[0]), r.w[it]), r.b[it]);
-        const float xp = r.xs[it];
-        if (P.mix_kind == MIX_LERP) v[it] = __fadd_rn(__fmul_rn(x0, r.mu[it]), __fsub_rn(xp, __fmul_rn(xp, r.mu[it])));
-        else                        v[it] = __fadd_rn(__fmul_rn(__fsub_rn(xp, x0), r.mu[it]), x0);
-        if (e < P.D && blockIdx.x == 0) P.state_out[e] = x0;
+    for (int it0 = 0; it0 < ITEMS; it0 += G) {
+        float v[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            const int it = it0 + g, e = it * PRO_NT + threadIdx.x;
+            float xs, w, b, m;
+            if constexpr (ITEMS <= 8) { xs = r.xs[it]; w = r.w[it]; b = r.b[it]; m = r.mu[it]; }
+            else {
+                const bool valid = e < P.D;
+                xs = valid ? P.state_in[e] : 0.0f; w = valid ? P.ln_w[e] : 0.0f; b = valid ? P.ln_b[e] : 0.0f; m = valid ? mu[e] : 0.0f;
+            }
+            const float x0 = __fadd_rn(__fmul_rn(__fmul_rn(x[0][it], scale[0]), w), b);
+            if (P.mix_kind == MIX_LERP) v[g] = __fadd_rn(__fmul_rn(x0, m), __fsub_rn(xs, __fmul_rn(xs, m)));
+            else                        v[g] = __fadd_rn(__fmul_rn(__fsub_rn(xs, x0), m), x0);
+            if (e < P.D && blockIdx.x == 0) P.state_out[e] = x0;
+        }
+        pro_store_group<G>(px, v, it0, P.D);
     }
-    pro_store_all<ITEMS>(px, v, P.D);
     TRACE(8);
 }
 
-template <int ITEMS> struct ProWkvRegs { float aa[ITEMS], bb[ITEMS], pp[ITEMS], u[ITEMS], w[ITEMS]; };
+template <int ITEMS> struct ProWkvRegs { float aa[ITEMS <= 8 ? ITEMS : 1], bb[ITEMS <= 8 ? ITEMS : 1], pp[ITEMS <= 8 ? ITEMS : 1], u[ITEMS <= 8 ? ITEMS : 1], w[ITEMS <= 8 ? ITEMS : 1]; };
 template <int ITEMS>
 __device__ __forceinline__ void pro_wkv4_pre(const MatvecPrologue & P, ProWkvRegs<ITEMS> & r) {
+    if constexpr (ITEMS <= 8) {
+        const int sd = P.state_D ? P.state_D : P.D;
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-        const int e = it * PRO_NT + threadIdx.x;
-        const bool valid = e < P.D;
-        r.aa[it] = valid ? P.state_in[e] : 0.0f; r.bb[it] = valid ? P.state_in[P.D + e] : 0.0f; r.pp[it] = valid ? P.state_in[2 * P.D + e] : 0.0f;
-        r.u[it] = valid ? P.u[e] : 0.0f; r.w[it] = valid ? P.decay[e] : 0.0f;
+        for (int it = 0; it < ITEMS; it++) {
+            const int e = it * PRO_NT + threadIdx.x;
+            const bool valid = e < P.D;
+            r.aa[it] = valid ? P.state_in[e] : 0.0f; r.bb[it] = valid ? P.state_in[sd + e] : 0.0f; r.pp[it] = valid ? P.state_in[2 * sd + e] : 0.0f;
+            r.u[it] = valid ? P.u[e] : 0.0f; r.w[it] = valid ? P.decay[e] : 0.0f;
+        }
     }
 }
 // same arithmetic as wkv4_kernel (wkv.cu; rwkv_operators.inc / rwkv_graph.inc v4 att)
-template <int ITEMS>
-__device__ __forceinline__ void pro_wkv4_post(const MatvecPrologue & P, const ProWkvRegs<ITEMS> & g, ProX & px) {
-    float k[ITEMS], v[ITEMS], r[ITEMS], out[ITEMS];
+template <int ITEMS, typename PX>
+__device__ __forceinline__ void pro_wkv4_post(const MatvecPrologue & P, const ProWkvRegs<ITEMS> & g, PX & px) {
+    constexpr int G = 4;
+    const int sd = P.state_D ? P.state_D : P.D;
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-        const int e = it * PRO_NT + threadIdx.x;
-        const bool valid = e < P.D;
-        k[it] = valid ? P.k[e] : 0.0f; v[it] = valid ? P.v[e] : 0.0f; r[it] = valid ? P.r[e] : 0.0f;
-    }
+    for (int it0 = 0; it0 < ITEMS; it0 += G) {
+        float k[G], v[G], r[G], out[G], aa[G], bb[G], pp[G], u[G], w[G];
 #pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-        const int e = it * PRO_NT + threadIdx.x;
-        float aa = g.aa[it], bb = g.bb[it];
-        const float pp = g.pp[it];
-        float ww = __fadd_rn(g.u[it], k[it]);
-        float qq = fmaxf(pp, ww);
-        float e1 = expf(__fsub_rn(pp, qq)), e2 = expf(__fsub_rn(ww, qq));
-        const float num = __fadd_rn(__fmul_rn(e1, aa), __fmul_rn(e2, v[it]));
-        const float den = __fadd_rn(__fmul_rn(e1, bb), e2);
-        ww = __fadd_rn(pp, g.w[it]);
-        qq = fmaxf(ww, k[it]);
-        e1 = expf(__fsub_rn(ww, qq)); e2 = expf(__fsub_rn(k[it], qq));
-        aa = __fadd_rn(__fmul_rn(e1, aa), __fmul_rn(e2, v[it]));
-        bb = __fadd_rn(__fmul_rn(e1, bb), e2);
-        out[it] = e < P.D ? __fmul_rn(r[it], __fdiv_rn(num, den)) : 0.0f;
-        if (e < P.D && blockIdx.x == 0) { P.state_out[e] = aa; P.state_out[P.D + e] = bb; P.state_out[2 * P.D + e] = qq; }
+        for (int q = 0; q < G; q++) {
+            const int it = it0 + q, e = it * PRO_NT + threadIdx.x;
+            const bool valid = e < P.D;
+            k[q] = valid ? P.k[e] : 0.0f; v[q] = valid ? P.v[e] : 0.0f; r[q] = valid ? P.r[e] : 0.0f;
+            if constexpr (ITEMS <= 8) { aa[q] = g.aa[it]; bb[q] = g.bb[it]; pp[q] = g.pp[it]; u[q] = g.u[it]; w[q] = g.w[it]; }
+            else {
+                aa[q] = valid ? P.state_in[e] : 0.0f; bb[q] = valid ? P.state_in[sd + e] : 0.0f; pp[q] = valid ? P.state_in[2 * sd + e] : 0.0f;
+                u[q] = valid ? P.u[e] : 0.0f; w[q] = valid ? P.decay[e] : 0.0f;
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < G; q++) {
+            const int e = (it0 + q) * PRO_NT + threadIdx.x;
+            float ww = __fadd_rn(u[q], k[q]);
+            float qq = fmaxf(pp[q], ww);
+            float e1 = expf(__fsub_rn(pp[q], qq)), e2 = expf(__fsub_rn(ww, qq));
+            const float num = __fadd_rn(__fmul_rn(e1, aa[q]), __fmul_rn(e2, v[q]));
+            const float den = __fadd_rn(__fmul_rn(e1, bb[q]), e2);
+            ww = __fadd_rn(pp[q], w[q]);
+            qq = fmaxf(ww, k[q]);
+            e1 = expf(__fsub_rn(ww, qq)); e2 = expf(__fsub_rn(k[q], qq));
+            const float na = __fadd_rn(__fmul_rn(e1, aa[q]), __fmul_rn(e2, v[q]));
+            const float nb = __fadd_rn(__fmul_rn(e1, bb[q]), e2);
+            out[q] = e < P.D ? __fmul_rn(r[q], __fdiv_rn(num, den)) : 0.0f;
+            if (e < P.D && blockIdx.x == 0) { P.state_out[e] = na; P.state_out[sd + e] = nb; P.state_out[2 * sd + e] = qq; }
+        }
+        pro_store_group<G>(px, out, it0, P.D);
     }
-    pro_store_all<ITEMS>(px, out, P.D);
 }
 
+static_assert(sizeof(MatvecBatch) <= 4096, "kernel parameter space");
+
 template <int TYPE, int NCOL, int S, int PRO = PRO_NONE, int PIT = 4>
-__global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? (QFmt<TYPE>::QB == 32 ? 2 : 3) : (NCOL == 2 ? 2 : 1))
+__global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? ((QFmt<TYPE>::QB == 32 || (PRO != PRO_NONE && PIT >= 16)) ? 2 : 3) : (NCOL == 2 ? 2 : 1))
 matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     static_assert(PRO == PRO_NONE || NCOL == 1, "prologues are single-row");
     using F = QFmt<TYPE>;
@@ -243,7 +283,7 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     constexpr bool PREFETCH_X = (NCOL == 1);               // next chunk's activations one iteration ahead
     extern __shared__ __align__(128) uint8_t ga_smem[];
     __shared__ float tile[NCOL][GA_WARPS * GA_R];
-    __shared__ ProXT<PRO != PRO_NONE> pro_xs;
+    __shared__ ProXT<PRO != PRO_NONE, PIT> pro_xs;
     __shared__ double pro_red[PRO == PRO_LNMIX ? 2 : 1][32];
 
     TRACE_DECL; TRACE(0);
@@ -296,7 +336,7 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     pdl_wait();                                         // activations (and the residual) come from the preceding kernels
     TRACE(2);
     if constexpr (PRO != PRO_NONE) {
-        if (PRO == PRO_LNMIX) pro_lnmix_post<PIT>(B.pro, pln, pro_xs, pro_red TRACE_PASS);
+        if (PRO == PRO_LNMIX) pro_lnmix_post<PIT>(B, J.pro_mu, pln, pro_xs, pro_red TRACE_PASS);
         if (PRO == PRO_WKV4)  pro_wkv4_post<PIT>(B.pro, pwk, pro_xs);
         __syncthreads();
         xc.q = pro_xs.q + lane * 32; xc.d = pro_xs.d + lane; xc.s = pro_xs.s + lane; xc.isum = pro_xs.isum + lane;
@@ -404,6 +444,17 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
             mine = tsum;
         }
     }
+    if (NCOL == 1 && (J.epi == EPI_TP_PUSH || J.epi == EPI_TP_PUSH_SIGMOID)) {        // uniform per CTA
+        // fused all-reduce, producer side: lane = (row r, peer p) stores {value, flag} into slot `rank` of peer p's inbox
+        static_assert(GA_R * TP_LL_WORLD == 32, "one lane per (row, peer)");
+        float val = __shfl_sync(FULL, mine, lane & (GA_R - 1));
+        if (J.epi == EPI_TP_PUSH_SIGMOID) val = sigmoidf_ref(val);
+        const int m = row0 + (lane & (GA_R - 1)), peer = lane / GA_R;
+        if (m < M && peer < B.tp.world) tp_push(B.tp, B.tp.site_push, tp_flag(B.tp, B.tp.site_push), peer, (size_t) J.tp_off + m, val);
+        TRACE(5);
+        TRACE_FLUSH(PRO, gridDim.x);
+        return;
+    }
     const bool want_q = (J.out_act.f != nullptr);
     if (lane < GA_R * NCOL) {
         const int r = lane / NCOL, c = lane % NCOL;
@@ -462,20 +513,25 @@ static cudaError_t launch_async_n(const MatvecBatch & b, int total_ctas, int ygr
 
 template <int TYPE, int PRO>
 static cudaError_t launch_async_pro(const MatvecBatch & b, int total, cudaStream_t st) {
-    constexpr int S = QFmt<TYPE>::QB == 32 ? 3 : 4;          // small models: grids well below 3 x 148 CTAs
-    if (b.pro.D <= 4 * PRO_NT)
-        return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 4>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
-    return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 8>, dim3(total, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, S>(), st, b);
+    constexpr int S = QFmt<TYPE>::QB == 32 ? 3 : 4;          // a CTA's rows are a handful of chunks: the ring holds most of them while the prologue runs
+    const dim3 grid(total, 1), block(GA_WARPS * 32);
+    if (b.pro.D <= 4 * PRO_NT)  return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 4>, grid, block, ga_smem_bytes<TYPE, S>(), st, b);
+    if (b.pro.D <= 8 * PRO_NT)  return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 8>, grid, block, ga_smem_bytes<TYPE, S>(), st, b);
+    if (b.pro.D <= 16 * PRO_NT) return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 16>, grid, block, ga_smem_bytes<TYPE, S>(), st, b);
+    return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 32>, grid, block, ga_smem_bytes<TYPE, S>(), st, b);
 }
 
 template <int TYPE>
 static cudaError_t launch_async_t(const MatvecBatch & b, int total, cudaStream_t st) {
     if (b.pro.kind != PRO_NONE) {
-        if (b.T != 1 || b.ks != 1 || b.pro.D > LN_SMALL_D || b.pro.D % 32 != 0) return cudaErrorInvalidValue;
+        if (b.T != 1 || b.ks != 1 || b.pro.D > LN_PRO_MAX_D || b.pro.D % 32 != 0) return cudaErrorInvalidValue;
+        if (b.pro.wait.site >= 0 && (b.pro.kind != PRO_LNMIX || !b.tp.ll[0] || !b.pro.wait.x_out)) return cudaErrorInvalidValue;
         for (int j = 0; j < b.n_jobs; j++)
             if ((int) b.job[j].W.K != b.pro.D || b.job[j].x_off != 0 || (b.pro.kind == PRO_LNMIX && !b.job[j].pro_mu)) return cudaErrorInvalidValue;
         return b.pro.kind == PRO_LNMIX ? launch_async_pro<TYPE, PRO_LNMIX>(b, total, st) : launch_async_pro<TYPE, PRO_WKV4>(b, total, st);
     }
+    for (int j = 0; j < b.n_jobs; j++)
+        if ((b.job[j].epi == EPI_TP_PUSH || b.job[j].epi == EPI_TP_PUSH_SIGMOID) && (b.T != 1 || !b.tp.ll[0] || b.tp.site_push < 0)) return cudaErrorInvalidValue;
     if (b.T == 1)      return launch_async_n<TYPE, 1>(b, total, 1, st);
     else if (b.T == 2) return launch_async_n<TYPE, 2>(b, total, 1, st);
     else if (b.T <= 4) return launch_async_n<TYPE, 4>(b, total, 1, st);
@@ -515,6 +571,10 @@ static cudaError_t set_smem_attr() {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     return e;
 }
 

@@ -20,9 +20,21 @@ struct TpPeer {
     void *     base = nullptr;       // local region
     uint8_t *  peer[TP_MAX_WORLD] = {};    // every rank's region mapped into this process (peer[rank] == base)
     bool       connected = false;
+    unsigned int * h_err = nullptr;  // host-mapped error word (cudaHostAlloc): a kernel that gave up waiting for a peer sets it,
+    unsigned int * d_err = nullptr;  // the API reads and clears it after every synchronised call and fails the call
 };
 inline size_t tp_region_flags_bytes() { return 4096; }
-inline size_t tp_region_bytes(int world) { return tp_region_flags_bytes() + (size_t) 2 * world * TP_NMAX * sizeof(float); }
+// Low-latency inbox of the FUSED all-reduce (kernels.h TpFused; producer = epilogue of a row-split mat-vec,
+// consumer = prologue of the next mat-vec): 2 generations (site parity) x world source slots x TP_LL_SLOT
+// entries of {float value, u32 flag}, flag = pass counter << 8 | site.  A slot holds the D partial sums of the
+// source rank followed by its D / world receptance slice (ffn sites).  Sites alternate generations, and a rank
+// can only reach site s + 2 after every rank has produced site s + 1, i.e. consumed site s: no slot is
+// overwritten while a peer still reads it.
+constexpr size_t TP_LL_MAX_D = 8192;
+constexpr size_t TP_LL_SLOT = TP_LL_MAX_D + TP_LL_MAX_D / 2;
+inline size_t tp_region_ll_offset(int world) { return tp_region_flags_bytes() + (size_t) 2 * world * TP_NMAX * sizeof(float); }
+inline size_t tp_region_bytes(int world) { return tp_region_ll_offset(world) + (size_t) 2 * world * TP_LL_SLOT * 8; }
+constexpr int TP_STEP_WORD = 1000;           // u32 index of the pass counter inside the flags page (local use only)
 
 struct TpInfo {
     int rank = 0, world = 1;
@@ -49,5 +61,8 @@ bool tp_p2p_alloc(TpInfo & tp, void * handle_out_64);
 bool tp_p2p_connect(TpInfo & tp, const void * handles /* world x 64 bytes, rank order */);
 void tp_p2p_destroy(TpInfo & tp);
 cudaError_t tp_p2p_collective(const TpInfo & tp, const float * send, float * recv, size_t n, bool gather, cudaStream_t st);
+struct TpFused;
+TpFused tp_fused_desc(const TpInfo & tp);                          // launch descriptor of the fused collectives (ll[0] == nullptr: peer memory not connected)
+bool tp_error_pending(const TpInfo & tp);                          // true (and the word cleared) when a collective kernel timed out since the last call
 
 } // namespace rb

@@ -9,6 +9,7 @@
 // Two inbox generations alternate by epoch parity: a peer can be at most one call ahead.
 #include "tp.h"
 #include "launch.cuh"
+#include "tp_ll.cuh"
 #include <cstdio>
 #include <cstring>
 
@@ -20,6 +21,7 @@ struct P2pArgs {
     const float * send; float * recv;
     unsigned n;            // floats contributed by this rank
     int gather;            // 0: recv[i] = sum_r slot_r[i];  1: recv[r * n + i] = slot_r[i]
+    unsigned int * err;    // host-mapped error word
 };
 
 __device__ __forceinline__ uint32_t * region_flags(uint8_t * base) { return reinterpret_cast<uint32_t *>(base); }
@@ -59,7 +61,7 @@ __global__ void __launch_bounds__(256) tp_p2p_kernel(const __grid_constant__ P2p
         for (;;) {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(w) : "memory");
             if ((int) (seen - e) >= 0) break;
-            if (clock64() - t0 > 4000000000LL) { *region_error(mine) = 1; break; }      // ~2 s: a peer is gone; never hang the GPU
+            if (clock64() - t0 > 4000000000LL) { *region_error(mine) = 1; if (a.err) *a.err = 1u; break; }      // ~2 s: a peer is gone; never hang the GPU
         }
     }
     __syncthreads();
@@ -84,6 +86,40 @@ __global__ void __launch_bounds__(256) tp_p2p_kernel(const __grid_constant__ P2p
     if (tid == 0) region_epoch(mine)[cta] = e;
 }
 
+// Fused tensor parallelism: the residual row of a site materialised outside a mat-vec prologue (the last
+// ffn site of a pass, in front of ln_out): same arithmetic as the prologue gather (tp_ll.cuh).
+__global__ void __launch_bounds__(256) tp_gather_row_kernel(const __grid_constant__ TpFused tp, const __grid_constant__ TpWait w, const float * base) {
+    pdl_trigger();
+    pdl_wait();
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e >= w.n) return;
+    w.x_out[e] = tp_gather_element(tp, w, tp_inbox(tp, w.site), tp_flag(tp, w.site), base[e], e);
+}
+
+cudaError_t launch_tp_gather_row(const TpFused & tp, const TpWait & w, const float * base, cudaStream_t st) {
+    if (!tp.ll[0] || w.site < 0 || !w.x_out || w.n <= 0) return cudaErrorInvalidValue;
+    return launch_pdl(tp_gather_row_kernel, dim3((w.n + 255) / 256), dim3(256), 0, st, tp, w, base);
+}
+
+TpFused tp_fused_desc(const TpInfo & tp) {
+    TpFused f;
+    if (!tp.p2p.connected || tp.world < 2 || tp.world > TP_LL_WORLD) return f;
+    for (int r = 0; r < tp.world; r++) f.ll[r] = tp.p2p.peer[r] + tp_region_ll_offset(tp.world);
+    f.rank = tp.rank; f.world = tp.world;
+    f.step = reinterpret_cast<const unsigned int *>(tp.p2p.base) + TP_STEP_WORD;
+    f.err = tp.p2p.d_err;
+    f.slot_entries = (unsigned) TP_LL_SLOT;
+    return f;
+}
+
+bool tp_error_pending(const TpInfo & tp) {
+    if (!tp.p2p.h_err) return false;
+    volatile unsigned int * w = tp.p2p.h_err;
+    const unsigned int v = *w;
+    if (v) *w = 0u;
+    return v != 0;
+}
+
 bool tp_p2p_alloc(TpInfo & tp, void * handle_out_64) {
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     if (tp.world < 2 || tp.world > TP_MAX_WORLD) return false;
@@ -91,6 +127,9 @@ bool tp_p2p_alloc(TpInfo & tp, void * handle_out_64) {
         if (cudaMalloc(&tp.p2p.base, tp_region_bytes(tp.world)) != cudaSuccess) { tp.p2p.base = nullptr; return false; }
         if (cudaMemset(tp.p2p.base, 0, tp_region_bytes(tp.world)) != cudaSuccess) return false;
         if (cudaDeviceSynchronize() != cudaSuccess) return false;
+        if (cudaHostAlloc((void **) &tp.p2p.h_err, sizeof(unsigned int), cudaHostAllocMapped) != cudaSuccess) { tp.p2p.h_err = nullptr; return false; }
+        *tp.p2p.h_err = 0u;
+        if (cudaHostGetDevicePointer((void **) &tp.p2p.d_err, tp.p2p.h_err, 0) != cudaSuccess) return false;
     }
     cudaIpcMemHandle_t h;
     if (cudaIpcGetMemHandle(&h, tp.p2p.base) != cudaSuccess) return false;
@@ -117,6 +156,7 @@ void tp_p2p_destroy(TpInfo & tp) {
     for (int r = 0; r < tp.world; r++)
         if (r != tp.rank && tp.p2p.peer[r]) cudaIpcCloseMemHandle(tp.p2p.peer[r]);
     if (tp.p2p.base) cudaFree(tp.p2p.base);
+    if (tp.p2p.h_err) cudaFreeHost(tp.p2p.h_err);
     tp.p2p = TpPeer();
 }
 
@@ -124,7 +164,7 @@ cudaError_t tp_p2p_collective(const TpInfo & tp, const float * send, float * rec
     if (!tp.p2p.connected || n > TP_NMAX) return cudaErrorInvalidValue;
     P2pArgs a;
     for (int r = 0; r < TP_MAX_WORLD; r++) a.peer[r] = r < tp.world ? tp.p2p.peer[r] : nullptr;
-    a.rank = tp.rank; a.world = tp.world; a.send = send; a.recv = recv; a.n = (unsigned) n; a.gather = gather ? 1 : 0;
+    a.rank = tp.rank; a.world = tp.world; a.send = send; a.recv = recv; a.n = (unsigned) n; a.gather = gather ? 1 : 0; a.err = tp.p2p.d_err;
     return launch_pdl(tp_p2p_kernel, dim3(TP_CTAS), dim3(256), 0, st, a);
 }
 
