@@ -167,7 +167,7 @@ struct Pass {
         return on;
     }
     bool can_fuse(std::initializer_list<const DevMat *> mats) const {
-        if (!fusion_enabled() || R != 1 || D > (size_t) LN_SMALL_D || D % 32 != 0 || m.tp.world > 1) return false;
+        if (!fusion_enabled() || R != 1 || D > (size_t) LN_PRO_MAX_D || D % 32 != 0 || m.tp.world > 1) return false;
         for (const DevMat * W : mats) if (!type_quantized(W->type) || W->K != D) return false;
         return true;
     }
