@@ -48,7 +48,11 @@ bool ctx_setup(rwkv_context * ctx) {
     RB_CUDA(cudaSetDevice(m.device), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, false);
     RB_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, false);
     const size_t n = m.state_len();
-    for (int i = 0; i < 2; i++) RB_CUDA(cudaMalloc((void **) &ctx->d_state[i], n * sizeof(float)), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, false);
+    for (int i = 0; i < 2; i++) {
+        RB_CUDA(cudaMalloc((void **) &ctx->d_state[i], n * sizeof(float)), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, false);
+        // tensor parallel: a rank only writes the aa / bb / pp slices of its own channels; the rest of state_out must not be uninitialised memory
+        RB_CUDA(cudaMemset(ctx->d_state[i], 0, n * sizeof(float)), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, false);
+    }
     RB_CUDA(cudaMalloc((void **) &ctx->d_init_state, n * sizeof(float)), RWKV_ERROR_CTX | RWKV_ERROR_ALLOC, false);
     std::vector<float> init(n);
     host_init_state(m, init.data());
@@ -132,6 +136,8 @@ bool store_outputs(rwkv_context * ctx, const float * d_state, const float * d_lo
     if (state_out)  CTX_CUDA(ctx, cudaMemcpyAsync(state_out, d_state, m.state_len() * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream), false);
     if (logits_out) CTX_CUDA(ctx, cudaMemcpyAsync(logits_out, d_logits, (size_t) m.n_vocab * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream), false);
     CTX_CUDA(ctx, cudaStreamSynchronize(ctx->stream), false);
+    // a collective kernel that gave up waiting for a peer (dead or > 2 s late) has summed garbage: fail the call instead of returning it
+    CTX_CHECK(ctx, !tp_error_pending(m.tp), RWKV_ERROR_GRAPH, false, "Tensor-parallel collective timed out waiting for a peer rank; results of this call are invalid");
     return true;
 }
 

@@ -200,6 +200,7 @@ bool rwkv_b200_batch_eval(struct rwkv_b200_batch * b, const uint32_t * tokens, f
     b->cur ^= 1;
     if (logits_out) CTX_CUDA(ctx, cudaMemcpyAsync(logits_out, b->ws.logits, b->n * (size_t) m.n_vocab * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream), false);
     CTX_CUDA(ctx, cudaStreamSynchronize(ctx->stream), false);
+    CTX_CHECK(ctx, !tp_error_pending(m.tp), RWKV_ERROR_GRAPH, false, "Tensor-parallel collective timed out waiting for a peer rank; results of this call are invalid");
     return true;
 }
 

@@ -9,6 +9,7 @@
 //   v7 mixes                   rwkv_graph.inc:395-404         x + (xp-x)*mu
 #include "device_utils.cuh"
 #include "launch.cuh"
+#include "tp_ll.cuh"
 
 namespace rb {
 
@@ -84,6 +85,15 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
         const bool valid = e < D;
         x[0][it] = valid ? a.x[(size_t) r * D + e] : 0.0f;
         x[1][it] = (valid && !from_state) ? a.x[(size_t) (r - 1) * D + e] : 0.0f;
+    }
+    if (a.wait.site >= 0) {                                  // tensor-parallel decode: x = base row (+) the ranks' partial sums, still in flight
+        const uint2 * inbox = tp_inbox(a.tp, a.wait.site);
+        const unsigned want = tp_flag(a.tp, a.wait.site);
+#pragma unroll
+        for (int it = 0; it < ITEMS; it++) {
+            const int e = it * nt + threadIdx.x;
+            if (e < D) { x[0][it] = tp_gather_element(a.tp, a.wait, inbox, want, x[0][it], e); a.wait.x_out[e] = x[0][it]; }
+        }
     }
     const int nrow = from_state ? 1 : 2;                     // rows to normalise (uniform per CTA)
     float scale[2];
@@ -241,6 +251,7 @@ static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_
 }
 
 cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
+    if (a.wait.site >= 0 && (a.R != 1 || !a.tp.ll[0] || !a.wait.x_out)) return cudaErrorInvalidValue;
     if (a.D > LN_PRO_MAX_D) return cudaErrorInvalidValue;
     if (ln_mix_seq_ok(a)) {
         switch (a.D / 128) {

@@ -80,8 +80,14 @@ struct Pass {
     int R; size_t D;
     size_t sstride;
 
+    TpFused tpf;                  // fused tensor-parallel collectives: single-row decode over connected peer memory
+    bool tp_fused = false;
+
     Pass(const Model & m_, Workspace & ws_, const ForwardArgs & fa_, cudaStream_t st_)
-        : m(m_), ws(ws_), fa(fa_), st(st_), R(fa_.R), D(m_.n_embed), sstride(m_.state_len()) {}
+        : m(m_), ws(ws_), fa(fa_), st(st_), R(fa_.R), D(m_.n_embed), sstride(m_.state_len()) {
+        static const bool off = [] { const char * e = getenv("RWKV_B200_TP_NO_FUSE"); return e && e[0] == '1'; }();
+        if (m.tp.world > 1 && R == 1 && !off && D <= TP_LL_MAX_D) { tpf = tp_fused_desc(m.tp); tp_fused = tpf.ll[0] != nullptr; }
+    }
 
     void chk(cudaError_t e) { if (err == cudaSuccess && e != cudaSuccess) err = e; }
 
@@ -94,7 +100,7 @@ struct Pass {
 
     // launches the jobs grouped by weight type, `rows` rows each; wide row counts go to the
     // tensor-core MATMUL (FP16 operands), everything else to the exact mat-vec kernels
-    void matvec(std::vector<MatvecJob> jobs, int rows, const MatvecPrologue * pro = nullptr) {
+    void matvec(std::vector<MatvecJob> jobs, int rows, const MatvecPrologue * pro = nullptr, int tp_site = -1) {
         std::vector<bool> done(jobs.size(), false);
         // ---- tensor-core path ----
         for (size_t i = 0; i < jobs.size(); i++) {
@@ -130,6 +136,7 @@ struct Pass {
             if (done[i]) continue;
             MatvecBatch b; b.T = rows;
             if (pro) b.pro = *pro;
+            if (tp_site >= 0) { b.tp = tpf; b.tp.site_push = tp_site; }
             for (size_t k = i; k < jobs.size() && b.n_jobs < MATVEC_MAX_JOBS; k++)
                 if (!done[k] && jobs[k].W.type == jobs[i].W.type &&
                     (!type_quantized(jobs[i].W.type) || matvec_ksplit(jobs[k].W.M, jobs[k].W.K) == matvec_ksplit(jobs[i].W.M, jobs[i].W.K))) {
@@ -167,7 +174,10 @@ struct Pass {
         return on;
     }
     bool can_fuse(std::initializer_list<const DevMat *> mats) const {
-        if (!fusion_enabled() || R != 1 || D > (size_t) LN_PRO_MAX_D || D % 32 != 0 || m.tp.world > 1) return false;
+        // Rows wider than LN_SMALL_D: every CTA of a fused launch would rebuild a row whose operands (x, norm vectors, shift state,
+        // mixes: 5 x 4 D bytes from L2) rival its share of the weights -- measured on the 14B shape (D = 5120): 7.18 ms per token
+        // fused against 3.44 ms with the stand-alone layer-norm launch.  Fusion pays where the launch chain dominates, not bytes.
+        if (!fusion_enabled() || R != 1 || D > (size_t) LN_SMALL_D || D % 32 != 0 || m.tp.world > 1) return false;
         for (const DevMat * W : mats) if (!type_quantized(W->type) || W->K != D) return false;
         return true;
     }
@@ -184,9 +194,14 @@ struct Pass {
     const float * sin(uint32_t layer, size_t off) const { return fa.state_in + (size_t) layer * m.layer_state_len() + off; }
     float * sout(uint32_t layer, size_t off) const { return fa.state_out + (size_t) layer * m.layer_state_len() + off; }
 
-    void ln_mix(uint32_t layer, bool att, int kind, int n_out, const float * const * mu, bool want_sx, const Act * outs = nullptr) {
+    TpWait tp_wait(int site, bool gated) const {
+        TpWait w; w.site = site; w.gated = gated ? 1 : 0; w.n = (int) D; w.n_slice = (int) (D / m.tp.world); w.x_out = ws.x;
+        return w;
+    }
+    void ln_mix(uint32_t layer, bool att, int kind, int n_out, const float * const * mu, bool want_sx, const Act * outs = nullptr, const TpWait * wait = nullptr) {
         const LayerW & l = m.layers[layer];
         LnMixArgs a;
+        if (wait) { a.tp = tpf; a.wait = *wait; }
         a.x = ws.x; a.ln_w = att ? l.ln1_w : l.ln2_w; a.ln_b = att ? l.ln1_b : l.ln2_b;
         const size_t slot = att ? D : 0;                       // [ffn_xx, att_xx, ...] (rwkv_graph.inc:545-606)
         a.state_in = sin(layer, slot); a.state_out = sout(layer, slot);
@@ -215,7 +230,43 @@ struct Pass {
     // att output and ffn value, one all-reduce per block -------------------------------
     void tp_all_reduce(const float * send, float * recv, size_t n) { chk(tp_allreduce(m.tp, send, recv, n, st)); }
 
+    // Fused form (single-row decode, peer memory connected): no collective launches.  The row-split mat-vecs push their partial
+    // sums into every peer's low-latency inbox from their epilogue (site 2*layer: att, 2*layer + 1: ffn), and the layer norm that
+    // follows gathers them in rank order on top of the residual row it already holds (kernels.h TpFused / TpWait).
+    void att_v4_tp_fused(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        const int Dl = (int) l.att_key.M;
+        const TpWait w = tp_wait(2 * (int) layer - 1, true);
+        ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false, nullptr, layer > 0 ? &w : nullptr);
+        pdl_site() = 1;
+        matvec({job(l.att_key, ws.mix[0], ws.k, Dl, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, Dl, EPI_STORE),
+                job(l.att_receptance, ws.mix[2], ws.r, Dl, EPI_SIGMOID)}, R);
+        WkvArgs a = wkv_base(layer);
+        a.D = Dl; a.state_D = (int) D; a.chan0 = m.tp.rank * Dl;
+        a.y = ws.y; a.y.K = Dl; a.y.h = nullptr; tc_written.erase(ws.y.f);
+        a.u = l.time_first; a.decay = l.time_decay;
+        pdl_site() = 2;
+        chk(launch_wkv4(a, st));
+        Act yl = ws.y; yl.K = Dl;
+        pdl_site() = 4;
+        matvec({job(l.att_output, yl, nullptr, 0, EPI_TP_PUSH)}, R, nullptr, 2 * (int) layer);
+    }
+    void ffn_v4_tp_fused(uint32_t layer) {
+        const LayerW & l = m.layers[layer];
+        const int Fl = (int) l.ffn_key.M;
+        const TpWait w = tp_wait(2 * (int) layer, false);
+        pdl_site() = 8;
+        ln_mix(layer, false, MIX_LERP, 2, l.ffn_mu, false, nullptr, &w);
+        MatvecJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = Fl;
+        MatvecJob r = job(l.ffn_receptance, ws.mix[1], nullptr, 0, EPI_TP_PUSH_SIGMOID); r.tp_off = (int) D;     // this rank's slice of r rides in its slot behind the partial sums
+        matvec({k, r}, R, nullptr, 2 * (int) layer + 1);
+        Act kin = ws.ffn_k; kin.K = Fl;
+        pdl_site() = 16;
+        matvec({job(l.ffn_value, kin, nullptr, 0, EPI_TP_PUSH)}, R, nullptr, 2 * (int) layer + 1);
+    }
+
     void att_v4_tp(uint32_t layer) {
+        if (tp_fused) { att_v4_tp_fused(layer); return; }
         const LayerW & l = m.layers[layer];
         const int Dl = (int) l.att_key.M;
         ln_mix(layer, true, MIX_LERP, 3, l.att_mu, false);
@@ -234,6 +285,7 @@ struct Pass {
     }
 
     void ffn_v4_tp(uint32_t layer) {
+        if (tp_fused) { ffn_v4_tp_fused(layer); return; }
         const LayerW & l = m.layers[layer];
         const int Fl = (int) l.ffn_key.M, Dl = (int) l.ffn_receptance.M;
         ln_mix(layer, false, MIX_LERP, 2, l.ffn_mu, false);
@@ -417,7 +469,8 @@ struct Pass {
     }
 
     void run() {
-        chk(launch_embed_ln0(m.emb, ws.tokens, R, m.ln0_w, m.ln0_b, ws.x, st));
+        chk(launch_embed_ln0(m.emb, ws.tokens, R, m.ln0_w, m.ln0_b, ws.x, st,
+                             tp_fused ? reinterpret_cast<unsigned int *>(m.tp.p2p.base) + TP_STEP_WORD : nullptr));
         for (uint32_t i = 0; i < m.n_layer; i++) {
             pdl_site() = 1;
             switch (m.arch_major) {
@@ -429,6 +482,10 @@ struct Pass {
             ffn(i);
         }
         pdl_site() = 0;
+        if (tp_fused && fa.logits) {                          // the last ffn's partial sums are still in the inbox: materialise the final residual row
+            const TpWait w = tp_wait(2 * (int) m.n_layer - 1, true);
+            chk(launch_tp_gather_row(tpf, w, ws.x, st));
+        }
         if (fa.logits) {
             const int rows = fa.batch ? R : 1;
             const float * x = fa.batch ? ws.x : ws.x + (size_t) (R - 1) * D;

@@ -180,6 +180,9 @@ struct LnMixArgs {
     Act    out[MIX_MAX_OUT];
     float * x0 = nullptr;            // optional [R][D] copy of LN(x)
     float * sx = nullptr;            // optional [R][D] xp - LN(x)
+    // fused tensor parallelism (R == 1): the row is first gathered from the peers' partial sums (kernels.h TpWait; `x` is the base row)
+    TpFused tp;
+    TpWait  wait;
 };
 cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st);
 

@@ -517,14 +517,13 @@ static cudaError_t launch_async_pro(const MatvecBatch & b, int total, cudaStream
     const dim3 grid(total, 1), block(GA_WARPS * 32);
     if (b.pro.D <= 4 * PRO_NT)  return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 4>, grid, block, ga_smem_bytes<TYPE, S>(), st, b);
     if (b.pro.D <= 8 * PRO_NT)  return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 8>, grid, block, ga_smem_bytes<TYPE, S>(), st, b);
-    if (b.pro.D <= 16 * PRO_NT) return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 16>, grid, block, ga_smem_bytes<TYPE, S>(), st, b);
-    return launch_pdl(matvec_q_kernel<TYPE, 1, S, PRO, 32>, grid, block, ga_smem_bytes<TYPE, S>(), st, b);
+    return cudaErrorInvalidValue;                            // wider rows: not instantiated (see forward.cpp can_fuse: fusion loses there)
 }
 
 template <int TYPE>
 static cudaError_t launch_async_t(const MatvecBatch & b, int total, cudaStream_t st) {
     if (b.pro.kind != PRO_NONE) {
-        if (b.T != 1 || b.ks != 1 || b.pro.D > LN_PRO_MAX_D || b.pro.D % 32 != 0) return cudaErrorInvalidValue;
+        if (b.T != 1 || b.ks != 1 || b.pro.D > LN_SMALL_D || b.pro.D % 32 != 0) return cudaErrorInvalidValue;
         if (b.pro.wait.site >= 0 && (b.pro.kind != PRO_LNMIX || !b.tp.ll[0] || !b.pro.wait.x_out)) return cudaErrorInvalidValue;
         for (int j = 0; j < b.n_jobs; j++)
             if ((int) b.job[j].W.K != b.pro.D || b.job[j].x_off != 0 || (b.pro.kind == PRO_LNMIX && !b.job[j].pro_mu)) return cudaErrorInvalidValue;
@@ -571,10 +570,6 @@ static cudaError_t set_smem_attr() {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     return e;
 }
 

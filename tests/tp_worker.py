@@ -34,7 +34,15 @@ def main():
         logits, state = model.eval(t, state, use_numpy=True)
     lseq, sseq = model.eval_sequence(toks, None, use_numpy=True)
     out = {"ok": True}
+    # every rank must hold the same logits bit for bit (the replicated layer norms stay in lockstep)
+    mine = torch.from_numpy(logits.copy()).cuda()
+    ref = mine.clone()
+    dist.broadcast(ref, src=0)
+    same = torch.tensor([1 if torch.equal(mine, ref) else 0], device="cuda")
+    dist.all_reduce(same, op=dist.ReduceOp.MIN)
     if rank == 0:
+        out["ranks_identical"] = bool(same.item())
+        out["state_finite"] = bool(np.isfinite(state).all())
         full = rwkv_cppy_b200.RWKVModel(lib, path)
         s1, l1 = None, None
         for t in toks:
