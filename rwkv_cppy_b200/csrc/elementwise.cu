@@ -55,19 +55,16 @@ __device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, i
 // aligned 32-element blocks.  LN(x[r]) and -- in sequence mode -- LN(x[r-1]) (the token-shift
 // source, recomputed instead of waiting for the neighbouring CTA) run through the same
 // reductions; both use identical arithmetic, so the recomputed row is bit-identical.
-// LAZY (rows wider than LN_SMALL_D): only the two rows stay in registers; the norm vectors, the
-// shift state and the mix vectors are fetched where they are used.
-template <int ITEMS, int NOUT, int NT, bool LAZY = false>
+template <int ITEMS, int NOUT, int NT>
 __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMixArgs a) {
     __shared__ double red[4][32];
     const int r = blockIdx.x, D = a.D, nt = blockDim.x;
     const bool from_state = a.batch || r == 0;
     const size_t soff = a.batch ? (size_t) r * a.state_stride : 0;
-    constexpr int PRE = LAZY ? 1 : ITEMS;
 
     pdl_trigger();
-    float x[2][ITEMS], xs[PRE], w[PRE], bia[PRE], mu[NOUT][PRE];
-    if constexpr (!LAZY) {      // constants and the (read-only) input state first, then wait for the producer of x
+    float x[2][ITEMS], xs[ITEMS], w[ITEMS], bia[ITEMS], mu[NOUT][ITEMS];
+    {      // constants and the (read-only) input state first, then wait for the producer of x
 #pragma unroll
         for (int it = 0; it < ITEMS; it++) {
             const int e = it * nt + threadIdx.x;
@@ -103,14 +100,7 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
     for (int it = 0; it < ITEMS; it++) {
         const int e = it * nt + threadIdx.x;
         const bool valid = e < D;
-        const int p = LAZY ? 0 : it;
-        if constexpr (LAZY) {
-            if (e - (int) (threadIdx.x & 31) >= D) continue;  // a whole warp past the row (uniform per warp): nothing to fetch or store
-            xs[0] = (valid && from_state) ? a.state_in[soff + e] : 0.0f;
-            w[0] = valid ? a.ln_w[e] : 0.0f; bia[0] = valid ? a.ln_b[e] : 0.0f;
-#pragma unroll
-            for (int o = 0; o < NOUT; o++) mu[o][0] = valid ? a.mu[o][e] : 0.0f;
-        }
+        const int p = it;
         const float x0 = __fadd_rn(__fmul_rn(__fmul_rn(x[0][it], scale[0]), w[p]), bia[p]);
         float xp = xs[p];                                    // state value ...
         if (nrow == 2) xp = __fadd_rn(__fmul_rn(__fmul_rn(x[1][it], scale[1]), w[p]), bia[p]);   // ... or LN(x[r-1])
@@ -238,14 +228,14 @@ static bool ln_mix_seq_ok(const LnMixArgs & a) {
     return true;
 }
 
-template <int ITEMS, int NT, bool LAZY = false>
+template <int ITEMS, int NT>
 static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_t st) {
     switch (a.n_out) {
-        case 1: return launch_pdl(ln_mix_kernel<ITEMS, 1, NT, LAZY>, dim3(a.R), dim3(threads), 0, st, a);
-        case 2: return launch_pdl(ln_mix_kernel<ITEMS, 2, NT, LAZY>, dim3(a.R), dim3(threads), 0, st, a);
-        case 3: return launch_pdl(ln_mix_kernel<ITEMS, 3, NT, LAZY>, dim3(a.R), dim3(threads), 0, st, a);
-        case 4: return launch_pdl(ln_mix_kernel<ITEMS, 4, NT, LAZY>, dim3(a.R), dim3(threads), 0, st, a);
-        case 6: return launch_pdl(ln_mix_kernel<ITEMS, 6, NT, LAZY>, dim3(a.R), dim3(threads), 0, st, a);
+        case 1: return launch_pdl(ln_mix_kernel<ITEMS, 1, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 2: return launch_pdl(ln_mix_kernel<ITEMS, 2, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 3: return launch_pdl(ln_mix_kernel<ITEMS, 3, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 4: return launch_pdl(ln_mix_kernel<ITEMS, 4, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 6: return launch_pdl(ln_mix_kernel<ITEMS, 6, NT>, dim3(a.R), dim3(threads), 0, st, a);
         default: return cudaErrorInvalidValue;
     }
 }
@@ -265,16 +255,22 @@ cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
             default: break;                                   // other widths: the general kernel below
         }
     }
-    // ONE thread shape for every row width: 256 threads, element it*256 + tid.  The decode mat-vecs rebuild
-    // these rows in their prologue (matvec_q.cu) with the same shape, hence the same sums: decode, sequence
-    // and batch evaluation of a model stay bit-identical whatever its width.
-    const int items = (a.D + 255) / 256;
-    if (items <= 1) return launch_ln_mix_i<1, 256>(a, 256, st);
-    if (items <= 2) return launch_ln_mix_i<2, 256>(a, 256, st);
-    if (items <= 4) return launch_ln_mix_i<4, 256>(a, 256, st);
-    if (items <= 8) return launch_ln_mix_i<8, 256>(a, 256, st);
-    if (items <= 16) return launch_ln_mix_i<16, 256, true>(a, 256, st);
-    return launch_ln_mix_i<32, 256, true>(a, 256, st);
+    if (a.D <= LN_SMALL_D) {
+        // Rows up to 2048 wide: 256 threads, element it*256 + tid.  The decode mat-vecs rebuild these
+        // rows in their prologue (matvec_q.cu) with the same thread shape, hence the same sums.
+        const int items = (a.D + 255) / 256;
+        if (items <= 1) return launch_ln_mix_i<1, 256>(a, 256, st);
+        if (items <= 2) return launch_ln_mix_i<2, 256>(a, 256, st);
+        if (items <= 4) return launch_ln_mix_i<4, 256>(a, 256, st);
+        return launch_ln_mix_i<8, 256>(a, 256, st);
+    }
+    // Wider rows (no fused prologue exists for them): up to 1024 threads with every operand in registers before the dependency
+    // wait.  (A 256-thread shape with operands fetched item by item was tried for these widths: the fetches serialise behind the
+    // warp shuffles of the q8 blocks, 88 us per launch on the 14B shape.)
+    const int items = a.D <= 4096 ? 4 : 8;
+    const int threads = (((a.D + items - 1) / items) + 31) / 32 * 32;
+    if (items == 4) return launch_ln_mix_i<4, 1024>(a, threads, st);
+    return launch_ln_mix_i<8, 1024>(a, threads, st);
 }
 
 __global__ void __launch_bounds__(256) ln_act_kernel(const float * x /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */, int ldx, int D, const float * __restrict__ w,

@@ -19,6 +19,7 @@
 // epilogue (one q8 block per column), so chained products need no extra launch.
 #include "matvec_common.cuh"
 #include "launch.cuh"
+#include "tp_ll.cuh"
 #include <cstdlib>
 
 namespace rb {
@@ -134,6 +135,14 @@ matvec_kernel(const __grid_constant__ MatvecBatch B) {
     for (int r = 0; r < MATVEC_R; r++)
 #pragma unroll
         for (int c = 0; c < NCOL; c++) if (lane == r * NCOL + c) mine = res[r][c];
+    if (NCOL == 1 && (J.epi == EPI_TP_PUSH || J.epi == EPI_TP_PUSH_SIGMOID)) {        // fused tensor-parallel all-reduce, producer side (see matvec_q.cu)
+        static_assert(MATVEC_R * TP_LL_WORLD == 32, "one lane per (row, peer)");
+        float val = __shfl_sync(FULL, mine, lane & (MATVEC_R - 1));
+        if (J.epi == EPI_TP_PUSH_SIGMOID) val = sigmoidf_ref(val);
+        const int m = row0 + (lane & (MATVEC_R - 1)), peer = lane / MATVEC_R;
+        if (m < M && peer < B.tp.world) tp_push(B.tp, B.tp.site_push, tp_flag(B.tp, B.tp.site_push), peer, (size_t) J.tp_off + m, val);
+        return;
+    }
     const bool want_q = (J.out_act.f != nullptr);
     if (lane < MATVEC_R * NCOL) {
         const int r = lane / NCOL, c = lane % NCOL;
@@ -249,6 +258,8 @@ cudaError_t launch_matvec(const MatvecBatch & b_in, cudaStream_t st) {
         total += (((int) b.job[j].W.M + MATVEC_ROWS - 1) / MATVEC_ROWS) * b.ks;
     }
     b.cta_begin[b.n_jobs] = total;
+    for (int j = 0; j < b.n_jobs; j++)
+        if ((b.job[j].epi == EPI_TP_PUSH || b.job[j].epi == EPI_TP_PUSH_SIGMOID) && (b.T != 1 || !b.tp.ll[0] || b.tp.site_push < 0)) return cudaErrorInvalidValue;
     if (type_quantized(type)) return launch_matvec_async(b, total, st);
     if (b.pro.kind != PRO_NONE) return cudaErrorInvalidValue;      // prologues exist in the quantised kernel only
     if (type == T_F32 && smallk_ok(b)) return launch_smallk(b, st);
