@@ -55,7 +55,9 @@ __device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, i
 // aligned 32-element blocks.  LN(x[r]) and -- in sequence mode -- LN(x[r-1]) (the token-shift
 // source, recomputed instead of waiting for the neighbouring CTA) run through the same
 // reductions; both use identical arithmetic, so the recomputed row is bit-identical.
-template <int ITEMS, int NOUT, int NT>
+// TPG (tensor-parallel decode, one row): the row is first gathered from the peers' partial sums (kernels.h TpWait); that variant
+// fetches its constants after the gather (it waits for the peers anyway) to stay within the register budget.
+template <int ITEMS, int NOUT, int NT, bool TPG = false>
 __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMixArgs a) {
     __shared__ double red[4][32];
     const int r = blockIdx.x, D = a.D, nt = blockDim.x;
@@ -64,7 +66,7 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
 
     pdl_trigger();
     float x[2][ITEMS], xs[ITEMS], w[ITEMS], bia[ITEMS], mu[NOUT][ITEMS];
-    {      // constants and the (read-only) input state first, then wait for the producer of x
+    auto load_constants = [&]() {
 #pragma unroll
         for (int it = 0; it < ITEMS; it++) {
             const int e = it * nt + threadIdx.x;
@@ -74,7 +76,8 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
 #pragma unroll
             for (int o = 0; o < NOUT; o++) mu[o][it] = valid ? a.mu[o][e] : 0.0f;
         }
-    }
+    };
+    if constexpr (!TPG) load_constants();      // constants and the (read-only) input state first, then wait for the producer of x
     pdl_wait();
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
@@ -83,7 +86,7 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
         x[0][it] = valid ? a.x[(size_t) r * D + e] : 0.0f;
         x[1][it] = (valid && !from_state) ? a.x[(size_t) (r - 1) * D + e] : 0.0f;
     }
-    if (a.wait.site >= 0) {                                  // tensor-parallel decode: x = base row (+) the ranks' partial sums, still in flight
+    if constexpr (TPG) {                                     // x = base row (+) the ranks' partial sums, still in flight
         const uint2 * inbox = tp_inbox(a.tp, a.wait.site);
         const unsigned want = tp_flag(a.tp, a.wait.site);
 #pragma unroll
@@ -91,6 +94,7 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
             const int e = it * nt + threadIdx.x;
             if (e < D) { x[0][it] = tp_gather_element(a.tp, a.wait, inbox, want, x[0][it], e); a.wait.x_out[e] = x[0][it]; }
         }
+        load_constants();
     }
     const int nrow = from_state ? 1 : 2;                     // rows to normalise (uniform per CTA)
     float scale[2];
@@ -230,6 +234,11 @@ static bool ln_mix_seq_ok(const LnMixArgs & a) {
 
 template <int ITEMS, int NT>
 static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_t st) {
+    if (a.wait.site >= 0) {                                  // tensor-parallel decode (v4: 3 att mixes, 2 ffn mixes)
+        if (a.n_out == 3) return launch_pdl(ln_mix_kernel<ITEMS, 3, NT, true>, dim3(1), dim3(threads), 0, st, a);
+        if (a.n_out == 2) return launch_pdl(ln_mix_kernel<ITEMS, 2, NT, true>, dim3(1), dim3(threads), 0, st, a);
+        return cudaErrorInvalidValue;
+    }
     switch (a.n_out) {
         case 1: return launch_pdl(ln_mix_kernel<ITEMS, 1, NT>, dim3(a.R), dim3(threads), 0, st, a);
         case 2: return launch_pdl(ln_mix_kernel<ITEMS, 2, NT>, dim3(a.R), dim3(threads), 0, st, a);
@@ -270,6 +279,7 @@ cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st) {
     const int items = a.D <= 4096 ? 4 : 8;
     const int threads = (((a.D + items - 1) / items) + 31) / 32 * 32;
     if (items == 4) return launch_ln_mix_i<4, 1024>(a, threads, st);
+    if (threads <= 768) return launch_ln_mix_i<8, 768>(a, threads, st);      // 85 registers per thread instead of 64: no spills at D = 5120 (640 threads)
     return launch_ln_mix_i<8, 1024>(a, threads, st);
 }
 
