@@ -66,9 +66,13 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
 
     pdl_trigger();
     float x[2][ITEMS], xs[ITEMS], w[ITEMS], bia[ITEMS], mu[NOUT][ITEMS];
+    // SPLIT (few wide rows, i.e. decode of a wide model): gridDim.y = ITEMS CTAs share a row; each computes the row statistics
+    // (same reduction, same bits) but mixes / quantises only item blockIdx.y, so the serial q8 shuffle chains of a row run in parallel.
+    const int my_it = gridDim.y > 1 ? (int) blockIdx.y : -1;
     auto load_constants = [&]() {
 #pragma unroll
         for (int it = 0; it < ITEMS; it++) {
+            if (my_it >= 0 && it != my_it) continue;
             const int e = it * nt + threadIdx.x;
             const bool valid = e < D;
             xs[it] = (valid && from_state) ? a.state_in[soff + e] : 0.0f;
@@ -92,7 +96,10 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
 #pragma unroll
         for (int it = 0; it < ITEMS; it++) {
             const int e = it * nt + threadIdx.x;
-            if (e < D) { x[0][it] = tp_gather_element(a.tp, a.wait, inbox, want, x[0][it], e); a.wait.x_out[e] = x[0][it]; }
+            if (e < D) {
+                x[0][it] = tp_gather_element(a.tp, a.wait, inbox, want, x[0][it], e);
+                if (my_it < 0 || it == my_it) a.wait.x_out[e] = x[0][it];
+            }
         }
         load_constants();
     }
@@ -105,6 +112,7 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
         const int e = it * nt + threadIdx.x;
         const bool valid = e < D;
         const int p = it;
+        if (my_it >= 0 && it != my_it) continue;
         const float x0 = __fadd_rn(__fmul_rn(__fmul_rn(x[0][it], scale[0]), w[p]), bia[p]);
         float xp = xs[p];                                    // state value ...
         if (nrow == 2) xp = __fadd_rn(__fmul_rn(__fmul_rn(x[1][it], scale[1]), w[p]), bia[p]);   // ... or LN(x[r-1])
@@ -234,17 +242,21 @@ static bool ln_mix_seq_ok(const LnMixArgs & a) {
 
 template <int ITEMS, int NT>
 static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_t st) {
+    // a handful of wide rows: split every row over ITEMS CTAs (see the kernel).  A TP gather must then not be in place: every CTA
+    // reads the whole base row while its siblings write their items of the gathered row.
+    const int items_used = (a.D + threads - 1) / threads;
+    const dim3 grid(a.R, (a.D > LN_SMALL_D && a.R <= 8 && (a.wait.site < 0 || a.wait.x_out != a.x)) ? items_used : 1);
     if (a.wait.site >= 0) {                                  // tensor-parallel decode (v4: 3 att mixes, 2 ffn mixes)
-        if (a.n_out == 3) return launch_pdl(ln_mix_kernel<ITEMS, 3, NT, true>, dim3(1), dim3(threads), 0, st, a);
-        if (a.n_out == 2) return launch_pdl(ln_mix_kernel<ITEMS, 2, NT, true>, dim3(1), dim3(threads), 0, st, a);
+        if (a.n_out == 3) return launch_pdl(ln_mix_kernel<ITEMS, 3, NT, true>, grid, dim3(threads), 0, st, a);
+        if (a.n_out == 2) return launch_pdl(ln_mix_kernel<ITEMS, 2, NT, true>, grid, dim3(threads), 0, st, a);
         return cudaErrorInvalidValue;
     }
     switch (a.n_out) {
-        case 1: return launch_pdl(ln_mix_kernel<ITEMS, 1, NT>, dim3(a.R), dim3(threads), 0, st, a);
-        case 2: return launch_pdl(ln_mix_kernel<ITEMS, 2, NT>, dim3(a.R), dim3(threads), 0, st, a);
-        case 3: return launch_pdl(ln_mix_kernel<ITEMS, 3, NT>, dim3(a.R), dim3(threads), 0, st, a);
-        case 4: return launch_pdl(ln_mix_kernel<ITEMS, 4, NT>, dim3(a.R), dim3(threads), 0, st, a);
-        case 6: return launch_pdl(ln_mix_kernel<ITEMS, 6, NT>, dim3(a.R), dim3(threads), 0, st, a);
+        case 1: return launch_pdl(ln_mix_kernel<ITEMS, 1, NT>, grid, dim3(threads), 0, st, a);
+        case 2: return launch_pdl(ln_mix_kernel<ITEMS, 2, NT>, grid, dim3(threads), 0, st, a);
+        case 3: return launch_pdl(ln_mix_kernel<ITEMS, 3, NT>, grid, dim3(threads), 0, st, a);
+        case 4: return launch_pdl(ln_mix_kernel<ITEMS, 4, NT>, grid, dim3(threads), 0, st, a);
+        case 6: return launch_pdl(ln_mix_kernel<ITEMS, 6, NT>, grid, dim3(threads), 0, st, a);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -64,6 +64,7 @@ struct Workspace {
     float * wkv_ds = nullptr, * wkv_pc = nullptr;   // chunk-parallel WKV5/6 scratch (head size 64, rows on the tensor-core path)
     float * tp_send = nullptr, * tp_recv = nullptr;   // tensor parallel: [rows][2*D] all-reduce buffers of the ffn ([partial Wv k | r shards])
     float * tp_att = nullptr;                         // [rows][D] partial att output
+    float * x_alt = nullptr;                          // fused tensor parallelism: second residual row (a gather reads one and writes the other)
     float * logits = nullptr;     // [logit_rows][V]
     float * logits_part = nullptr; // tensor parallel: this rank's vocabulary slice
     int   logit_rows = 0;

@@ -61,7 +61,7 @@ bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows
         ok = ok && dalloc(ws, ws.wkv_ds, chunks * D * 64) && dalloc(ws, ws.wkv_pc, chunks * D);
     }
     if (m.tp.world > 1) {
-        ok = ok && dalloc(ws, ws.tp_send, 2 * n) && dalloc(ws, ws.tp_recv, 2 * n) && dalloc(ws, ws.tp_att, n);
+        ok = ok && dalloc(ws, ws.tp_send, 2 * n) && dalloc(ws, ws.tp_recv, 2 * n) && dalloc(ws, ws.tp_att, n) && dalloc(ws, ws.x_alt, n);
         ok = ok && cudaMemset(ws.tp_send, 0, 2 * n * sizeof(float)) == cudaSuccess;     // the r-shard half stays zero outside this rank's slice
     }
     const size_t v_pad = m.tp.world > 1 ? (size_t) m.tp.world * ((m.n_vocab + m.tp.world - 1) / m.tp.world) : m.n_vocab;
@@ -82,9 +82,10 @@ struct Pass {
 
     TpFused tpf;                  // fused tensor-parallel collectives: single-row decode over connected peer memory
     bool tp_fused = false;
+    float * xres = nullptr;       // the residual row(s); under fused tensor parallelism it alternates between ws.x and ws.x_alt
 
     Pass(const Model & m_, Workspace & ws_, const ForwardArgs & fa_, cudaStream_t st_)
-        : m(m_), ws(ws_), fa(fa_), st(st_), R(fa_.R), D(m_.n_embed), sstride(m_.state_len()) {
+        : m(m_), ws(ws_), fa(fa_), st(st_), R(fa_.R), D(m_.n_embed), sstride(m_.state_len()), xres(ws_.x) {
         static const bool off = [] { const char * e = getenv("RWKV_B200_TP_NO_FUSE"); return e && e[0] == '1'; }();
         if (m.tp.world > 1 && R == 1 && !off && D <= TP_LL_MAX_D) { tpf = tp_fused_desc(m.tp); tp_fused = tpf.ll[0] != nullptr; }
     }
@@ -195,14 +196,16 @@ struct Pass {
     float * sout(uint32_t layer, size_t off) const { return fa.state_out + (size_t) layer * m.layer_state_len() + off; }
 
     TpWait tp_wait(int site, bool gated) const {
-        TpWait w; w.site = site; w.gated = gated ? 1 : 0; w.n = (int) D; w.n_slice = (int) (D / m.tp.world); w.x_out = ws.x;
+        TpWait w; w.site = site; w.gated = gated ? 1 : 0; w.n = (int) D; w.n_slice = (int) (D / m.tp.world);
+        w.x_out = xres == ws.x ? ws.x_alt : ws.x;             // never in place: several CTAs gather the same base row
         return w;
     }
     void ln_mix(uint32_t layer, bool att, int kind, int n_out, const float * const * mu, bool want_sx, const Act * outs = nullptr, const TpWait * wait = nullptr) {
         const LayerW & l = m.layers[layer];
         LnMixArgs a;
         if (wait) { a.tp = tpf; a.wait = *wait; }
-        a.x = ws.x; a.ln_w = att ? l.ln1_w : l.ln2_w; a.ln_b = att ? l.ln1_b : l.ln2_b;
+        a.x = xres;
+        if (wait) xres = wait->x_out;                         // from here on the gathered row is the residual a.ln_w = att ? l.ln1_w : l.ln2_w; a.ln_b = att ? l.ln1_b : l.ln2_b;
         const size_t slot = att ? D : 0;                       // [ffn_xx, att_xx, ...] (rwkv_graph.inc:545-606)
         a.state_in = sin(layer, slot); a.state_out = sout(layer, slot);
         a.state_stride = sstride; a.batch = fa.batch; a.R = R; a.D = (int) D; a.kind = kind; a.n_out = n_out;
@@ -484,11 +487,12 @@ struct Pass {
         pdl_site() = 0;
         if (tp_fused && fa.logits) {                          // the last ffn's partial sums are still in the inbox: materialise the final residual row
             const TpWait w = tp_wait(2 * (int) m.n_layer - 1, true);
-            chk(launch_tp_gather_row(tpf, w, ws.x, st));
+            chk(launch_tp_gather_row(tpf, w, xres, st));
+            xres = w.x_out;
         }
         if (fa.logits) {
             const int rows = fa.batch ? R : 1;
-            const float * x = fa.batch ? ws.x : ws.x + (size_t) (R - 1) * D;
+            const float * x = fa.batch ? xres : xres + (size_t) (R - 1) * D;
             pdl_site() = 32;
             chk(launch_ln_act(x, (int) D, rows, (int) D, m.ln_out_w, m.ln_out_b, produced(ws.head_in, {&m.head}, rows), st));
             if (m.tp.world > 1) {      // vocabulary rows are sharded: gather the slices (equal-sized, zero-padded at the end)
