@@ -90,7 +90,21 @@ struct Pass {
         if (m.tp.world > 1 && R == 1 && !off && D <= TP_LL_MAX_D) { tpf = tp_fused_desc(m.tp); tp_fused = tpf.ll[0] != nullptr; }
     }
 
-    void chk(cudaError_t e) { if (err == cudaSuccess && e != cudaSuccess) err = e; }
+    // RWKV_B200_SYNC_DEBUG=1 (never under graph capture: use sequence calls): synchronise after every launch and name the first that fails
+    int n_launch = 0;
+    void chk(cudaError_t e) {
+        static const bool dbg = [] { const char * v = getenv("RWKV_B200_SYNC_DEBUG"); return v && v[0] == '1'; }();
+        n_launch++;
+        if (dbg && err == cudaSuccess && e == cudaSuccess) {
+            cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+            cudaStreamIsCapturing(st, &cs);
+            if (cs == cudaStreamCaptureStatusNone) {
+                e = cudaStreamSynchronize(st);
+                if (e != cudaSuccess) fprintf(stderr, "[rwkv_b200] launch group %d (site %d, R = %d) failed: %s\n", n_launch, pdl_site(), R, cudaGetErrorString(e));
+            }
+        }
+        if (err == cudaSuccess && e != cudaSuccess) err = e;
+    }
 
     static MatvecJob job(const DevMat & W, const Act & x, float * out, int ldo, int epi) {
         MatvecJob j; j.W = W; j.x = x; j.out = out; j.ldo = ldo; j.epi = epi; return j;
@@ -205,7 +219,8 @@ struct Pass {
         LnMixArgs a;
         if (wait) { a.tp = tpf; a.wait = *wait; }
         a.x = xres;
-        if (wait) xres = wait->x_out;                         // from here on the gathered row is the residual a.ln_w = att ? l.ln1_w : l.ln2_w; a.ln_b = att ? l.ln1_b : l.ln2_b;
+        if (wait) xres = wait->x_out;                         // from here on the gathered row is the residual
+        a.ln_w = att ? l.ln1_w : l.ln2_w; a.ln_b = att ? l.ln1_b : l.ln2_b;
         const size_t slot = att ? D : 0;                       // [ffn_xx, att_xx, ...] (rwkv_graph.inc:545-606)
         a.state_in = sin(layer, slot); a.state_out = sout(layer, slot);
         a.state_stride = sstride; a.batch = fa.batch; a.R = R; a.D = (int) D; a.kind = kind; a.n_out = n_out;
