@@ -86,8 +86,10 @@ struct Pass {
 
     Pass(const Model & m_, Workspace & ws_, const ForwardArgs & fa_, cudaStream_t st_)
         : m(m_), ws(ws_), fa(fa_), st(st_), R(fa_.R), D(m_.n_embed), sstride(m_.state_len()), xres(ws_.x) {
-        static const bool off = [] { const char * e = getenv("RWKV_B200_TP_NO_FUSE"); return e && e[0] == '1'; }();
-        if (m.tp.world > 1 && R == 1 && !off && D <= TP_LL_MAX_D) { tpf = tp_fused_desc(m.tp); tp_fused = tpf.ll[0] != nullptr; }
+        // opt-in: measured slower than the one-shot collective kernels on the 14B shape at 2 / 4 / 8 GPUs (profiles/r02/tp_scaling_midround.md)
+        const char * e = getenv("RWKV_B200_TP_FUSE");
+        const bool on = e && e[0] == '1';
+        if (m.tp.world > 1 && R == 1 && on && D <= TP_LL_MAX_D) { tpf = tp_fused_desc(m.tp); tp_fused = tpf.ll[0] != nullptr; }
     }
 
     // RWKV_B200_SYNC_DEBUG=1 (never under graph capture: use sequence calls): synchronise after every launch and name the first that fails

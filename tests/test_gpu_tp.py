@@ -24,7 +24,7 @@ def test_tp_matches_single_gpu(fmt, collective, world):
     norm (no collective launch; quantised decode), "p2p" = one-shot all-reduce kernel over peer memory, "nccl" = ncclAllReduce."""
     if n_gpus() < world:
         pytest.skip(f"needs {world} GPUs")
-    env = dict(os.environ, RWKV_B200_TP_NCCL_ONLY="1" if collective == "nccl" else "0", RWKV_B200_TP_NO_FUSE="0" if collective == "fused" else "1")
+    env = dict(os.environ, RWKV_B200_TP_NCCL_ONLY="1" if collective == "nccl" else "0", RWKV_B200_TP_FUSE="1" if collective == "fused" else "0")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
            "--master-port", "29541", os.path.join(ROOT, "tests", "tp_worker.py"), "v4-mini", fmt]
     p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600, env=env)
