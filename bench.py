@@ -1,22 +1,26 @@
 #!/usr/bin/env python3
 """bench.py -- throughput of the hot path on B200 (contract: see the task statement).
 
-Default workload = BASELINE.json configs[1]: RWKV v4 Pile-169M shape, Q4_0 body + FP16
-head, random-init weights written in the ggmf format, single-token decode of one stream per
-GPU with logits.  One "step" = one token through every layer + head.
+Default workload ("main") = BASELINE.json configs[4], the largest single-GPU configuration and the one decode
+shape that is HBM-bound rather than launch-bound: RWKV v4 Pile-14B shape, Q4_1 body + FP16 head, random-init
+weights in the ggmf format, single-token decode of one stream with logits.  One "step" = one token through every
+layer + the head.
+  N = 1   the whole model on one GPU
+  N > 1   the same model tensor-parallel over the N ranks (column / row split weights, all-reduce over NVLink
+          peer memory twice per layer, logits all-gather): same metric string, "scaling": "strong"
+  value         tokens/s with state + token ids resident in HBM (CUDA-graph replay, device-timed; 9.6 GB of weights
+                per step, 75 x the L2)
+  e2e           tokens/s through the rwkv.h C ABI (rwkv_eval with HOST state / logits buffers, copies inside the
+                timed region); pinned buffers, and pageable numpy buffers as the reference's callers pass them
+  roofline      the STEP: algorithmic bytes of one token (every weight byte except the embedding rows not gathered,
+                + state + vectors) / device time per step, against the measured HBM copy bandwidth
+  cpu_baseline  the unmodified reference CPU library (oracle/_ref) on the same model file and tokens; its logits
+                are compared with the GPU arm's ("parity_max_rel")
+  extras        (N = 1) the other BASELINE configs, one compact record each: 169M decode (configs[1]), the Q5_1
+                mat-vec table, v6-1.6B prefill (configs[2]), 256 v7-2.9B streams (configs[3])
+  --impl reference   times that reference alone (all host threads), same config dict
 
-  value  tokens/s with state + token ids resident in HBM (CUDA-graph replay, device-timed)
-  e2e    tokens/s through the rwkv.h C ABI (rwkv_eval with HOST state/logits buffers,
-         host<->device copies inside the timed region)
-  roofline       the dominant kernel of the step (the FP16 head mat-vec, 77 MB) timed with
-                 CUDA events on the engine's stream over rotating copies (> L2)
-  cpu_baseline   the unmodified reference CPU library (oracle/_ref) on the same model file
-  --impl reference  times that reference alone (all host threads it can use)
-
-Other workloads (`--workload`) report the remaining BASELINE configs the same way:
-  gemv      the Q5_1 mat-vec microbenchmark (HBM GB/s on 14B / 1.6B shapes)
-  prefill   v6 1.6B-shape Q5_1, one 1024-token rwkv_eval_sequence
-  streams   v7 2.9B-shape Q8_0, 256 independent streams sharded over the GPUs
+Other workloads (`--workload`) run one config alone: decode (169M), matvec, prefill, streams, tp.
 """
 from __future__ import annotations
 
@@ -118,41 +122,36 @@ def reference_lib():
     return load_reference()
 
 
-def time_reference_decode(model_file: str, tokens, warmup: int, steps: int, threads=None):
-    """tokens/s of the reference's rwkv_eval loop on host cores; picks the best thread count
-    from a short sweep when `threads` is None.  Returns (tok_s, threads, sysinfo)."""
+def time_reference_decode(model_file: str, tokens, warmup: int, per_repeat: int, repeats: int = 5, threads=None, want_logits_at=None):
+    """tokens/s of the reference's rwkv_eval loop on the host cores: ONE model load, `warmup` evals, then `repeats`
+    timed runs of `per_repeat` evals each (>= 0.5 s per run is the caller's job); the best run counts (ggml spawns a
+    disposable thread pool per call, so short cold samples under-report).  Returns (tok_s, threads, sysinfo, logits
+    after token index `want_logits_at` or None, all runs)."""
     L = reference_lib()
     L.lib.rwkv_set_print_errors(None, False)
-    cores = host_cores()
-    cands = [threads] if threads else sorted({c for c in (4, 8, 16, 32, cores // 2, cores) if 1 <= c <= cores})
-    best = (0.0, cands[0])
-    for n in cands:
-        ctx = L.load(model_file, n, 0)
-        st = None
-        lg = np.empty(ctx.logits_len, np.float32)
-        for t in tokens[:max(2, warmup // 2)]:
-            st, _ = ctx.eval(int(t), st, state_out=st, logits_out=lg)
+    n = threads or host_cores()
+    ctx = L.load(model_file, n, 0)
+    st = None
+    lg = np.empty(ctx.logits_len, np.float32)
+    keep = None
+    for i, t in enumerate(tokens[:warmup]):
+        st, _ = ctx.eval(int(t), st, state_out=st, logits_out=lg)
+        if want_logits_at is not None and i == want_logits_at:
+            keep = lg.copy()
+    runs = []
+    pos = warmup
+    for _ in range(repeats):
+        seg = [int(t) for t in tokens[pos:pos + per_repeat]]
+        if len(seg) < per_repeat:
+            pos = warmup
+            seg = [int(t) for t in tokens[pos:pos + per_repeat]]
+        pos += per_repeat
         t0 = time.perf_counter()
-        k = max(4, min(steps, 16)) if len(cands) > 1 else steps
-        for t in tokens[:k]:
-            st, _ = ctx.eval(int(t), st, state_out=st, logits_out=lg)
-        dt = time.perf_counter() - t0
-        ctx.free()
-        if k / dt > best[0]:
-            best = (k / dt, n)
-    if len(cands) > 1:                       # full-length run at the best thread count
-        ctx = L.load(model_file, best[1], 0)
-        st = None
-        lg = np.empty(ctx.logits_len, np.float32)
-        for t in tokens[:warmup]:
-            st, _ = ctx.eval(int(t), st, state_out=st, logits_out=lg)
-        t0 = time.perf_counter()
-        for t in tokens[:steps]:
-            st, _ = ctx.eval(int(t), st, state_out=st, logits_out=lg)
-        dt = time.perf_counter() - t0
-        ctx.free()
-        best = (steps / dt, best[1])
-    return best[0], best[1], L.system_info()
+        for t in seg:
+            st, _ = ctx.eval(t, st, state_out=st, logits_out=lg)
+        runs.append(len(seg) / (time.perf_counter() - t0))
+    ctx.free()
+    return max(runs), n, L.system_info(), keep, runs
 
 
 class Dist:
@@ -292,22 +291,26 @@ def run_decode(args):
             "unit": "tokens/s", "n_gpus": d.world, "steps": K, "warmup": W, "ms_per_step": ms_max / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 dp4a blocks + f32 accumulate (Q4_0 body), f16 head",
             "data": "synthetic (random-init weights in ggmf format, uniform random token ids)",
-            "config": dict(DECODE_CFG, l2="256 MiB scratch written before every timed step (cold L2), one CUDA event pair per step",
-                           value_l2_warm=d.world * K / (ms_warm_max * 1e-3), algorithmic_bytes_per_step=129.8e6,
-                           step_hbm_gbs=129.8e6 / (ms_max / K * 1e-3) / 1e9),
+            "config": DECODE_CFG,
+            "detail": {"l2": "256 MiB scratch written before every timed step (cold L2), one CUDA event pair per step",
+                       "value_l2_warm": d.world * K / (ms_warm_max * 1e-3)},
             "clocks": clocks,
             "e2e": {"value": d.world * K / e2e_s, "unit": "tokens/s", "h2d_bytes_per_step": S * 4 + 4, "d2h_bytes_per_step": S * 4 + V * 4,
                     "api": "rwkv_eval(ctx, token, state_in, state_out, logits_out) with pinned host buffers"},
             "gpu_launches": launches * K,
-            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": ncu_traffic("head_gemv_f16_50277x768"),
-                         "kernel": "gemv_kernel<F16,1> head 50277x768 (77.2 MB), dominant launch of the step",
-                         "us_per_launch": kms * 1e3, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)" if which == "measured" else which},
+            # the STEP against the HBM roofline (129.8 MB per token); this shape is launch-latency-bound, not HBM-bound
+            "roofline": {"bound": "hbm", "achieved": 129.8e6 / (ms_max / K * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                         "frac": 129.8e6 / (ms_max / K * 1e-3) / 1e9 / hbm, "traffic": None,
+                         "what": "whole decode step: 129.8 MB algorithmic bytes per token / device time per token",
+                         "largest_kernel": {"kernel": "matvec_kernel<F16,1> head 50277x768 (77.2 MB)", "us_per_launch": kms * 1e3, "achieved": ach, "frac": ach / hbm,
+                                            "traffic": ncu_traffic("head_gemv_f16_50277x768")},
+                         "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)" if which == "measured" else which},
         }
         if not args.no_cpu:
             try:
-                tok_s, thr, info = time_reference_decode(path, toks[:, 0], 4, 48)
+                tok_s, thr, info, _, runs = time_reference_decode(path, toks[:, 0], 8, 64, repeats=5, threads=min(host_cores(), 16))
                 out["cpu_baseline"] = {"value": tok_s, "unit": "tokens/s", "cores": thr, "kind": "reference",
-                                       "sample": "48 rwkv_eval calls (after 4 warm-up) of the unmodified reference CPU build on the same model file; " + info}
+                                       "sample": "best of 5 runs of 64 rwkv_eval calls (after 8 warm-up, one model load) of the unmodified reference CPU build on the same model file; " + info}
             except Exception as e:  # the baseline is a report, not a dependency
                 out["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": 0, "kind": "reference", "sample": f"not run: {e}"}
     model.free()
@@ -315,28 +318,231 @@ def run_decode(args):
     return out
 
 
+MAIN_SHAPE, MAIN_FMT = "v4-14b", "Q4_1"
+MAIN_CFG = {"workload": "RWKV v4 Pile-14B shape (L40 D5120 V50277 F20480), Q4_1 body + FP16 head, single-token decode of one stream with logits "
+                        "(BASELINE.json configs[4]); one GPU holds the whole model, N > 1 GPUs hold it tensor-parallel",
+            "shape": MAIN_SHAPE, "format": MAIN_FMT, "streams": 1}
+MAIN_METRIC = "decode tokens/s (RWKV v4 14B-shape Q4_1, 1 stream)"
+REF_WARMUP, REF_PER_REPEAT, REF_REPEATS = 2, 5, 5          # reference CPU arm: ~0.15 s per token on 14B -> >= 0.5 s per timed run
+
+
+def main_tokens(n_vocab: int, n: int):
+    return np.random.default_rng(1).integers(0, n_vocab, size=n).astype(np.uint32)
+
+
+def reference_leg(path: str, n_vocab: int):
+    """The reference CPU implementation on the main workload: shared by --impl reference and the cpu_baseline leg, so the two
+    agree by construction (same threads, tokens, repeats)."""
+    toks = main_tokens(n_vocab, REF_WARMUP + REF_PER_REPEAT * REF_REPEATS)
+    tok_s, thr, info, lg, runs = time_reference_decode(path, toks, REF_WARMUP, REF_PER_REPEAT, REF_REPEATS, want_logits_at=REF_WARMUP - 1)
+    sample = (f"best of {REF_REPEATS} runs of {REF_PER_REPEAT} rwkv_eval calls (one model load, {REF_WARMUP} warm-up evals) of the unmodified reference "
+              f"(oracle/_ref) with {thr} threads on the same model file and token stream; runs tok/s = {[round(r, 2) for r in runs]}; " + info)
+    return tok_s, thr, sample, lg
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the same workload."""
+    """--impl reference: the reference's own CPU implementation of the main workload (rank 0 only)."""
     rank, world, _ = dist_env()
     if rank != 0:
         return None
-    import rwkv_cppy_b200
-    from rwkv_cppy_b200 import synth
-    lib = rwkv_cppy_b200.load_rwkv_shared_library()            # only its host-side quantiser is used here
-    path = synth.ensure_model(lib, DECODE_CFG["shape"], DECODE_CFG["format"])
-    K, W = args.steps, max(args.warmup, 3)
-    K = min(K, 96)                                             # bounded sample: ~10 ms/token on host cores
-    rng = np.random.default_rng(1)
-    toks = rng.integers(0, 50277, size=W + K).astype(np.uint32)
-    tok_s, thr, info = time_reference_decode(path, toks, W, K)
-    return {"impl": "reference", "metric": "decode tokens/s (RWKV v4 169M-shape Q4_0, single stream per GPU)", "value": tok_s, "unit": "tokens/s",
-            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": 1e3 / tok_s, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "int8 blocks + f32 accumulate (ggml CPU)", "data": "synthetic (same model file and token stream)",
-            "config": DECODE_CFG,
-            "cpu_baseline": {"value": tok_s, "unit": "tokens/s", "cores": thr, "kind": "reference",
-                             "sample": f"{K} rwkv_eval calls of the unmodified reference (oracle/_ref) on rank 0; best of a thread sweep; " + info},
+    from rwkv_cppy_b200 import synth                           # pure-numpy writer: this process never maps librwkv.so
+    path = synth.ensure_model(None, MAIN_SHAPE, MAIN_FMT)
+    tok_s, thr, sample, _ = reference_leg(path, synth.SHAPES[MAIN_SHAPE].n_vocab)
+    return {"impl": "reference", "metric": MAIN_METRIC, "value": tok_s, "unit": "tokens/s",
+            "n_gpus": world, "steps": REF_PER_REPEAT, "warmup": REF_WARMUP, "ms_per_step": 1e3 / tok_s, "higher_is_better": True,
+            "scaling": "strong" if world > 1 else "weak",
+            "vs_baseline": None, "dtype": "int8 blocks + f32 accumulate (ggml CPU)", "data": "synthetic (random-init weights in ggmf format, uniform random token ids)",
+            "config": MAIN_CFG,
+            "cpu_baseline": {"value": tok_s, "unit": "tokens/s", "cores": thr, "kind": "reference", "sample": sample},
             "e2e": {"value": tok_s, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+
+
+def main_bytes_per_gpu(shape, world: int) -> dict:
+    """Algorithmic bytes one decode step moves per GPU: every quantised block and FP16 head row this rank owns
+    once, the replicated FP32 vectors, one embedding row, the v4 state read + written."""
+    D, L, V, F = shape.n_embed, shape.n_layer, shape.n_vocab, shape.ffn
+    body = (4 * D * D + 2 * D * F + D * D) * L * 20 // 32          # att k, v, r, out + ffn key, value, receptance; Q4_1 = 20 bytes per 32 weights
+    head = V * D * 2
+    vectors = (11 * D * L + 4 * D) * 4                               # ln1, ln2 (w, b), 5 mixes, time_first, time_decay per layer; ln0, ln_out
+    state = 2 * 5 * D * L * 4
+    emb_row = D * 2
+    return {"body": body // world, "head": head // world, "vectors": vectors, "state": state, "emb_row": emb_row,
+            "total": body // world + head // world + vectors + state + emb_row}
+
+
+def kernel_split():
+    """Share of a decode step by kernel class, from the committed ncu launch list of this workload (profiles/)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "main_kernel_split.json")))
+    except Exception:
+        return None
+
+
+def run_main(args):
+    """BASELINE configs[4]: v4 14B-shape Q4_1 single-stream decode; one GPU, or tensor parallel over the ranks."""
+    import rwkv_cppy_b200
+    from rwkv_cppy_b200 import synth
+    d = Dist()
+    lib = rwkv_cppy_b200.load_rwkv_shared_library()
+    if lib.library.rwkv_b200_device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: the engine has no CPU path")
+    lib.library.rwkv_b200_set_device(d.local)
+    t0 = time.perf_counter()
+    if d.rank == 0:
+        synth.ensure_model(None, MAIN_SHAPE, MAIN_FMT)
+    d.barrier()
+    path = synth.ensure_model(None, MAIN_SHAPE, MAIN_FMT)
+    synth_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    if d.world > 1:
+        ids = [lib.rwkv_b200_tp_unique_id() if d.rank == 0 else None]
+        d.dist.broadcast_object_list(ids, src=0)
+        model = rwkv_cppy_b200.RWKVModel(lib, path, tensor_parallel=(d.rank, d.world, ids[0]))
+        if os.environ.get("RWKV_B200_TP_NCCL_ONLY") != "1":      # collectives over NVLink peer memory instead of NCCL
+            handles = [None] * d.world
+            d.dist.all_gather_object(handles, lib.rwkv_b200_tp_ipc_handle(model._ctx))
+            lib.rwkv_b200_tp_connect(model._ctx, handles)
+    else:
+        model = rwkv_cppy_b200.RWKVModel(lib, path)
+    load_s = time.perf_counter() - t0
+    V, S = model.n_vocab, model.state_len
+    K, W = args.steps, max(args.warmup, 3)
+    toks = main_tokens(V, W + K).reshape(-1, 1)                  # the same stream on every rank
+
+    # ---- value: state + tokens resident, CUDA-graph replay, device-timed ----
+    batch = model.create_batch(1)
+    launches = batch.launches_per_step(True)
+    batch.run_timed(toks[:W], True)
+    d.barrier()
+    sampler = ClockSampler(d.local)
+    sampler.start()
+    ms = batch.run_timed(toks[W:], True)
+    d.barrier()
+    clocks = sampler.stop()
+    ms_max = d.max(ms)
+    batch.free()
+
+    # ---- e2e: rwkv_eval through the C ABI, host buffers, copies inside the timed region (every rank calls it: collective under TP) ----
+    import torch
+    L = lib.library
+    ctxp = model._ctx.ptr
+    n_e2e = min(K, 32)
+
+    def e2e_run(state, logits):
+        L.rwkv_init_state(ctxp, state.ctypes.data_as(PF))
+        sp, lp = state.ctypes.data_as(PF), logits.ctypes.data_as(PF)
+        for t in toks[:W, 0]:
+            assert L.rwkv_eval(ctxp, int(t), sp, sp, lp)
+        d.barrier()
+        t0 = time.perf_counter()
+        for t in toks[W:W + n_e2e, 0]:
+            L.rwkv_eval(ctxp, int(t), sp, sp, lp)
+        dt = time.perf_counter() - t0
+        d.barrier()
+        assert np.isfinite(logits).all()
+        return d.max(dt)
+
+    e2e_pinned = e2e_run(torch.zeros(S, dtype=torch.float32).pin_memory().numpy(), torch.zeros(V, dtype=torch.float32).pin_memory().numpy())
+    e2e_pageable = e2e_run(np.zeros(S, np.float32), np.zeros(V, np.float32))          # what the reference's callers pass (rwkv_cpp_model.py:330-351)
+
+    # logits after the reference leg's comparison token, for the parity figure
+    gpu_lg = None
+    if d.world == 1:
+        ref_toks = main_tokens(V, REF_WARMUP + REF_PER_REPEAT * REF_REPEATS)
+        st = np.zeros(S, np.float32); gpu_lg = np.zeros(V, np.float32)
+        L.rwkv_init_state(ctxp, st.ctypes.data_as(PF))
+        for t in ref_toks[:REF_WARMUP]:
+            L.rwkv_eval(ctxp, int(t), st.ctypes.data_as(PF), st.ctypes.data_as(PF), gpu_lg.ctypes.data_as(PF))
+    model.free()
+
+    out = None
+    if d.rank == 0:
+        hbm, _, which = peaks()
+        step_ms = ms_max / K
+        nb = main_bytes_per_gpu(synth.SHAPES[MAIN_SHAPE], d.world)
+        ach = nb["total"] / (step_ms * 1e-3) / 1e9
+        out = {
+            "metric": MAIN_METRIC, "value": K / (ms_max * 1e-3), "unit": "tokens/s", "n_gpus": d.world, "steps": K, "warmup": W,
+            "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong" if d.world > 1 else "weak", "vs_baseline": None,
+            "dtype": "int8 dp4a blocks + f32 accumulate (Q4_1 body), f16 head", "data": "synthetic (random-init weights in ggmf format, uniform random token ids)",
+            "config": MAIN_CFG, "clocks": clocks,
+            "e2e": {"value": n_e2e / e2e_pinned, "unit": "tokens/s", "h2d_bytes_per_step": S * 4 + 4, "d2h_bytes_per_step": S * 4 + V * 4,
+                    "api": "rwkv_eval(ctx, token, state_in, state_out, logits_out), pinned host buffers" + (" on every rank" if d.world > 1 else ""),
+                    "value_pageable_buffers": n_e2e / e2e_pageable},
+            "gpu_launches": launches * K,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": ncu_traffic("main_step"),
+                         "what": "the whole decode step on one rank: algorithmic bytes per GPU per token / device time per token "
+                                 "(weights stream once per token; 75 x the L2, so every step is cold)",
+                         "algorithmic_bytes_per_gpu_per_step": nb, "kernel_split": kernel_split(),
+                         "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)" if which == "measured" else which},
+            "detail": {"parallelism": f"tp{d.world}" if d.world > 1 else "1 gpu", "launches_per_step": launches, "model_synth_s": round(synth_s, 1),
+                       "model_load_s": round(load_s, 2), "file_bytes": os.path.getsize(path),
+                       "collective": None if d.world == 1 else ("NCCL" if os.environ.get("RWKV_B200_TP_NCCL_ONLY") == "1" else
+                                     ("fused: push from the mat-vec epilogue + gather in the next layer norm" if os.environ.get("RWKV_B200_TP_FUSE") == "1"
+                                      else "one-shot all-reduce kernel over NVLink peer memory (csrc/tp_p2p.cu)"))},
+        }
+        if d.world == 1 and not args.no_cpu:
+            try:
+                tok_s, thr, sample, ref_lg = reference_leg(path, V)
+                out["cpu_baseline"] = {"value": tok_s, "unit": "tokens/s", "cores": thr, "kind": "reference", "sample": sample}
+                if ref_lg is not None and gpu_lg is not None:
+                    out["cpu_baseline"]["parity_max_rel"] = float(np.abs(gpu_lg - ref_lg).max() / max(1.0, float(np.abs(ref_lg).max())))
+                    out["cpu_baseline"]["parity_note"] = f"max |logit_gpu - logit_reference| / max |logit_reference| after {REF_WARMUP} tokens of the same stream"
+            except Exception as e:  # the baseline is a report, not a dependency
+                out["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": 0, "kind": "reference", "sample": f"not run: {e}"}
+    d.close()
+    if out is not None and d.world == 1 and not args.no_extras:
+        out["extras"] = run_extras(args)
+    return out
+
+
+def run_extras(args):
+    """The other BASELINE configs at N = 1, one compact record each (each is also a workload of its own: --workload decode | matvec | prefill | streams)."""
+    ex = {}
+    ns = argparse.Namespace(**vars(args))
+    ns.no_cpu = True
+
+    def attempt(name, fn):
+        t0 = time.perf_counter()
+        try:
+            ex[name] = fn()
+        except Exception as e:                                    # an extra never fails the headline line
+            ex[name] = {"error": str(e)[:300]}
+        ex[name]["wall_s"] = round(time.perf_counter() - t0, 1)
+
+    def decode():
+        ns.steps, ns.warmup = 256, 16
+        r = run_decode(ns)
+        return {"config": "configs[1]: v4 169M-shape Q4_0 decode, 1 stream", "tokens_per_s": r["value"], "us_per_step": r["ms_per_step"] * 1e3,
+                "e2e_tokens_per_s": r["e2e"]["value"], "launches_per_step": r["gpu_launches"] // r["steps"],
+                "step_roofline_frac": r["roofline"]["frac"], "step_hbm_gbs": r["roofline"]["achieved"]}
+
+    def matvec():
+        r = run_gemv(ns)
+        return {"config": "headline kernel metric: dequant-fused mat-vec, rotating copies > L2", "peak_gbs": r["roofline"]["peak"],
+                "rows": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in row.items() if k in ("type", "M", "K", "us", "GBps", "frac_measured")}
+                         for row in r["config"]["rows"]]}
+
+    def prefill():
+        ns.steps, ns.warmup, ns.tokens, ns.shape = 5, 2, 1024, None
+        r = run_prefill(ns)
+        return {"config": "configs[2]: v6 1.6B-shape Q5_1 rwkv_eval_sequence T=1024", "tokens_per_s": r["value"], "ms_per_pass": r["ms_per_step"],
+                "e2e_tokens_per_s": r["e2e"]["value"], "whole_pass_tflops": r["roofline"]["whole_pass_tflops"],
+                "whole_pass_tensor_frac": r["roofline"]["whole_pass_tflops"] / r["roofline"]["peak"],
+                "ffn_key_matmul_tflops": r["roofline"]["achieved"], "ffn_key_matmul_frac": r["roofline"]["frac"]}
+
+    def streams():
+        ns.steps, ns.warmup, ns.streams, ns.shape = 16, 3, 256, None
+        r = run_streams(ns)
+        return {"config": "configs[3]: v7 2.9B-shape Q8_0, 256 independent streams on one GPU", "tokens_per_s": r["value"], "ms_per_step": r["ms_per_step"],
+                "e2e_tokens_per_s": r["e2e"]["value"], "step_roofline_frac": r["roofline"]["frac"], "step_hbm_gbs": r["roofline"]["achieved"]}
+
+    attempt("decode_169m", decode)
+    attempt("matvec", matvec)
+    attempt("prefill_v6_1b6", prefill)
+    attempt("streams_v7_2b9", streams)
+    return ex
 
 
 GEMV_SHAPES = [("Q5_1", 8, 5120, 5120), ("Q5_1", 8, 20480, 5120), ("Q5_1", 8, 5120, 20480), ("Q5_1", 8, 7168, 2048),
@@ -346,16 +552,19 @@ GEMV_SHAPES = [("Q5_1", 8, 5120, 5120), ("Q5_1", 8, 20480, 5120), ("Q5_1", 8, 51
 def run_gemv(args):
     """BASELINE headline kernel metric: achieved HBM GB/s of the dequant-fused mat-vec."""
     import rwkv_cppy_b200
-    from oracle import rwkv_oracle as O          # only to produce valid ggml blocks for the synthetic matrices
+    from rwkv_cppy_b200 import synth
     lib = rwkv_cppy_b200.load_rwkv_shared_library()
     hbm, _, which = peaks()
     rng = np.random.default_rng(0)
     rows = []
     shapes = GEMV_SHAPES if args.only is None else [GEMV_SHAPES[args.only]]
     for name, tid, M, K in shapes:
-        w = (rng.random((min(M, 4096), K), dtype=np.float32) * 2 - 1) / np.float32(np.sqrt(K))
-        raw1 = w.astype(np.float16).view(np.uint8).reshape(-1) if tid == 1 else O.quantize_ref(tid, w.reshape(-1))
-        raw = np.tile(raw1, (M + w.shape[0] - 1) // w.shape[0])[: (raw1.size // w.shape[0]) * M]
+        rows_gen = min(M, 4096)
+        if tid == 1:
+            raw1 = ((rng.random((rows_gen, K), dtype=np.float32) * 2 - 1) / np.float32(np.sqrt(K))).astype(np.float16).view(np.uint8).reshape(-1)
+        else:
+            raw1 = synth._random_blocks(rng, name, rows_gen * K // 32, float(1 / np.sqrt(K))).reshape(-1)      # valid ggml blocks of the format
+        raw = np.ascontiguousarray(np.tile(raw1, (M + rows_gen - 1) // rows_gen)[: (raw1.size // rows_gen) * M])
         one = raw.size
         copies = max(2, int(np.ceil(400e6 / one)))
         m = lib.library.rwkv_b200_matrix_create(tid, raw.ctypes.data, M, K, copies)
@@ -382,9 +591,9 @@ def run_prefill(args):
     lib.library.rwkv_b200_set_device(d.local)
     shape = args.shape or "v6-1b6"
     if d.rank == 0:
-        synth.ensure_model(lib, shape, "FP16-to-Q5_1")
+        synth.ensure_model(lib, shape, "Q5_1")
     d.barrier()
-    path = synth.ensure_model(lib, shape, "FP16-to-Q5_1")
+    path = synth.ensure_model(lib, shape, "Q5_1")
     model = rwkv_cppy_b200.RWKVModel(lib, path)
     T = args.tokens
     toks = np.random.default_rng(1 + d.rank).integers(0, model.n_vocab, size=T).astype(np.uint32)
@@ -415,10 +624,7 @@ def run_prefill(args):
         roof = {"bound": "tensor", "achieved": None, "peak": tf_peak, "unit": "TFLOP/s", "frac": None, "traffic": None,
                 "peak_source": which + " (MEASURED_PEAKS.json dense bf16, sustained)", "whole_pass_tflops": flops / (ms_max * 1e-3) / 1e12}
         try:
-            from oracle import rwkv_oracle as O          # only to produce valid ggml blocks for a synthetic matrix
-            rngw = np.random.default_rng(0)
-            w = (rngw.random((256, D), dtype=np.float32) * 2 - 1) / np.float32(np.sqrt(D))
-            raw1 = O.quantize_ref(8, w.reshape(-1))
+            raw1 = synth._random_blocks(np.random.default_rng(0), "Q5_1", 256 * D // 32, float(1 / np.sqrt(D))).reshape(-1)
             raw = np.ascontiguousarray(np.tile(raw1, (F + 255) // 256)[: (raw1.size // 256) * F])
             L_ = lib.library
             L_.rwkv_b200_matrix_create.restype = ctypes.c_void_p
@@ -436,7 +642,7 @@ def run_prefill(args):
         out = {"metric": f"prefill tokens/s ({shape} Q5_1, T={T})", "value": d.world * T / (ms_max * 1e-3), "unit": "tokens/s", "n_gpus": d.world,
                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                "dtype": "f16 operands (weights dequantised in-kernel), f32 accumulate (tcgen05 / TMEM); f32 recurrence", "data": "synthetic (random-init weights in ggmf format, uniform random token ids)",
-               "config": {"workload": f"{shape} FP16-to-Q5_1 rwkv_eval_sequence T={T} (BASELINE.json configs[2])", "algorithmic_flops_per_step": flops,
+               "config": {"workload": f"{shape} Q5_1 rwkv_eval_sequence T={T} (BASELINE.json configs[2])", "algorithmic_flops_per_step": flops,
                           "l2": "weights 1.26 GB per pass > L2"},
                "clocks": clocks, "e2e": {"value": d.world * T / e2e, "unit": "tokens/s", "h2d_bytes_per_step": T * 4, "d2h_bytes_per_step": (model.state_len + model.n_vocab) * 4,
                                          "api": "rwkv_eval_sequence(ctx, tokens, T, NULL, state_out, logits_out) with host buffers"},
@@ -471,9 +677,9 @@ def run_streams(args):
     lib.library.rwkv_b200_set_device(d.local)
     shape = args.shape or "v7-2b9"
     if d.rank == 0:
-        synth.ensure_model(lib, shape, "FP16-to-Q8_0")
+        synth.ensure_model(lib, shape, "Q8_0")
     d.barrier()
-    path = synth.ensure_model(lib, shape, "FP16-to-Q8_0")
+    path = synth.ensure_model(lib, shape, "Q8_0")
     model = rwkv_cppy_b200.RWKVModel(lib, path)
     B = args.streams // d.world
     batch = model.create_batch(B)
@@ -493,12 +699,29 @@ def run_streams(args):
     launches = batch.launches_per_step(True)
     out = None
     if d.rank == 0:
+        # algorithmic bytes per step per GPU: every weight byte the step multiplies once (file - embedding + B embedding rows)
+        # + each stream's state read and written
+        sh = synth.SHAPES[shape]
+        wbytes = os.path.getsize(path) - sh.n_vocab * sh.n_embed * 2 + B * sh.n_embed * 2
+        step_bytes = wbytes + 2 * B * model.state_len * 4
+        hbm, _, which = peaks()
         out = {"metric": f"decode tokens/s ({shape} Q8_0, {args.streams} independent streams)", "value": d.world * B * K / (ms_max * 1e-3), "unit": "tokens/s",
                "n_gpus": d.world, "steps": K, "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-               "dtype": "int8 dp4a blocks + f32 accumulate", "data": "synthetic", "config": {"workload": f"{shape} FP16-to-Q8_0, {B} streams per GPU, state resident"},
+               "dtype": "int8 dp4a blocks + f32 accumulate", "data": "synthetic", "config": {"workload": f"{shape} Q8_0, {B} streams per GPU, state resident (BASELINE.json configs[3])"},
                "clocks": clocks, "gpu_launches": launches * K,
                "e2e": {"value": d.world * B / e2e, "unit": "tokens/s", "h2d_bytes_per_step": B * 4, "d2h_bytes_per_step": B * model.n_vocab * 4,
-                       "api": "rwkv_b200_batch_eval (host tokens in, host logits out)"}}
+                       "api": "rwkv_b200_batch_eval (host tokens in, host logits out)"},
+               "roofline": {"bound": "hbm", "achieved": step_bytes / (ms_max / K * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                            "frac": step_bytes / (ms_max / K * 1e-3) / 1e9 / hbm, "traffic": None,
+                            "what": "whole batch step per GPU: weights once + every stream's state read and written", "algorithmic_bytes_per_gpu_per_step": step_bytes,
+                            "peak_source": which}}
+        if not args.no_cpu:
+            try:                                           # one stream of the same workload on the host cores (the reference has no batch API: streams are a loop over rwkv_eval)
+                tok_s, thr, info, _, runs = time_reference_decode(path, toks[:, 0], 2, 6, repeats=3)
+                out["cpu_baseline"] = {"value": tok_s, "unit": "tokens/s", "cores": thr, "kind": "reference",
+                                       "sample": "best of 3 runs of 6 rwkv_eval calls of ONE stream (the reference evaluates streams one after the other) on the same model file; " + info}
+            except Exception as ex:
+                out["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": 0, "kind": "reference", "sample": "not run: " + str(ex)}
     batch.free(); model.free(); d.close()
     return out
 
@@ -567,10 +790,11 @@ def run_tp(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=256)
-    ap.add_argument("--warmup", type=int, default=16)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="decode", choices=["decode", "gemv", "prefill", "streams", "tp"])
+    ap.add_argument("--workload", default="main", choices=["main", "decode", "matvec", "gemv", "prefill", "streams", "tp"])
+    ap.add_argument("--no-extras", action="store_true", help="main workload: skip the records of the other BASELINE configs")
     ap.add_argument("--shape", default=None)
     ap.add_argument("--format", default=None, help="tp workload: model format (FP16 or FP16-to-Q4_1)")
     ap.add_argument("--tokens", type=int, default=1024)
@@ -581,7 +805,7 @@ def main():
     if args.impl == "reference":
         out = run_reference(args)
     else:
-        out = {"decode": run_decode, "gemv": run_gemv, "prefill": run_prefill, "streams": run_streams, "tp": run_tp}[args.workload](args)
+        out = {"main": run_main, "decode": run_decode, "matvec": run_gemv, "gemv": run_gemv, "prefill": run_prefill, "streams": run_streams, "tp": run_tp}[args.workload](args)
     if out is not None:
         print(json.dumps(out), flush=True)
 
