@@ -153,6 +153,12 @@ struct Pass {
             if (done[i]) continue;
             MatvecBatch b; b.T = rows;
             if (pro) b.pro = *pro;
+            for (const DevMat * W : pf_next) {                 // weights of the next dependent launch: prefetched into the L2 by this one
+                if (b.n_pf >= 3 || !type_quantized(jobs[i].W.type)) break;
+                const size_t bytes = type_quantized(W->type) ? tiled_bytes(W->type, W->M, W->K) : (size_t) W->M * W->K * type_block_bytes(W->type);
+                b.pf_ptr[b.n_pf] = W->qs; b.pf_bytes[b.n_pf] = (unsigned) std::min<size_t>(bytes & ~(size_t) 15, MATVEC_PF_MAX_BYTES); b.n_pf++;
+            }
+            pf_next.clear();
             if (tp_site >= 0) { b.tp = tpf; b.tp.site_push = tp_site; }
             for (size_t k = i; k < jobs.size() && b.n_jobs < MATVEC_MAX_JOBS; k++)
                 if (!done[k] && jobs[k].W.type == jobs[i].W.type &&
@@ -168,6 +174,15 @@ struct Pass {
         }
     }
     std::vector<const float *> to_half_marks;
+    // set right before a matvec() call: the matrices of the launch that depends on it (single-row decode only; see MatvecBatch::pf_ptr)
+    std::vector<const DevMat *> pf_next;
+    void prefetch_next(std::initializer_list<const DevMat *> mats) {
+        // opt-in (RWKV_B200_L2_PREFETCH=1): on the 14B shape it measured SLOWER (2.93 ms against 2.78 ms per token): the prefetch of up to
+        // 48 MB competes with the 50 - 80 MB stream of the running launch for the 126 MB L2 and for HBM, and costs more than the hand-off it hides
+        static const bool on = [] { const char * e = getenv("RWKV_B200_L2_PREFETCH"); return e && e[0] == '1'; }();
+        pf_next.clear();
+        if (R == 1 && on) pf_next.assign(mats.begin(), mats.end());
+    }
     bool tc_job(const MatvecJob & j, int rows) const {
         return j.x.h != nullptr && (j.x_off % 8) == 0 && (j.x.K % 8) == 0 && matmul_tc_supported(j.W, rows, fa.batch != 0);
     }
@@ -342,6 +357,7 @@ struct Pass {
         const int kind = m.arch_major == 6 ? MIX_SX : MIX_LERP;
         MatvecJob k = job(l.ffn_key, ws.mix[0], nullptr, 0, EPI_RELU_SQ); k.out_act = ws.ffn_k; k.out_act.K = (int) l.ffn_key.M;
         MatvecJob r = job(l.ffn_receptance, ws.mix[1], ws.ffn_r, (int) D, EPI_SIGMOID);
+        prefetch_next({&l.ffn_value});
         if (can_fuse({&l.ffn_key, &l.ffn_receptance})) {
             const MatvecPrologue P = ln_prologue(layer, false, kind);
             k.pro_mu = l.ffn_mu[0]; r.pro_mu = l.ffn_mu[1];
@@ -354,6 +370,10 @@ struct Pass {
         Act kin = ws.ffn_k; kin.K = (int) l.ffn_key.M;
         MatvecJob v = job(l.ffn_value, kin, ws.x, (int) D, EPI_MULADD_TO); v.aux = ws.ffn_r; v.ld_aux = (int) D;
         pdl_site() = 16;
+        if (layer + 1 < m.n_layer) {
+            const LayerW & nx = m.layers[layer + 1];
+            if (m.arch_major == 6) prefetch_next({&nx.maa_w1}); else prefetch_next({&nx.att_key, &nx.att_value, &nx.att_receptance});
+        } else if (fa.logits) prefetch_next({&m.head});
         matvec({v}, R);
     }
 
@@ -361,6 +381,7 @@ struct Pass {
         const LayerW & l = m.layers[layer];
         std::vector<MatvecJob> kvr = {job(l.att_key, ws.mix[0], ws.k, (int) D, EPI_STORE), job(l.att_value, ws.mix[1], ws.v, (int) D, EPI_STORE),
                                     job(l.att_receptance, ws.mix[2], ws.r, (int) D, EPI_SIGMOID)};
+        prefetch_next({&l.att_output});
         if (can_fuse({&l.att_key, &l.att_value, &l.att_receptance})) {
             const MatvecPrologue P = ln_prologue(layer, true, MIX_LERP);
             for (int i = 0; i < 3; i++) kvr[i].pro_mu = l.att_mu[i];
@@ -373,6 +394,7 @@ struct Pass {
         WkvArgs a = wkv_base(layer);
         a.u = l.time_first; a.decay = l.time_decay;
         MatvecJob o = job(l.att_output, ws.y, ws.x, (int) D, EPI_ADD_TO);
+        prefetch_next({&l.ffn_key, &l.ffn_receptance});
         if (can_fuse({&l.att_output})) {
             MatvecPrologue P;
             P.kind = PRO_WKV4; P.D = (int) D;

@@ -2,6 +2,7 @@
 // Every launcher enqueues on the given stream and returns cudaGetLastError().
 #pragma once
 #include "common.h"
+#include <cstdlib>
 
 namespace rb {
 
@@ -103,15 +104,23 @@ struct MatvecBatch {
     int     n_jobs = 0;
     int     T = 1;
     int     ks = 1;                         // K split (cluster size along x) of the quantised kernel; all jobs of a batch share it
+    // L2 prefetch of the weights of the NEXT dependent launch: a decode step is a chain of dependent launches, and between two of them
+    // (tail of one, dependency wait + activation fetch of the next) HBM idles; every warp of this launch asks the L2 for its slice of the
+    // next matrices before it waits, so the memory system keeps streaming through the hand-off.
+    const void * pf_ptr[3] = {};
+    unsigned     pf_bytes[3] = {};
+    int          n_pf = 0;
 };
+constexpr unsigned MATVEC_PF_MAX_BYTES = 48u << 20;      // per matrix: the L2 also holds the stream of the running launch
 // K split of a quantised (M x K) mat-vec: a function of the shape only, so that every evaluation
 // of the same matrix adds its partial sums in the same order.  Splits while the row blocks alone
 // would leave most SMs idle and every CTA keeps at least five 1024-weight chunks (below that the
 // fixed cost of a CTA outweighs the extra parallelism: measured on 5120x5120 vs 5120x20480).
 inline int matvec_ksplit(uint32_t M, uint32_t K) {
+    static const int min_chunks = [] { const char * e = getenv("RWKV_B200_KSPLIT_MIN_CHUNKS"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 5; }();   // tuning switch
     const int row_blocks = (int) ((M + 31) / 32), nch = (int) ((K / 32 + TILE_BLOCKS - 1) / TILE_BLOCKS);
     int ks = 1;
-    while (row_blocks * ks < 3 * device_sm_count() && ks < 4 && nch / (ks * 2) >= 5) ks *= 2;
+    while (row_blocks * ks < 3 * device_sm_count() && ks < 4 && nch / (ks * 2) >= min_chunks) ks *= 2;
     return ks;
 }
 
@@ -183,6 +192,7 @@ struct LnMixArgs {
     // fused tensor parallelism (R == 1): the row is first gathered from the peers' partial sums (kernels.h TpWait; `x` is the base row)
     TpFused tp;
     TpWait  wait;
+    int     dbg_skip_stats = 0;      // timing experiments only
 };
 cudaError_t launch_ln_mix(const LnMixArgs & a, cudaStream_t st);
 

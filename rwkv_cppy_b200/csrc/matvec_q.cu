@@ -326,6 +326,16 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
             }
         }
     }
+    if (B.n_pf > 0 && lane == 0) {                       // this warp's slice of the next launch's weights -> L2 (see MatvecBatch)
+        const unsigned nw = gridDim.x * gridDim.y * GA_WARPS, wid = (blockIdx.y * gridDim.x + blockIdx.x) * GA_WARPS + warp;
+        for (int p = 0; p < B.n_pf; p++) {
+            const unsigned per = ((B.pf_bytes[p] + nw - 1) / nw + 15u) & ~15u, off = wid * per;
+            if (off < B.pf_bytes[p]) {
+                const unsigned len = min(per, B.pf_bytes[p] - off) & ~15u;
+                if (len) bulk_prefetch_l2(reinterpret_cast<const uint8_t *>(B.pf_ptr[p]) + off, len);
+            }
+        }
+    }
     XCursor<TYPE, NCOL> xc;
     if (PRO == PRO_NONE) xc.init(J.x, J.x_off, col0, T, lane);
     ProLnRegs<PIT> pln; ProWkvRegs<PIT> pwk;

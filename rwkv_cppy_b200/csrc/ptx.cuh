@@ -45,6 +45,10 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+// hint: bring [src, src + bytes) into the L2 (bytes % 16 == 0); no completion, no destination
+__device__ __forceinline__ void bulk_prefetch_l2(const void * src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(src), "r"(bytes) : "memory");
+}
 // 2-D tiled tensor copy global -> shared through a CUtensorMap (SASS UTMALDG)
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void * tmap, int c0, int c1, uint32_t bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
