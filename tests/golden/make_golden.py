@@ -35,7 +35,7 @@ def main():
     os.makedirs(os.path.join(HERE, "models"), exist_ok=True)
     for a, v in ARCHS.items():
         shutil.copy(f"{REF_TESTS}/expected-logits-{v}.bin", HERE)
-        fmts = SIX if a == "6v0" else ["FP32", "FP16"]
+        fmts = SIX + ["FP32-to-Q5_0"] if a == "6v0" else ["FP32", "FP16"]      # FP32-to-Q5_0: the file tests/test_quantization_format_compatibility.c opens as 6v0-3m-Q5_0.bin
         for f in fmts:
             shutil.copy(f"{REF_TESTS}/tiny-rwkv-{v}-{f}.bin", os.path.join(HERE, "models"))
     out, sha = {}, {}
