@@ -49,6 +49,17 @@ RWKV_API bool   rwkv_b200_batch_eval(struct rwkv_b200_batch * batch, const uint3
  * with_logits != 0 computes the head every step (logits stay in HBM).  Measurement aid. */
 RWKV_API bool   rwkv_b200_batch_run_timed(struct rwkv_b200_batch * batch, const uint32_t * tokens, size_t n_steps, int with_logits, double * ms);
 
+/* One token per stream like rwkv_b200_batch_eval, then temperature / top-p sampling ON THE DEVICE: tokens_out[n_streams] (host)
+ * receives one sampled id per stream and the logits never leave HBM (at 256 streams of V = 65536 that is 1 KB instead of 67 MB of
+ * device-to-host traffic per step).  Restates python/sampling.py:10-52 of the reference (softmax; temperature == 0 -> argmax;
+ * top_p < 1 -> probabilities below the top-p cutoff zeroed; probs ** (1 / temperature); np.random.choice).  np.random.choice draws one
+ * uniform per call: the caller supplies it, uniforms[n_streams] in [0, 1) (host), from any generator.  logit_bias is not supported here. */
+RWKV_API bool   rwkv_b200_batch_eval_sample(struct rwkv_b200_batch * batch, const uint32_t * tokens, float temperature, float top_p,
+                                            const float * uniforms, uint32_t * tokens_out);
+/* The same sampler on n_rows x n_vocab host logits (parity tests). */
+RWKV_API bool   rwkv_b200_sample_logits(const float * logits, size_t n_rows, size_t n_vocab, float temperature, float top_p,
+                                        const float * uniforms, uint32_t * tokens_out);
+
 /* Number of kernel launches one decode step of this batch performs (graph nodes). */
 RWKV_API size_t rwkv_b200_batch_launches_per_step(const struct rwkv_b200_batch * batch, int with_logits);
 

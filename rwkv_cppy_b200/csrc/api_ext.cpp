@@ -19,6 +19,9 @@ struct rwkv_b200_batch {
     int * h_tokens = nullptr;                    // pinned [n]
     cudaGraphExec_t graph[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};   // [state parity][logits]
     size_t graph_nodes[2] = {0, 0};
+    // on-device sampling (allocated on first use)
+    float * d_probs = nullptr, * d_u = nullptr, * h_u = nullptr;
+    uint32_t * d_picked = nullptr, * h_picked = nullptr;
 };
 
 namespace {
@@ -142,6 +145,11 @@ void rwkv_b200_batch_free(struct rwkv_b200_batch * b) {
     for (int p = 0; p < 2; p++) for (int l = 0; l < 2; l++) if (b->graph[p][l]) cudaGraphExecDestroy(b->graph[p][l]);
     for (int i = 0; i < 2; i++) if (b->d_state[i]) cudaFree(b->d_state[i]);
     if (b->h_tokens) cudaFreeHost(b->h_tokens);
+    if (b->d_probs) cudaFree(b->d_probs);
+    if (b->d_u) cudaFree(b->d_u);
+    if (b->d_picked) cudaFree(b->d_picked);
+    if (b->h_u) cudaFreeHost(b->h_u);
+    if (b->h_picked) cudaFreeHost(b->h_picked);
     b->ws.~Workspace(); new (&b->ws) Workspace();
     rwkv_free(b->ctx);
     delete b;
@@ -201,6 +209,63 @@ bool rwkv_b200_batch_eval(struct rwkv_b200_batch * b, const uint32_t * tokens, f
     if (logits_out) CTX_CUDA(ctx, cudaMemcpyAsync(logits_out, b->ws.logits, b->n * (size_t) m.n_vocab * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream), false);
     CTX_CUDA(ctx, cudaStreamSynchronize(ctx->stream), false);
     CTX_CHECK(ctx, !tp_error_pending(m.tp), RWKV_ERROR_GRAPH, false, "Tensor-parallel collective timed out waiting for a peer rank; results of this call are invalid");
+    return true;
+}
+
+// ---- on-device sampling ------------------------------------------------------------------------
+static bool batch_sample_buffers(rwkv_b200_batch * b) {
+    rwkv_context * ctx = b->ctx;
+    if (b->d_probs) return true;
+    const size_t V = ctx->model->n_vocab;
+    CTX_CUDA(ctx, cudaMalloc((void **) &b->d_probs, b->n * V * sizeof(float)), false);
+    CTX_CUDA(ctx, cudaMalloc((void **) &b->d_u, b->n * sizeof(float)), false);
+    CTX_CUDA(ctx, cudaMalloc((void **) &b->d_picked, b->n * sizeof(uint32_t)), false);
+    CTX_CUDA(ctx, cudaMallocHost((void **) &b->h_u, b->n * sizeof(float)), false);
+    CTX_CUDA(ctx, cudaMallocHost((void **) &b->h_picked, b->n * sizeof(uint32_t)), false);
+    return true;
+}
+
+bool rwkv_b200_batch_eval_sample(struct rwkv_b200_batch * b, const uint32_t * tokens, float temperature, float top_p, const float * uniforms, uint32_t * tokens_out) {
+    if (!b) return false;
+    rwkv_context * ctx = b->ctx;
+    const Model & m = *ctx->model;
+    CTX_CHECK(ctx, tokens && uniforms && tokens_out, RWKV_ERROR_ARGS, false, "NULL argument");
+    CTX_CHECK(ctx, temperature >= 0.0f && top_p >= 0.0f && top_p <= 1.0f, RWKV_ERROR_ARGS, false, "temperature must be >= 0 and top_p in [0, 1]");
+    for (size_t i = 0; i < b->n; i++) {
+        CTX_CHECK(ctx, tokens[i] < m.n_vocab, RWKV_ERROR_ARGS, false, "Token of stream %zu (%u) is out of range", i, tokens[i]);
+        CTX_CHECK(ctx, uniforms[i] >= 0.0f && uniforms[i] < 1.0f, RWKV_ERROR_ARGS, false, "uniforms[%zu] must be in [0, 1)", i);
+    }
+    CTX_CUDA(ctx, cudaSetDevice(m.device), false);
+    if (!batch_graph(b, b->cur, 1) || !batch_sample_buffers(b)) return false;
+    for (size_t i = 0; i < b->n; i++) { b->h_tokens[i] = (int) tokens[i]; b->h_u[i] = uniforms[i]; }
+    CTX_CUDA(ctx, cudaMemcpyAsync(b->ws.tokens, b->h_tokens, b->n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream), false);
+    CTX_CUDA(ctx, cudaMemcpyAsync(b->d_u, b->h_u, b->n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream), false);
+    CTX_CUDA(ctx, cudaGraphLaunch(b->graph[b->cur][1], ctx->stream), false);
+    b->cur ^= 1;
+    CTX_CUDA(ctx, launch_sample(b->ws.logits, b->d_probs, (int) b->n, (int) m.n_vocab, temperature, top_p, b->d_u, b->d_picked, ctx->stream), false);
+    CTX_CUDA(ctx, cudaMemcpyAsync(b->h_picked, b->d_picked, b->n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream), false);
+    CTX_CUDA(ctx, cudaStreamSynchronize(ctx->stream), false);
+    CTX_CHECK(ctx, !tp_error_pending(m.tp), RWKV_ERROR_GRAPH, false, "Tensor-parallel collective timed out waiting for a peer rank; results of this call are invalid");
+    memcpy(tokens_out, b->h_picked, b->n * sizeof(uint32_t));
+    return true;
+}
+
+bool rwkv_b200_sample_logits(const float * logits, size_t n_rows, size_t n_vocab, float temperature, float top_p, const float * uniforms, uint32_t * tokens_out) {
+    g_last_error = RWKV_ERROR_NONE;
+    RB_CHECK(logits && uniforms && tokens_out && n_rows > 0 && n_vocab > 0, RWKV_ERROR_ARGS, false, "Bad arguments");
+    RB_CHECK(temperature >= 0.0f && top_p >= 0.0f && top_p <= 1.0f, RWKV_ERROR_ARGS, false, "temperature must be >= 0 and top_p in [0, 1]");
+    const int dev = pick_device();
+    RB_CHECK(dev >= 0, RWKV_ERROR_CTX | RWKV_ERROR_UNSUPPORTED, false, "No CUDA device");
+    RB_CUDA(cudaSetDevice(dev), RWKV_ERROR_CTX, false);
+    float * d_l = nullptr, * d_p = nullptr, * d_u = nullptr; uint32_t * d_o = nullptr;
+    const size_t nb = n_rows * n_vocab * sizeof(float);
+    bool ok = cudaMalloc((void **) &d_l, nb) == cudaSuccess && cudaMalloc((void **) &d_p, nb) == cudaSuccess
+              && cudaMalloc((void **) &d_u, n_rows * sizeof(float)) == cudaSuccess && cudaMalloc((void **) &d_o, n_rows * sizeof(uint32_t)) == cudaSuccess;
+    ok = ok && cudaMemcpy(d_l, logits, nb, cudaMemcpyHostToDevice) == cudaSuccess && cudaMemcpy(d_u, uniforms, n_rows * sizeof(float), cudaMemcpyHostToDevice) == cudaSuccess;
+    ok = ok && launch_sample(d_l, d_p, (int) n_rows, (int) n_vocab, temperature, top_p, d_u, d_o, nullptr) == cudaSuccess;
+    ok = ok && cudaMemcpy(tokens_out, d_o, n_rows * sizeof(uint32_t), cudaMemcpyDeviceToHost) == cudaSuccess;
+    cudaFree(d_l); cudaFree(d_p); cudaFree(d_u); cudaFree(d_o);
+    RB_CHECK(ok, RWKV_ERROR_GRAPH, false, "sampling failed: %s", cudaGetErrorString(cudaGetLastError()));
     return true;
 }
 

@@ -242,6 +242,10 @@ bool wkv5_chunked_supported(const WkvArgs & a);                // head size 64, 
 cudaError_t launch_wkv5_chunked(const WkvArgs & a, cudaStream_t st);
 constexpr int WKV_CHUNK_TOKENS = 16;
 
+// ---- on-device sampling (sampling.cu; python/sampling.py:10-52 of the reference) ---------------------
+// one token id per row of logits [rows][V]; probs = scratch [rows][V]; u = one uniform in [0, 1) per row (device)
+cudaError_t launch_sample(const float * logits, float * probs, int rows, int V, float temperature, float top_p, const float * u, uint32_t * out, cudaStream_t st);
+
 // tensor parallel ffn tail: x[t][m] += recv[t][D + m] * recv[t][m]  (recv = all-reduced [partial Wv k | r shards], 2*D per row)
 cudaError_t launch_tp_ffn_combine(float * x, const float * recv, int R, int D, cudaStream_t st);
 // fused tensor parallelism: materialise the residual row of a site outside a mat-vec prologue (before ln_out)

@@ -191,6 +191,25 @@ class RWKVBatch:
             raise ValueError("rwkv_b200_batch_eval failed, check stderr")
         return logits
 
+    def eval_sample(self, tokens: Sequence[int], temperature: float = 1.0, top_p: float = 0.8, uniforms: Optional[np.ndarray] = None,
+                    rng: Optional[np.random.Generator] = None) -> np.ndarray:
+        """One step of every stream + temperature / top-p sampling on the device (python/sampling.py semantics): returns the
+        sampled token ids [n_streams]; the logits never leave the GPU.  `uniforms` (one draw in [0, 1) per stream) default to rng.random()."""
+        toks = np.ascontiguousarray(tokens, np.uint32)
+        if toks.shape != (self.n_streams,):
+            raise ValueError(f"tokens has invalid shape {toks.shape}, expected ({self.n_streams},)")
+        if uniforms is None:
+            uniforms = (rng or np.random.default_rng()).random(self.n_streams)
+        u = np.ascontiguousarray(uniforms, np.float32)
+        u = np.minimum(u, np.float32(1.0 - 2.0 ** -24))            # a double just below 1 may round up to 1.0f
+        if u.shape != (self.n_streams,):
+            raise ValueError(f"uniforms has invalid shape {u.shape}, expected ({self.n_streams},)")
+        out = np.empty(self.n_streams, np.uint32)
+        if not self._lib.rwkv_b200_batch_eval_sample(self._ptr, toks.ctypes.data_as(_lib.P_U32), float(temperature), float(top_p),
+                                                     u.ctypes.data_as(_lib.P_FLOAT), out.ctypes.data_as(_lib.P_U32)):
+            raise ValueError("rwkv_b200_batch_eval_sample failed, check stderr")
+        return out
+
     def run_timed(self, tokens: np.ndarray, with_logits: bool = True) -> float:
         """tokens [n_steps][n_streams]; returns device milliseconds for all steps."""
         toks = np.ascontiguousarray(tokens, np.uint32)

@@ -69,6 +69,8 @@ class RWKVSharedLibrary:
         sig("rwkv_b200_batch_get_state", [vp, sz, P_FLOAT], b)
         sig("rwkv_b200_batch_get_state_prefix", [vp, sz, P_FLOAT], b)
         sig("rwkv_b200_batch_eval", [vp, P_U32, P_FLOAT], b)
+        sig("rwkv_b200_batch_eval_sample", [vp, P_U32, ctypes.c_float, ctypes.c_float, P_FLOAT, P_U32], b)
+        sig("rwkv_b200_sample_logits", [P_FLOAT, sz, sz, ctypes.c_float, ctypes.c_float, P_FLOAT, P_U32], b)
         sig("rwkv_b200_batch_run_timed", [vp, P_U32, sz, ctypes.c_int, ctypes.POINTER(ctypes.c_double)], b)
         sig("rwkv_b200_batch_launches_per_step", [vp, ctypes.c_int], sz)
         sig("rwkv_b200_sequence_run_timed", [vp, P_U32, sz, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)], b)
