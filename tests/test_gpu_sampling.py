@@ -49,16 +49,16 @@ def test_device_sampler_edge_cases(raw_lib):
     V = 50277                                                # not a multiple of anything
     rng = np.random.default_rng(0)
     x = rng.standard_normal((4, V)).astype(np.float32)
-    x[0, 123] = 50.0                                         # one dominant token: every setting must return it
+    x[0, 123] = 50.0                                         # one dominant token: a mid-range draw must return it under every setting
     for T, P in ((1.0, 0.8), (0.3, 0.1), (2.0, 1.0), (0.0, 0.5)):
-        out = dev_sample(raw_lib.lib, x, T, P, np.float32([0.0, 0.25, 0.5, 0.999999]))
+        out = dev_sample(raw_lib.lib, x, T, P, np.float32([0.5, 0.25, 0.0, 0.999999]))
         assert out[0] == 123 and np.all(out < V)
         for i in range(1, 4):
             if T == 0.0:
                 assert out[i] == int(np.argmax(x[i]))
             else:
-                assert out[i] == S.sample_logits(x[i], T, P, float(np.float32([0.0, 0.25, 0.5, 0.999999])[i])) or \
-                    S.boundary_distance(x[i], T, P, float(np.float32([0.0, 0.25, 0.5, 0.999999])[i])) < 1e-5
+                assert out[i] == S.sample_logits(x[i], T, P, float(np.float32([0.5, 0.25, 0.0, 0.999999])[i])) or \
+                    S.boundary_distance(x[i], T, P, float(np.float32([0.5, 0.25, 0.0, 0.999999])[i])) < 1e-5
 
 
 def test_batch_eval_sample_equals_sampling_the_returned_logits(shared_library):
