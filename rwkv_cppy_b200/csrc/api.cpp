@@ -238,7 +238,10 @@ bool rwkv_eval_sequence_in_chunks(struct rwkv_context * ctx, const uint32_t * to
     CTX_CUDA(ctx, cudaSetDevice(m.device), false);
     int cur = 0;
     if (!load_state(ctx, state_in, ctx->d_state[cur])) return false;
-    if (!run_sequence(ctx, tokens, sequence_len, chunk_size, cur, logits_out != nullptr)) return false;
+    // The caller's chunk size only exists to stay under ggml's node limit (rwkv.h:121-155); there is no such limit here, and tiling by it
+    // would make FP16 / quantised results depend on it (rows >= 64 take the tensor-core path).  The engine's own tiling is used whatever
+    // the chunk size, so the call equals rwkv_eval_sequence bit for bit.
+    if (!run_sequence(ctx, tokens, sequence_len, SEQ_MAX_ROWS, cur, logits_out != nullptr)) return false;
     return store_outputs(ctx, ctx->d_state[cur], ctx->wsn.logits, state_out, logits_out);
 }
 

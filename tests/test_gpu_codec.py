@@ -30,6 +30,29 @@ def test_device_dequant_bit_exact_on_ggml_vectors(raw_lib, name):
     assert np.array_equal(y.reshape(-1).view(np.uint32), cv[f"{name}/deq"].view(np.uint32))
 
 
+@pytest.mark.parametrize("name", list(QT))
+def test_device_dequant_non_finite_scales(raw_lib, name):
+    """Blocks whose FP16 scale (or minimum) is +-inf or NaN: the device produces inf / NaN exactly where dequantize_row_* does (the numpy
+    restatement, pinned to ggml on the finite vectors) and the same finite values elsewhere.  NaN payloads are not compared: x86
+    propagates the operand's payload, the GPU returns the canonical NaN."""
+    rng = np.random.default_rng(7)
+    bs = {"q4_0": 18, "q4_1": 20, "q5_0": 22, "q5_1": 24, "q8_0": 34}[name]
+    raw = rng.integers(0, 256, size=(64, bs), dtype=np.uint8)
+    raw[:, 0:2] = (rng.standard_normal(64) * 0.05).astype(np.float16).view(np.uint8).reshape(64, 2)
+    if name in ("q4_1", "q5_1"):
+        raw[:, 2:4] = (rng.standard_normal(64) * 0.5).astype(np.float16).view(np.uint8).reshape(64, 2)
+    for i, v in enumerate([np.inf, -np.inf, np.nan]):
+        raw[i, 0:2] = np.array([v], np.float16).view(np.uint8)
+        if name in ("q4_1", "q5_1"):
+            raw[8 + i, 2:4] = np.array([v], np.float16).view(np.uint8)
+    y = dev_dequant(raw_lib.lib, QT[name], raw, 2, 32 * 32).reshape(-1)
+    with np.errstate(all="ignore"):
+        ref = O.dequantize(QT[name], raw.reshape(-1))
+    assert np.array_equal(np.isnan(y), np.isnan(ref)) and np.array_equal(np.isposinf(y), np.isposinf(ref)) and np.array_equal(np.isneginf(y), np.isneginf(ref))
+    fin = np.isfinite(ref)
+    assert np.array_equal(y[fin].view(np.uint32), ref[fin].view(np.uint32))
+
+
 @pytest.mark.parametrize("fmt", util.SIX)
 def test_device_dequant_bit_exact_on_model_tensors(raw_lib, fmt):
     """Every quantised tensor of the committed 6v0 files, after upload + repack."""
