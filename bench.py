@@ -155,9 +155,20 @@ def time_reference_decode(model_file: str, tokens, warmup: int, per_repeat: int,
 
 
 class Dist:
-    """torch.distributed only as plumbing: barrier + max over ranks."""
+    """torch.distributed only as plumbing: barrier + max over ranks.  One process group per process: Dist() returns the same object
+    every time (the main workload and its extras share it); close() only takes effect through Dist.shutdown()."""
+    _inst = None
+
+    def __new__(cls, use_cuda: bool = True):
+        if cls._inst is None:
+            cls._inst = super().__new__(cls)
+            cls._inst._setup(use_cuda)
+        return cls._inst
 
     def __init__(self, use_cuda: bool = True):
+        pass
+
+    def _setup(self, use_cuda: bool = True):
         self.rank, self.world, self.local = dist_env()
         self.torch = None
         if self.world > 1 or use_cuda:
@@ -197,8 +208,13 @@ class Dist:
         return float(t.item())
 
     def close(self):
-        if self.world > 1:
-            self.dist.destroy_process_group()
+        pass
+
+    @classmethod
+    def shutdown(cls):
+        if cls._inst is not None and cls._inst.world > 1:
+            cls._inst.dist.destroy_process_group()
+        cls._inst = None
 
 
 def head_roofline(lib, n_vocab: int, n_embed: int, iters: int = 200):
@@ -491,9 +507,22 @@ def run_main(args):
                     out["cpu_baseline"]["parity_note"] = f"max |logit_gpu - logit_reference| / max |logit_reference| after {REF_WARMUP} tokens of the same stream"
             except Exception as e:  # the baseline is a report, not a dependency
                 out["cpu_baseline"] = {"value": None, "unit": "tokens/s", "cores": 0, "kind": "reference", "sample": f"not run: {e}"}
-    d.close()
-    if out is not None and d.world == 1 and not args.no_extras:
+    if d.world == 1 and out is not None and not args.no_extras:
         out["extras"] = run_extras(args)
+    elif d.world > 1 and not args.no_extras:
+        # BASELINE configs[3] on the same ranks: 256 independent v7 2.9B-shape streams sharded 256 / N per GPU, weights replicated, no
+        # communication in the data path.  Every rank runs it; rank 0 reports.
+        ns = argparse.Namespace(**vars(args))
+        ns.steps, ns.warmup, ns.streams, ns.shape, ns.no_cpu = 16, 3, 256, None, True
+        try:
+            r = run_streams(ns)
+            rec = None if r is None else {"config": f"configs[3]: v7 2.9B-shape Q8_0, 256 independent streams sharded over {d.world} GPUs ({256 // d.world} per GPU), no collective",
+                                          "tokens_per_s": r["value"], "ms_per_step": r["ms_per_step"], "scaling": "strong (fixed 256-stream job)",
+                                          "step_roofline_frac_per_gpu": r["roofline"]["frac"], "step_hbm_gbs_per_gpu": r["roofline"]["achieved"]}
+        except Exception as e:
+            rec = {"error": str(e)[:300]}
+        if out is not None:
+            out["extras"] = {"streams_v7_2b9_sharded": rec}
     return out
 
 
@@ -806,6 +835,7 @@ def main():
         out = run_reference(args)
     else:
         out = {"main": run_main, "decode": run_decode, "matvec": run_gemv, "gemv": run_gemv, "prefill": run_prefill, "streams": run_streams, "tp": run_tp}[args.workload](args)
+    Dist.shutdown()
     if out is not None:
         print(json.dumps(out), flush=True)
 
