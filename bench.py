@@ -130,7 +130,9 @@ def time_reference_decode(model_file: str, tokens, warmup: int, per_repeat: int,
     L = reference_lib()
     L.lib.rwkv_set_print_errors(None, False)
     n = threads or host_cores()
+    t_load = time.perf_counter()
     ctx = L.load(model_file, n, 0)
+    time_reference_decode.last_load_s = time.perf_counter() - t_load
     st = None
     lg = np.empty(ctx.logits_len, np.float32)
     keep = None
@@ -352,7 +354,8 @@ def reference_leg(path: str, n_vocab: int):
     toks = main_tokens(n_vocab, REF_WARMUP + REF_PER_REPEAT * REF_REPEATS)
     tok_s, thr, info, lg, runs = time_reference_decode(path, toks, REF_WARMUP, REF_PER_REPEAT, REF_REPEATS, want_logits_at=REF_WARMUP - 1)
     sample = (f"best of {REF_REPEATS} runs of {REF_PER_REPEAT} rwkv_eval calls (one model load, {REF_WARMUP} warm-up evals) of the unmodified reference "
-              f"(oracle/_ref) with {thr} threads on the same model file and token stream; runs tok/s = {[round(r, 2) for r in runs]}; " + info)
+              f"(oracle/_ref) with {thr} threads on the same model file and token stream; runs tok/s = {[round(r, 2) for r in runs]}; "
+              f"rwkv_init_from_file took {time_reference_decode.last_load_s:.2f} s; " + info)
     return tok_s, thr, sample, lg
 
 

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <cmath>
 #include <algorithm>
+#include <thread>
 
 namespace rb {
 
@@ -32,6 +33,45 @@ static float half_bits_to_float(uint16_t h) {
 
 namespace {
 
+// Host -> device staging for the weight upload (replaces the reference's malloc / fread / ggml_backend_tensor_set / free per tensor,
+// rwkv_file_format.inc:300-313): the file is an mmap (page cache), a few threads copy slices of it into a ring of PINNED buffers, and
+// each filled buffer goes to the GPU with an asynchronous DMA on the load stream while the threads fill the next one.
+struct Stager {
+    static constexpr size_t BUF = (size_t) 32 << 20;
+    static constexpr int NB = 4, NT = 4;
+    uint8_t * buf[NB] = {};
+    cudaEvent_t ev[NB] = {};
+    int next = 0;
+    bool ok = true;
+    bool init() {
+        for (int i = 0; i < NB && ok; i++) ok = cudaMallocHost((void **) &buf[i], BUF) == cudaSuccess && cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) == cudaSuccess;
+        return ok;
+    }
+    ~Stager() { for (int i = 0; i < NB; i++) { if (buf[i]) cudaFreeHost(buf[i]); if (ev[i]) cudaEventDestroy(ev[i]); } }
+    static void fill(uint8_t * dst, const uint8_t * src, size_t n) {
+        if (n < ((size_t) 4 << 20)) { memcpy(dst, src, n); return; }
+        std::thread th[NT];
+        const size_t per = ((n + NT - 1) / NT + 4095) & ~(size_t) 4095;
+        for (int t = 0; t < NT; t++) {
+            const size_t o = std::min(n, per * t), l = std::min(per, n - o);
+            th[t] = std::thread([=] { if (l) memcpy(dst + o, src + o, l); });
+        }
+        for (int t = 0; t < NT; t++) th[t].join();
+    }
+    // [src, src + n) of the mapping -> device memory `dst`, ordered on `st`
+    bool copy(void * dst, const uint8_t * src, size_t n, cudaStream_t st) {
+        for (size_t off = 0; off < n && ok; off += BUF) {
+            const size_t len = std::min(BUF, n - off);
+            const int b = next++ % NB;
+            ok = cudaEventSynchronize(ev[b]) == cudaSuccess;          // the DMA that last used this buffer has finished
+            if (!ok) break;
+            fill(buf[b], src + off, len);
+            ok = cudaMemcpyAsync((uint8_t *) dst + off, buf[b], len, cudaMemcpyHostToDevice, st) == cudaSuccess && cudaEventRecord(ev[b], st) == cudaSuccess;
+        }
+        return ok;
+    }
+};
+
 struct Loader {
     const GgmfFile & f;
     Model & m;
@@ -39,6 +79,7 @@ struct Loader {
     uint8_t * scratch = nullptr; size_t scratch_size = 0;
     cudaStream_t st = nullptr;
     bool ok = true;
+    Stager stager;
 
     Loader(const GgmfFile & f_, Model & m_) : f(f_), m(m_) {}
 
@@ -120,14 +161,14 @@ struct Loader {
         if (!type_quantized(type)) {
             void * d = bump(nbytes);
             if (!d) return false;
-            if (cudaMemcpy(d, src, nbytes, cudaMemcpyHostToDevice) != cudaSuccess) { ok = false; return false; }
+            if (!stager.copy(d, src, nbytes, st)) { ok = false; return false; }      // stream-ordered; model_load synchronises at the end
             out.qs = d;
             return true;
         }
         void * tiled = bump(tiled_bytes(type, M, K));
         if (!tiled) return false;
         if (nbytes > scratch_size) { ok = false; return false; }
-        if (cudaMemcpyAsync(scratch, src, nbytes, cudaMemcpyHostToDevice, st) != cudaSuccess) { ok = false; return false; }
+        if (!stager.copy(scratch, src, nbytes, st)) { ok = false; return false; }
         if (launch_repack(type, scratch, M, K, tiled, st) != cudaSuccess) { ok = false; return false; }
         if (cudaStreamSynchronize(st) != cudaSuccess) { ok = false; return false; }
         out.qs = tiled; out.rg_stride = (uint32_t) tiled_rg_stride(type, K);
@@ -238,6 +279,7 @@ Model * model_load(const char * path, const TpInfo & tp) {
         L.scratch_size = scratch;
     }
     RB_CUDA(cudaStreamCreate(&L.st), RWKV_ERROR_MODEL | RWKV_ERROR_ALLOC, nullptr);
+    RB_CHECK(L.stager.init(), RWKV_ERROR_MODEL | RWKV_ERROR_ALLOC, nullptr, "Failed to allocate the pinned staging buffers");
     RB_CUDA(matvec_async_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
     RB_CUDA(wkv_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
     RB_CUDA(elementwise_init(), RWKV_ERROR_MODEL | RWKV_ERROR_UNSUPPORTED, nullptr);
