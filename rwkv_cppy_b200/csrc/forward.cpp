@@ -60,6 +60,10 @@ bool workspace_reserve(const Model & m, Workspace & ws, int rows, int logit_rows
         const size_t chunks = ((size_t) rows + WKV_CHUNK_TOKENS - 1) / WKV_CHUNK_TOKENS;
         ok = ok && dalloc(ws, ws.wkv_ds, chunks * D * 64) && dalloc(ws, ws.wkv_pc, chunks * D);
     }
+    if (m.arch_major == 7 && m.head_size == 64 && matmul_tc_enabled() && rows >= matmul_tc_min_rows()) {      // chunk-parallel WKV7: dS_c / S_start[c] and P_c per head and chunk
+        const size_t chunks = ((size_t) rows + WKV7_CHUNK_TOKENS - 1) / WKV7_CHUNK_TOKENS;
+        ok = ok && dalloc(ws, ws.wkv_ds, chunks * D * 64) && dalloc(ws, ws.wkv_pc, chunks * D * 64);
+    }
     if (m.tp.world > 1) {
         ok = ok && dalloc(ws, ws.tp_send, 2 * n) && dalloc(ws, ws.tp_recv, 2 * n) && dalloc(ws, ws.tp_att, n) && dalloc(ws, ws.x_alt, n);
         ok = ok && cudaMemset(ws.tp_send, 0, 2 * n * sizeof(float)) == cudaSuccess;     // the r-shard half stays zero outside this rank's slice

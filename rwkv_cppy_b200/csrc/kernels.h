@@ -238,6 +238,8 @@ constexpr int WKV_SEQ_MIN_ROWS = 8;       // sequences at least this long use th
 cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st);   // state slots: aa, bb, pp at state + {0,1,2}*D
 cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st);   // v5.1 / v5.2 / v6 (w != nullptr => per-token decay)
 cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st);
+bool wkv7_chunked_supported(const WkvArgs & a);                // head size 64, one stream, >= 64 rows, scratch present ([H][ceil(R/32)][64][64] floats x 2)
+constexpr int WKV7_CHUNK_TOKENS = 32;
 bool wkv5_chunked_supported(const WkvArgs & a);                // head size 64, one stream, scratch present, RWKV_B200_NO_WKV_CHUNK != 1
 cudaError_t launch_wkv5_chunked(const WkvArgs & a, cudaStream_t st);
 constexpr int WKV_CHUNK_TOKENS = 16;

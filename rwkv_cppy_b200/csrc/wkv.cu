@@ -368,7 +368,10 @@ cudaError_t launch_wkv5(const WkvArgs & a, cudaStream_t st) {
 // v7.  Thread (hl, i) owns ROW i (value index) of the head state S[i][j]:
 // state[h*S*S + i*S + j] (j = key index).
 // ----------------------------------------------------------------------------------------
-template <int S>
+// CHUNK (sequence rows on the tensor path, head size 64): blockIdx.y is a chunk of W7C tokens; the state entering the chunk comes from
+// the chunk scratch (written by wkv7_chunk_scan_kernel) and is not written back -- phase C of the chunk-parallel form below.
+constexpr int W7C = 32;
+template <int S, bool CHUNK = false>
 __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
     extern __shared__ __align__(16) float sm[];
     pdl_trigger();
@@ -380,8 +383,9 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
     const bool active = (tid < hpb * S) && h < a.H;
     const int e = h * S + i, D = a.D;
     const int hb = (tid / S) * S;
-    const int stream = a.batch ? blockIdx.y : 0;
+    const int stream = (a.batch && !CHUNK) ? blockIdx.y : 0;
     const size_t soff = (size_t) stream * a.state_stride;
+    const int chunk = CHUNK ? (int) blockIdx.y : 0, nchunks = CHUNK ? (int) gridDim.y : 1;
 
     // The head states of the CTA are one contiguous run of hpb*S*S floats.  They move between global and
     // shared memory as consecutive 16-byte pieces (fully coalesced: with 256 streams this kernel is the
@@ -390,7 +394,8 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
     constexpr int RS = S + 4, Q = S / 4;
     float * s_st = sm + 6 * nthr;
     const int h0 = blockIdx.x * hpb, nh = min(hpb, a.H - h0);
-    const float * gin = a.state_in + soff + (size_t) h0 * S * S;
+    const float * gin = CHUNK ? a.chunk_ds + ((size_t) h0 * nchunks + chunk) * S * S : a.state_in + soff + (size_t) h0 * S * S;
+    if (CHUNK) pdl_wait();                                // the chunk states come from the preceding kernel
     for (int f = tid; f < nh * S * Q; f += nthr)
         cp_async16(s_st + (f / Q) * RS + (f % Q) * 4, gin + (size_t) f * 4);
     cp_async_commit();
@@ -404,10 +409,11 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
 #pragma unroll
         for (int j = 0; j < Q; j++) { const float4 f = p[j]; st[4 * j] = f.x; st[4 * j + 1] = f.y; st[4 * j + 2] = f.z; st[4 * j + 3] = f.w; }
     }
-    pdl_wait();
-    const int steps = a.batch ? 1 : a.R;
-    for (int s = 0; s < steps; s++) {
-        const size_t row = a.batch ? stream : s;
+    if (!CHUNK) pdl_wait();
+    const int s_begin = CHUNK ? chunk * W7C : 0;
+    const int steps = CHUNK ? min(a.R, s_begin + W7C) : (a.batch ? 1 : a.R);
+    for (int s = s_begin; s < steps; s++) {
+        const size_t row = (a.batch && !CHUNK) ? stream : s;
         float k = 0, v = 0, r = 0, w = 0, av = 0, g = 0;
         if (active) {
             const size_t x = row * D + e;
@@ -452,6 +458,7 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
         }
         act_store_block(a.y, row, e, active, o);
     }
+    if (CHUNK) return;                                    // the final state is written by the chunk scan
     __syncthreads();
     if (active) {
         float4 * p = reinterpret_cast<float4 *>(s_st + (size_t) tid * RS);
@@ -464,6 +471,115 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
         *reinterpret_cast<float4 *>(gout + (size_t) f * 4) = *reinterpret_cast<const float4 *>(s_st + (f / Q) * RS + (f % Q) * 4);
 }
 
+// ---- chunk-parallel WKV7 (head size 64; sequence rows on the tensor-core path) -----------------------------------------------
+// The v7 recurrence is affine in the state: with G_t = diag(w_t) + a^_t b_t^T (a^ = -kk, b = kk * a; rwkv_operators_wkv_v7.inc:61-99)
+//     S_t = S_{t-1} G_t + v_t k_t^T,        y_t = S_t r_t
+// so over a chunk of W7C tokens   S_end = S_start P_c + dS_c   with   P_c = G_1 ... G_C (the identity pushed through the chunk) and
+// dS_c = the chunk run from a zero state.  Both are the per-row update of wkv7_kernel (a state ROW evolves independently of the others).
+//   A  wkv7_chunk_pd_kernel   grid (chunks, heads): P_c and dS_c of every chunk, all chunks in parallel
+//   B  wkv7_chunk_scan_kernel grid (heads, 4): S_start[c+1] = S_start[c] P_c + dS_c, one 64 x 64 x 64 product per chunk (the only
+//                             sequential part: T / 32 steps instead of T); S_start[c] replaces dS_c in the scratch; final state out
+//   C  wkv7_kernel<64, true>  grid (heads, chunks): the exact recurrence from S_start[c] for the chunk's tokens, outputs fused as before
+// FP32 sums in a different order than the token-by-token scan (S_start through products): tolerance mode, like the tensor-core
+// mat-mul that feeds it; short sequences, FP32 files, batches and other head sizes keep the scan.
+template <int S>
+__global__ void __launch_bounds__(2 * S) wkv7_chunk_pd_kernel(const __grid_constant__ WkvArgs a, float * ds, float * pm, int nchunks) {
+    __shared__ float s_a[S], s_b[S], s_k[S], s_w[S], sy[S];
+    pdl_trigger();
+    const int tid = threadIdx.x, i = tid % S, chunk = blockIdx.x, h = blockIdx.y;
+    const bool is_p = tid >= S;                            // second half of the CTA pushes the identity through the chunk
+    const int e = h * S + i, D = a.D;
+    const float kkc = a.k_k[e], kac = a.k_a[e];
+    float st[S];
+#pragma unroll
+    for (int j = 0; j < S; j++) st[j] = (is_p && j == i) ? 1.0f : 0.0f;
+    pdl_wait();
+    const int s_end = min(a.R, (chunk + 1) * W7C);
+    for (int t = chunk * W7C; t < s_end; t++) {
+        const size_t x = (size_t) t * D + e;
+        float k = a.k[x], v = a.v[x];
+        const float w = a.w[x], av = a.a[x];
+        if (a.layer != 0) v = __fadd_rn(v, __fmul_rn(__fsub_rn(a.v_first[x], v), a.vgate[x]));
+        const float kkp = __fmul_rn(k, kkc);
+        __syncthreads();
+        if (!is_p) sy[i] = kkp;
+        __syncthreads();
+        float ss = 0.0f;
+#pragma unroll
+        for (int j = 0; j < S; j++) ss = __fmaf_rn(sy[j], sy[j], ss);
+        const float kk = __fmul_rn(kkp, __fdiv_rn(1.0f, fmaxf(__fsqrt_rn(ss), 1e-12f)));
+        const float ka = __fmul_rn(k, kac);
+        k = __fadd_rn(k, __fsub_rn(__fmul_rn(av, ka), ka));
+        __syncthreads();
+        if (!is_p) { s_a[i] = -kk; s_b[i] = __fmul_rn(kk, av); s_k[i] = k; s_w[i] = w; }
+        __syncthreads();
+        float sa = 0.0f;
+#pragma unroll
+        for (int j = 0; j < S; j++) sa = __fmaf_rn(s_a[j], st[j], sa);
+        const float vv = is_p ? 0.0f : v;
+#pragma unroll
+        for (int j = 0; j < S; j++) st[j] = __fmaf_rn(sa, s_b[j], __fmaf_rn(st[j], s_w[j], __fmul_rn(vv, s_k[j])));
+    }
+    float * out = (is_p ? pm : ds) + ((size_t) h * nchunks + chunk) * S * S + (size_t) i * S;
+#pragma unroll
+    for (int j = 0; j < S; j += 4) *reinterpret_cast<float4 *>(out + j) = make_float4(st[j], st[j + 1], st[j + 2], st[j + 3]);
+}
+
+// CTA = 16 rows of one head's state; thread (row il, 4 columns).  P_c tiles are double-buffered through shared memory (cp.async).
+template <int S>
+__global__ void __launch_bounds__(256) wkv7_chunk_scan_kernel(const __grid_constant__ WkvArgs a, float * ds, const float * pm, int nchunks) {
+    static_assert(S == 64, "layout below is for 64 x 64 heads");
+    __shared__ __align__(16) float s_P[2][S][S];
+    __shared__ __align__(16) float s_S[16][S];
+    pdl_trigger();
+    const int tid = threadIdx.x, h = blockIdx.x, i0 = blockIdx.y * 16, il = tid / 16, j0 = (tid % 16) * 4;
+    const float * gin = a.state_in + (size_t) h * S * S + (size_t) (i0 + il) * S + j0;
+    *reinterpret_cast<float4 *>(&s_S[il][j0]) = *reinterpret_cast<const float4 *>(gin);      // input state: read-only, before the wait
+    pdl_wait();
+    auto fetch = [&](int c, int buf) {
+        const float * src = pm + ((size_t) h * nchunks + c) * S * S;
+        for (int f = tid; f < S * S / 4; f += 256) cp_async16(&s_P[buf][0][0] + f * 4, src + (size_t) f * 4);
+        cp_async_commit();
+    };
+    fetch(0, 0);
+    for (int c = 0; c < nchunks; c++) {
+        if (c + 1 < nchunks) fetch(c + 1, (c + 1) & 1);
+        float * slot = ds + ((size_t) h * nchunks + c) * S * S + (size_t) (i0 + il) * S + j0;
+        const float4 d = *reinterpret_cast<const float4 *>(slot);                          // dS_c
+        if (c + 1 < nchunks) cp_async_wait<1>(); else cp_async_wait<0>();
+        __syncthreads();                                                                    // P_c landed, s_S holds S_start[c]
+        const float4 cur = *reinterpret_cast<const float4 *>(&s_S[il][j0]);
+        *reinterpret_cast<float4 *>(slot) = cur;                                            // S_start[c] takes dS_c's place
+        float4 acc = d;
+        const float (*P)[S] = s_P[c & 1];
+#pragma unroll 16
+        for (int m = 0; m < S; m++) {
+            const float sv = s_S[il][m];
+            const float4 pv = *reinterpret_cast<const float4 *>(&P[m][j0]);
+            acc.x = __fmaf_rn(sv, pv.x, acc.x); acc.y = __fmaf_rn(sv, pv.y, acc.y); acc.z = __fmaf_rn(sv, pv.z, acc.z); acc.w = __fmaf_rn(sv, pv.w, acc.w);
+        }
+        __syncthreads();                                                                    // everyone has read s_S and this P buffer
+        *reinterpret_cast<float4 *>(&s_S[il][j0]) = acc;
+    }
+    __syncthreads();
+    *reinterpret_cast<float4 *>(a.state_out + (size_t) h * S * S + (size_t) (i0 + il) * S + j0) = *reinterpret_cast<const float4 *>(&s_S[il][j0]);
+}
+
+bool wkv7_chunked_supported(const WkvArgs & a) {
+    static const bool off = [] { const char * e = getenv("RWKV_B200_NO_WKV_CHUNK"); return e && e[0] == '1'; }();
+    return !off && !a.batch && a.S == 64 && a.D == a.H * 64 && a.chunk_ds != nullptr && a.chunk_pc != nullptr && a.R >= 2 * W7C;
+}
+
+static cudaError_t launch_wkv7_chunked(const WkvArgs & a, cudaStream_t st) {
+    const int nchunks = (a.R + W7C - 1) / W7C;
+    cudaError_t e = launch_pdl(wkv7_chunk_pd_kernel<64>, dim3(nchunks, a.H), dim3(128), 0, st, a, a.chunk_ds, a.chunk_pc, nchunks);
+    if (e != cudaSuccess) return e;
+    e = launch_pdl(wkv7_chunk_scan_kernel<64>, dim3(a.H, 4), dim3(256), 0, st, a, a.chunk_ds, (const float *) a.chunk_pc, nchunks);
+    if (e != cudaSuccess) return e;
+    constexpr int threads = 64;
+    return launch_pdl(wkv7_kernel<64, true>, dim3(a.H, nchunks), dim3(threads), (6 * threads + 64 * (64 + 4)) * sizeof(float), st, a);
+}
+
 template <int S>
 static cudaError_t launch_wkv7_t(const WkvArgs & a, cudaStream_t st) {
     const int hpb = S >= 32 ? 1 : 32 / S;
@@ -473,6 +589,7 @@ static cudaError_t launch_wkv7_t(const WkvArgs & a, cudaStream_t st) {
 }
 
 cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st) {
+    if (wkv7_chunked_supported(a)) return launch_wkv7_chunked(a, st);
     switch (a.S) {
         case 8:  return launch_wkv7_t<8>(a, st);
         case 16: return launch_wkv7_t<16>(a, st);
