@@ -427,7 +427,11 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
         sy[tid] = kkp;
         __syncthreads();
         float ss = 0.0f;
-        if (active) for (int j = 0; j < S; j++) ss = __fmaf_rn(sy[hb + j], sy[hb + j], ss);
+        if (active) {                                    // (the per-token vectors are read as float4: a quarter of the shared-memory instructions, same order of sums)
+            const float4 * y4 = reinterpret_cast<const float4 *>(sy + hb);
+#pragma unroll
+            for (int j = 0; j < S / 4; j++) { const float4 f = y4[j]; ss = __fmaf_rn(f.x, f.x, ss); ss = __fmaf_rn(f.y, f.y, ss); ss = __fmaf_rn(f.z, f.z, ss); ss = __fmaf_rn(f.w, f.w, ss); }
+        }
         const float kk = __fmul_rn(kkp, __fdiv_rn(1.0f, fmaxf(__fsqrt_rn(ss), 1e-12f)));
         const float ka = __fmul_rn(k, kac);
         k = __fadd_rn(k, __fsub_rn(__fmul_rn(av, ka), ka));
@@ -438,16 +442,24 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
         float y = 0.0f, bonus = 0.0f;
         if (active) {
             float sa = 0.0f;
+            const float4 * a4 = reinterpret_cast<const float4 *>(s_a + hb), * b4 = reinterpret_cast<const float4 *>(s_b + hb), * k4 = reinterpret_cast<const float4 *>(s_k + hb),
+                         * w4 = reinterpret_cast<const float4 *>(s_w + hb), * r4 = reinterpret_cast<const float4 *>(s_r + hb), * y4 = reinterpret_cast<const float4 *>(sy + hb);
 #pragma unroll
-            for (int j = 0; j < S; j++) sa = __fmaf_rn(s_a[hb + j], st[j], sa);
+            for (int j = 0; j < S / 4; j++) {
+                const float4 f = a4[j];
+                sa = __fmaf_rn(f.x, st[4 * j], sa); sa = __fmaf_rn(f.y, st[4 * j + 1], sa); sa = __fmaf_rn(f.z, st[4 * j + 2], sa); sa = __fmaf_rn(f.w, st[4 * j + 3], sa);
+            }
 #pragma unroll
-            for (int j = 0; j < S; j++) {
-                const float kv = __fmul_rn(v, s_k[hb + j]);
-                st[j] = __fmaf_rn(sa, s_b[hb + j], __fmaf_rn(st[j], s_w[hb + j], kv));
-                y = __fmaf_rn(st[j], s_r[hb + j], y);
+            for (int j = 0; j < S / 4; j++) {
+                const float4 fk = k4[j], fb = b4[j], fw = w4[j], fr = r4[j];
+                st[4 * j]     = __fmaf_rn(sa, fb.x, __fmaf_rn(st[4 * j],     fw.x, __fmul_rn(v, fk.x))); y = __fmaf_rn(st[4 * j],     fr.x, y);
+                st[4 * j + 1] = __fmaf_rn(sa, fb.y, __fmaf_rn(st[4 * j + 1], fw.y, __fmul_rn(v, fk.y))); y = __fmaf_rn(st[4 * j + 1], fr.y, y);
+                st[4 * j + 2] = __fmaf_rn(sa, fb.z, __fmaf_rn(st[4 * j + 2], fw.z, __fmul_rn(v, fk.z))); y = __fmaf_rn(st[4 * j + 2], fr.z, y);
+                st[4 * j + 3] = __fmaf_rn(sa, fb.w, __fmaf_rn(st[4 * j + 3], fw.w, __fmul_rn(v, fk.w))); y = __fmaf_rn(st[4 * j + 3], fr.w, y);
             }
             double rk = 0.0;
-            for (int j = 0; j < S; j++) rk += (double) sy[hb + j];
+#pragma unroll
+            for (int j = 0; j < S / 4; j++) { const float4 f = y4[j]; rk += (double) f.x; rk += (double) f.y; rk += (double) f.z; rk += (double) f.w; }
             bonus = __fmul_rn(v, (float) rk);
         }
         float o = head_norm<S>(y, sy, tid, active, a.gn_eps);
@@ -484,7 +496,7 @@ __global__ void wkv7_kernel(const __grid_constant__ WkvArgs a) {
 // mat-mul that feeds it; short sequences, FP32 files, batches and other head sizes keep the scan.
 template <int S>
 __global__ void __launch_bounds__(2 * S) wkv7_chunk_pd_kernel(const __grid_constant__ WkvArgs a, float * ds, float * pm, int nchunks) {
-    __shared__ float s_a[S], s_b[S], s_k[S], s_w[S], sy[S];
+    __shared__ __align__(16) float s_a[S], s_b[S], s_k[S], s_w[S], sy[S];
     pdl_trigger();
     const int tid = threadIdx.x, i = tid % S, chunk = blockIdx.x, h = blockIdx.y;
     const bool is_p = tid >= S;                            // second half of the CTA pushes the identity through the chunk
@@ -505,8 +517,11 @@ __global__ void __launch_bounds__(2 * S) wkv7_chunk_pd_kernel(const __grid_const
         if (!is_p) sy[i] = kkp;
         __syncthreads();
         float ss = 0.0f;
+        {
+            const float4 * y4 = reinterpret_cast<const float4 *>(sy);
 #pragma unroll
-        for (int j = 0; j < S; j++) ss = __fmaf_rn(sy[j], sy[j], ss);
+            for (int j = 0; j < S / 4; j++) { const float4 f = y4[j]; ss = __fmaf_rn(f.x, f.x, ss); ss = __fmaf_rn(f.y, f.y, ss); ss = __fmaf_rn(f.z, f.z, ss); ss = __fmaf_rn(f.w, f.w, ss); }
+        }
         const float kk = __fmul_rn(kkp, __fdiv_rn(1.0f, fmaxf(__fsqrt_rn(ss), 1e-12f)));
         const float ka = __fmul_rn(k, kac);
         k = __fadd_rn(k, __fsub_rn(__fmul_rn(av, ka), ka));
@@ -514,11 +529,21 @@ __global__ void __launch_bounds__(2 * S) wkv7_chunk_pd_kernel(const __grid_const
         if (!is_p) { s_a[i] = -kk; s_b[i] = __fmul_rn(kk, av); s_k[i] = k; s_w[i] = w; }
         __syncthreads();
         float sa = 0.0f;
+        const float4 * a4 = reinterpret_cast<const float4 *>(s_a), * b4 = reinterpret_cast<const float4 *>(s_b), * k4 = reinterpret_cast<const float4 *>(s_k), * w4 = reinterpret_cast<const float4 *>(s_w);
 #pragma unroll
-        for (int j = 0; j < S; j++) sa = __fmaf_rn(s_a[j], st[j], sa);
+        for (int j = 0; j < S / 4; j++) {
+            const float4 f = a4[j];
+            sa = __fmaf_rn(f.x, st[4 * j], sa); sa = __fmaf_rn(f.y, st[4 * j + 1], sa); sa = __fmaf_rn(f.z, st[4 * j + 2], sa); sa = __fmaf_rn(f.w, st[4 * j + 3], sa);
+        }
         const float vv = is_p ? 0.0f : v;
 #pragma unroll
-        for (int j = 0; j < S; j++) st[j] = __fmaf_rn(sa, s_b[j], __fmaf_rn(st[j], s_w[j], __fmul_rn(vv, s_k[j])));
+        for (int j = 0; j < S / 4; j++) {
+            const float4 fk = k4[j], fb = b4[j], fw = w4[j];
+            st[4 * j]     = __fmaf_rn(sa, fb.x, __fmaf_rn(st[4 * j],     fw.x, __fmul_rn(vv, fk.x)));
+            st[4 * j + 1] = __fmaf_rn(sa, fb.y, __fmaf_rn(st[4 * j + 1], fw.y, __fmul_rn(vv, fk.y)));
+            st[4 * j + 2] = __fmaf_rn(sa, fb.z, __fmaf_rn(st[4 * j + 2], fw.z, __fmul_rn(vv, fk.z)));
+            st[4 * j + 3] = __fmaf_rn(sa, fb.w, __fmaf_rn(st[4 * j + 3], fw.w, __fmul_rn(vv, fk.w)));
+        }
     }
     float * out = (is_p ? pm : ds) + ((size_t) h * nchunks + chunk) * S * S + (size_t) i * S;
 #pragma unroll
@@ -542,10 +567,13 @@ __global__ void __launch_bounds__(256) wkv7_chunk_scan_kernel(const __grid_const
         cp_async_commit();
     };
     fetch(0, 0);
+    float * slot0 = ds + (size_t) h * nchunks * S * S + (size_t) (i0 + il) * S + j0;
+    float4 d_next = *reinterpret_cast<const float4 *>(slot0);
     for (int c = 0; c < nchunks; c++) {
         if (c + 1 < nchunks) fetch(c + 1, (c + 1) & 1);
-        float * slot = ds + ((size_t) h * nchunks + c) * S * S + (size_t) (i0 + il) * S + j0;
-        const float4 d = *reinterpret_cast<const float4 *>(slot);                          // dS_c
+        float * slot = slot0 + (size_t) c * S * S;
+        const float4 d = d_next;                                                            // dS_c (fetched one step ahead: off the critical path)
+        if (c + 1 < nchunks) d_next = *reinterpret_cast<const float4 *>(slot + S * S);
         if (c + 1 < nchunks) cp_async_wait<1>(); else cp_async_wait<0>();
         __syncthreads();                                                                    // P_c landed, s_S holds S_start[c]
         const float4 cur = *reinterpret_cast<const float4 *>(&s_S[il][j0]);
