@@ -106,7 +106,11 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
     const int nrow = from_state ? 1 : 2;                     // rows to normalise (uniform per CTA)
     float scale[2];
     if (a.dbg_skip_stats) { scale[0] = scale[1] = 1.0f; }    // timing experiments only (RWKV_B200_DBG_LN_FAST): wrong results
-    else ln_rows_stats<ITEMS, 2>(x, D, nt, red, scale, 1e-5f);
+    else if (from_state) {                                   // decode / batch rows: one row to normalise, half the reduction chains (same sums for that row)
+        float s1[1];
+        ln_rows_stats<ITEMS, 1>(reinterpret_cast<float (&)[1][ITEMS]>(x[0]), D, nt, red, s1, 1e-5f);
+        scale[0] = s1[0]; scale[1] = 1.0f;
+    } else ln_rows_stats<ITEMS, 2>(x, D, nt, red, scale, 1e-5f);
     // ---- affine, shift state, mixes ----
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
