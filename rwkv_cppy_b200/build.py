@@ -16,6 +16,11 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "librwkv.so")
+# experiment builds (RWKV_B200_BUILD_NAME=trace RWKV_B200_NVCC_FLAGS=-DRWKV_B200_TRACE ...): objects and library go to
+# build/variants/ and leave the product library alone
+if os.environ.get("RWKV_B200_BUILD_NAME"):
+    OBJ = os.path.join(HERE, "build", "variants", "obj_" + os.environ["RWKV_B200_BUILD_NAME"])
+    LIB = os.path.join(HERE, "build", "variants", "librwkv_" + os.environ["RWKV_B200_BUILD_NAME"] + ".so")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

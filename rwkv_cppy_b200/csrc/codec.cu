@@ -198,6 +198,7 @@ template <int ITEMS>
 __global__ void __launch_bounds__(256) embed_ln0_reg_kernel(DevMat emb, const int * __restrict__ tokens, const float * __restrict__ w,
                                                             const float * __restrict__ b, float * __restrict__ x, unsigned int * step) {
     __shared__ double red[2][32];
+    TRACE_DECL_IF(false);
     pdl_trigger();
     if (step && blockIdx.x == 0 && threadIdx.x == 0) *step = *step + 1;     // plain stream-ordered launch: nothing of the previous pass is running
     const int t = blockIdx.x, D = emb.K;
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(256) embed_ln0_reg_kernel(DevMat emb, const in
         lw[it] = valid ? w[e] : 0.0f; lb[it] = valid ? b[e] : 0.0f;
     }
     float scale[1];
-    ln_rows_stats<ITEMS, 1>(v, D, 256, red, scale, 1e-5f);
+    ln_rows_stats<ITEMS, 1>(v, D, 256, red, scale, 1e-5f TRACE_PASS);
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
         const int e = it * 256 + threadIdx.x;

@@ -6,6 +6,7 @@
 #include <cuda_fp16.h>
 #include <cstdint>
 #include "kernels.h"
+#include "trace.cuh"
 
 namespace rb {
 
@@ -63,7 +64,7 @@ __device__ __forceinline__ float round_f16(float v) { return __half2float(__floa
 // warp, butterfly over the warp totals -- so for a given (D, nt) they agree bit for bit.
 // On return x holds x - mean and scale[k] = 1/sqrt(var + eps).  red: [2*NR][32] doubles shared.
 template <int ITEMS, int NR>
-__device__ __forceinline__ void ln_rows_stats(float (&x)[NR][ITEMS], int D, int nt, double (*red)[32], float (&scale)[NR], float eps) {
+__device__ __forceinline__ void ln_rows_stats(float (&x)[NR][ITEMS], int D, int nt, double (*red)[32], float (&scale)[NR], float eps TRACE_ARG) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = nt >> 5;
     double s[NR];
 #pragma unroll
@@ -72,9 +73,11 @@ __device__ __forceinline__ void ln_rows_stats(float (&x)[NR][ITEMS], int D, int 
 #pragma unroll
         for (int it = 0; it < ITEMS; it++) s[k] += (double) x[k][it];
     }
+    TRACE(6);                                                // (the per-thread sums consumed the row: its loads have returned)
 #pragma unroll
     for (int k = 0; k < NR; k++) { s[k] = warp_sum_d(s[k]); if (lane == 0) red[k][warp] = s[k]; }
     __syncthreads();
+    TRACE(7);
     float mean[NR];
 #pragma unroll
     for (int k = 0; k < NR; k++) { const double t = warp_totals_sum_d(lane < nw ? red[k][lane] : 0.0, nw); mean[k] = (float) (t / D); }
@@ -89,9 +92,11 @@ __device__ __forceinline__ void ln_rows_stats(float (&x)[NR][ITEMS], int D, int 
             x[k][it] = v; s2[k] += (double) __fmul_rn(v, v);
         }
     }
+    TRACE(8);
 #pragma unroll
     for (int k = 0; k < NR; k++) { s2[k] = warp_sum_d(s2[k]); if (lane == 0) red[NR + k][warp] = s2[k]; }
     __syncthreads();
+    TRACE(9);
 #pragma unroll
     for (int k = 0; k < NR; k++) {
         const double t = warp_totals_sum_d(lane < nw ? red[NR + k][lane] : 0.0, nw);

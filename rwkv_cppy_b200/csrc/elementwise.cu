@@ -10,6 +10,7 @@
 #include "device_utils.cuh"
 #include "launch.cuh"
 #include "tp_ll.cuh"
+#include "trace.cuh"
 
 namespace rb {
 
@@ -58,18 +59,21 @@ __device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, i
 // TPG (tensor-parallel decode, one row): the row is first gathered from the peers' partial sums (kernels.h TpWait); that variant
 // fetches its constants after the gather (it waits for the peers anyway) to stay within the register budget.
 template <int ITEMS, int NOUT, int NT, bool TPG = false>
-__global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMixArgs a) {
+__global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMixArgs ga) {
     __shared__ double red[4][32];
-    const int r = blockIdx.x, D = a.D, nt = blockDim.x;
-    const bool from_state = a.batch || r == 0;
-    const size_t soff = a.batch ? (size_t) r * a.state_stride : 0;
+    __shared__ __align__(16) unsigned char a_raw[sizeof(LnMixArgs)];
+    args_to_smem(a_raw, &ga);                  // everything read after the dependency wait comes from this copy (launch.cuh)
+    const int r = blockIdx.x, D = ga.D, nt = blockDim.x;
+    const bool from_state = ga.batch || r == 0;
+    const size_t soff = ga.batch ? (size_t) r * ga.state_stride : 0;
 
+    TRACE_DECL_IF(true); TRACE(0);
     pdl_trigger();
     float x[2][ITEMS], xs[ITEMS], w[ITEMS], bia[ITEMS], mu[NOUT][ITEMS];
     // SPLIT (few wide rows, i.e. decode of a wide model): gridDim.y = ITEMS CTAs share a row; each computes the row statistics
     // (same reduction, same bits) but mixes / quantises only item blockIdx.y, so the serial q8 shuffle chains of a row run in parallel.
     const int my_it = gridDim.y > 1 ? (int) blockIdx.y : -1;
-    auto load_constants = [&]() {
+    auto load_constants = [&](const LnMixArgs & a) {
 #pragma unroll
         for (int it = 0; it < ITEMS; it++) {
             if (my_it >= 0 && it != my_it) continue;
@@ -81,8 +85,12 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
             for (int o = 0; o < NOUT; o++) mu[o][it] = valid ? a.mu[o][e] : 0.0f;
         }
     };
-    if constexpr (!TPG) load_constants();      // constants and the (read-only) input state first, then wait for the producer of x
+    if constexpr (!TPG) load_constants(ga);    // constants and the (read-only) input state first, then wait for the producer of x
+    __syncthreads();                           // the argument copy is complete
+    const LnMixArgs & a = *reinterpret_cast<const LnMixArgs *>(a_raw);
+    TRACE(1);
     pdl_wait();
+    TRACE(2);
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
         const int e = it * nt + threadIdx.x;
@@ -101,16 +109,17 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
                 if (my_it < 0 || it == my_it) a.wait.x_out[e] = x[0][it];
             }
         }
-        load_constants();
+        load_constants(a);
     }
     const int nrow = from_state ? 1 : 2;                     // rows to normalise (uniform per CTA)
     float scale[2];
     if (a.dbg_skip_stats) { scale[0] = scale[1] = 1.0f; }    // timing experiments only (RWKV_B200_DBG_LN_FAST): wrong results
     else if (from_state) {                                   // decode / batch rows: one row to normalise, half the reduction chains (same sums for that row)
         float s1[1];
-        ln_rows_stats<ITEMS, 1>(reinterpret_cast<float (&)[1][ITEMS]>(x[0]), D, nt, red, s1, 1e-5f);
+        ln_rows_stats<ITEMS, 1>(reinterpret_cast<float (&)[1][ITEMS]>(x[0]), D, nt, red, s1, 1e-5f TRACE_PASS);
         scale[0] = s1[0]; scale[1] = 1.0f;
-    } else ln_rows_stats<ITEMS, 2>(x, D, nt, red, scale, 1e-5f);
+    } else ln_rows_stats<ITEMS, 2>(x, D, nt, red, scale, 1e-5f TRACE_PASS);
+    TRACE(3);
     // ---- affine, shift state, mixes ----
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
@@ -131,8 +140,11 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
             if (a.kind == MIX_LERP) v[o] = __fadd_rn(__fmul_rn(x0, mu[o][p]), __fsub_rn(xp, __fmul_rn(xp, mu[o][p])));
             else                    v[o] = __fadd_rn(__fmul_rn(sx, mu[o][p]), x0);
         }
+        TRACE(4);
         act_store_blocks<NOUT>(a.out, (size_t) r, e, valid, v);
     }
+    TRACE(5);
+    TRACE_FLUSH(100 + NOUT, gridDim.x * gridDim.y);
 }
 
 // Sequence rows whose consumers are all tensor-core MATMULs (FP16 outputs only: the tolerance-mode path).
@@ -324,6 +336,7 @@ __global__ void __launch_bounds__(256) ln_act_reg_kernel(const float * x /* writ
                                                          const float * __restrict__ b, Act out) {
     __shared__ double red[2][32];
     const int r = blockIdx.x;
+    TRACE_DECL_IF(false);
     pdl_trigger();
     float v[1][ITEMS], lw[ITEMS], lb[ITEMS];
 #pragma unroll
@@ -338,7 +351,7 @@ __global__ void __launch_bounds__(256) ln_act_reg_kernel(const float * x /* writ
         v[0][it] = e < D ? x[(size_t) r * ldx + e] : 0.0f;
     }
     float scale[1];
-    ln_rows_stats<ITEMS, 1>(v, D, 256, red, scale, 1e-5f);
+    ln_rows_stats<ITEMS, 1>(v, D, 256, red, scale, 1e-5f TRACE_PASS);
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
         const int e = it * 256 + threadIdx.x;
@@ -478,3 +491,4 @@ cudaError_t launch_quantize_act(Act a, int R, cudaStream_t st) {
 }
 
 } // namespace rb
+TRACE_EXPORT(rwkv_b200_debug_trace_ew)

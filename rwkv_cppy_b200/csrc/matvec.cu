@@ -33,14 +33,16 @@ constexpr int MATVEC_ROWS  = MATVEC_WARPS * MATVEC_R;     // 32 rows per CTA = o
 template <int TYPE, int NCOL>
 __global__ void __launch_bounds__(MATVEC_WARPS * 32)
 matvec_kernel(const __grid_constant__ MatvecBatch B) {
+    __shared__ __align__(16) unsigned char j_raw[sizeof(MatvecJob)];     // this CTA's job, read from here after the dependency wait (launch.cuh)
     pdl_trigger();
     // which job / row block
     int j = 0;
 #pragma unroll 1
     while (j + 1 < B.n_jobs && (int) blockIdx.x >= B.cta_begin[j + 1]) j++;
-    const MatvecJob & J = B.job[j];
+    args_to_smem(j_raw, &B.job[j]);
+    const MatvecJob & Jp = B.job[j];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int M = J.W.M, K = J.W.K, T = B.T;
+    const int M = Jp.W.M, K = Jp.W.K, T = B.T;
     const int row0 = ((int) blockIdx.x - B.cta_begin[j]) * MATVEC_ROWS + warp * MATVEC_R;
     const int col0 = blockIdx.y * NCOL;
 
@@ -49,10 +51,12 @@ matvec_kernel(const __grid_constant__ MatvecBatch B) {
         const size_t esz = (TYPE == T_F32) ? 4 : 2;
 #pragma unroll
         for (int r = 0; r < MATVEC_R; r++) {
-            const char * p = reinterpret_cast<const char *>(J.W.qs) + (size_t) min(row0 + r, M - 1) * K * esz + (size_t) lane * 128;
+            const char * p = reinterpret_cast<const char *>(Jp.W.qs) + (size_t) min(row0 + r, M - 1) * K * esz + (size_t) lane * 128;
             if ((size_t) lane * 128 < (size_t) K * esz) asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
         }
     }
+    __syncthreads();
+    const MatvecJob & J = *reinterpret_cast<const MatvecJob *>(j_raw);
     pdl_wait();
 
     {
@@ -260,7 +264,12 @@ cudaError_t launch_matvec(const MatvecBatch & b_in, cudaStream_t st) {
     b.cta_begin[b.n_jobs] = total;
     for (int j = 0; j < b.n_jobs; j++)
         if ((b.job[j].epi == EPI_TP_PUSH || b.job[j].epi == EPI_TP_PUSH_SIGMOID) && (b.T != 1 || !b.tp.ll[0] || b.tp.site_push < 0)) return cudaErrorInvalidValue;
-    if (type_quantized(type)) return launch_matvec_async(b, total, st);
+    if (type_quantized(type)) {
+        // single-row decode: tiles beyond the ring are prefetched into the L2 ahead of the dependency wait (matvec_q.cu); RWKV_B200_SELF_PF=<tiles per warp>
+        static const int self_pf = [] { const char * e = getenv("RWKV_B200_SELF_PF"); return e ? atoi(e) : MATVEC_SELF_PF_DEFAULT; }();
+        b.self_pf = b.T == 1 ? self_pf : 0;
+        return launch_matvec_async(b, total, st);
+    }
     if (b.pro.kind != PRO_NONE) return cudaErrorInvalidValue;      // prologues exist in the quantised kernel only
     if (type == T_F32 && smallk_ok(b)) return launch_smallk(b, st);
     if (type == T_F32) return launch_typed<T_F32>(b, total, st);

@@ -66,17 +66,42 @@ __device__ __forceinline__ void unpack_block(int (&wv)[8], const uint4 q0, const
     }
 }
 
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {          // unsigned bytes x signed bytes
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 // one row x one block for all columns
 template <int TYPE, int NCOL>
 __device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<NCOL> & xb,
                                           const uint4 q0, const uint4 q1, const uint32_t qh, const float dw, const float mw) {
     int wv[8];
-    unpack_block<TYPE>(wv, q0, q1, qh);
+#ifndef RWKV_B200_MVQ_NO_HI16
+    constexpr bool HI16 = (TYPE == T_Q4_0 || TYPE == T_Q4_1);
+#else
+    constexpr bool HI16 = false;
+#endif
+    // 4-bit formats: the high nibbles stay where they are (16 x their value, as unsigned bytes) and are summed in a chain of
+    // their own; the chain total is an exact multiple of 16, so `>> 4` gives the same integer the shifted nibbles would --
+    // four shifts fewer per block and two 4-deep dp4a chains instead of one 8-deep
+    if (HI16) { wv[0] = q0.x; wv[1] = q0.y; wv[2] = q0.z; wv[3] = q0.w; }
+    else unpack_block<TYPE>(wv, q0, q1, qh);
 #pragma unroll
     for (int c = 0; c < NCOL; c++) {
         int dp = 0;
+        if (HI16) {
+            int hi = 0;
 #pragma unroll
-        for (int i = 0; i < 8; i++) dp = dp4a_(wv[i], xb.w[c][i], dp);
+            for (int i = 0; i < 4; i++) {
+                dp = dp4a_(wv[i] & 0x0F0F0F0F, xb.w[c][i], dp);
+                hi = dp4a_us((uint32_t) wv[i] & 0xF0F0F0F0u, xb.w[c][4 + i], hi);
+            }
+            dp += hi >> 4;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) dp = dp4a_(wv[i], xb.w[c][i], dp);
+        }
         if (TYPE == T_Q4_0) dp -= 8 * xb.isum[c];
         if (TYPE == T_Q5_0) dp -= 16 * xb.isum[c];
         ra.acc[c] = __fmaf_rn(__fmul_rn(dw, xb.d[c]), (float) dp, ra.acc[c]);

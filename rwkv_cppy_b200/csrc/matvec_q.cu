@@ -19,7 +19,9 @@
 #include "launch.cuh"
 #include "ptx.cuh"
 #include "tp_ll.cuh"
+#include "trace.cuh"
 #include <cstdlib>
+#include <algorithm>
 
 namespace rb {
 
@@ -36,73 +38,66 @@ template <> struct QFmt<T_Q8_0> { static constexpr int QB = 32, HB = 0, DB = 2, 
 template <int TYPE> __host__ __device__ constexpr int ga_stage_bytes() { return GA_R * GA_KC * (QFmt<TYPE>::QB + QFmt<TYPE>::HB + QFmt<TYPE>::DB); }
 template <int TYPE, int S> __host__ __device__ constexpr int ga_smem_bytes() { return GA_WARPS * S * (ga_stage_bytes<TYPE>() + 8); }
 
-// Per-lane cursors into the q8 activation rows (block `lane` of column col0); hoisted out of
-// the chunk loop so an iteration costs one add per pointer.
+// Per-lane cursor into the q8 activation rows (block `lane` of column col0 of the current chunk).  The pointers are
+// loop-carried: an iteration costs one add per plane, nothing is re-derived from the kernel parameters.
 template <int TYPE, int NCOL>
 struct XCursor {
+    static constexpr bool HAS_S = (TYPE == T_Q4_1 || TYPE == T_Q5_1), HAS_I = (TYPE == T_Q4_0 || TYPE == T_Q5_0);
     const int8_t * q; const float * d; const float * s; const int * isum;
     int K, nbrow, tmax;
-    __device__ __forceinline__ void init(const Act & x, int x_off, int col0, int T, int lane) {
+    // positioned at chunk `chunk` of the row
+    __device__ __forceinline__ void init(const Act & x, int x_off, int col0, int T, int lane, int chunk) {
         K = x.K; nbrow = x.K >> 5; tmax = T - 1 - col0;
-        q = x.q + (size_t) col0 * K + x_off + lane * 32;
-        const size_t b0 = (size_t) col0 * nbrow + (x_off >> 5) + lane;
+        q = x.q + (size_t) col0 * K + x_off + lane * 32 + (size_t) chunk * (GA_KC * 32);
+        const size_t b0 = (size_t) col0 * nbrow + (x_off >> 5) + lane + (size_t) chunk * GA_KC;
         d = x.d + b0; s = x.s + b0; isum = x.isum + b0;
+        pin();
     }
-    // Fire-and-forget loads of this lane's share of chunks [0, nch): pulls the whole activation
+    // keeps the pointers in registers (the compiler otherwise rebuilds them from constant memory every iteration)
+    __device__ __forceinline__ void pin() {
+#ifndef RWKV_B200_MVQ_NO_PIN
+        asm volatile("" : "+l"(q), "+l"(d));
+        if (HAS_S) asm volatile("" : "+l"(s));
+        if (HAS_I) asm volatile("" : "+l"(isum));
+#endif
+    }
+    __device__ __forceinline__ void next() { q += GA_KC * 32; d += GA_KC; s += GA_KC; isum += GA_KC; pin(); }
+    // Fire-and-forget loads of this lane's share of the next `n` chunks: pulls the whole activation
     // row into L1 in one round trip.  Under a saturated L2 a dependent load per chunk costs a
     // microsecond each; this way the later load() calls hit L1 (or merge with the miss in flight).
-    __device__ __forceinline__ void warm(int c_lo, int c_hi, int nb, int lane) const {
+    // nb_left = blocks of the row from the current chunk on
+    __device__ __forceinline__ void warm(int n, int nb_left, int lane) const {
 #pragma unroll
         for (int cc = 0; cc < NCOL; cc++) {
             const int dt = NCOL == 1 ? 0 : min(cc, tmax);
 #pragma unroll 1
-            for (int c = c_lo; c < c_hi; c++) {
-                if (c * GA_KC + lane < nb) {
+            for (int c = 0; c < n; c++) {
+                if (c * GA_KC + lane < nb_left) {
                     uint32_t t0, t1;
                     asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t0) : "l"(q + (size_t) dt * K + c * (GA_KC * 32)));
                     asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t1) : "l"(d + dt * nbrow + c * GA_KC));
-                    if (TYPE == T_Q4_1 || TYPE == T_Q5_1) asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t1) : "l"(s + dt * nbrow + c * GA_KC));
-                    if (TYPE == T_Q4_0 || TYPE == T_Q5_0) asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t1) : "l"(isum + dt * nbrow + c * GA_KC));
+                    if (HAS_S) asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t1) : "l"(s + dt * nbrow + c * GA_KC));
+                    if (HAS_I) asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(t1) : "l"(isum + dt * nbrow + c * GA_KC));
                 }
             }
         }
     }
-    __device__ __forceinline__ void load(XBlock<NCOL> & xb, int c) const {      // block c*32 + lane
+    __device__ __forceinline__ void load(XBlock<NCOL> & xb) const {             // this lane's block of the current chunk
 #pragma unroll
         for (int cc = 0; cc < NCOL; cc++) {
             const int dt = NCOL == 1 ? 0 : min(cc, tmax);
-            const int8_t * qp = q + (size_t) dt * K + c * (GA_KC * 32);
+            const int8_t * qp = q + (size_t) dt * K;
             const uint4 lo = *reinterpret_cast<const uint4 *>(qp);
             const uint4 hi = *reinterpret_cast<const uint4 *>(qp + 16);
             xb.w[cc][0] = lo.x; xb.w[cc][1] = lo.y; xb.w[cc][2] = lo.z; xb.w[cc][3] = lo.w;
             xb.w[cc][4] = hi.x; xb.w[cc][5] = hi.y; xb.w[cc][6] = hi.z; xb.w[cc][7] = hi.w;
-            const int bo = dt * nbrow + c * GA_KC;
+            const int bo = dt * nbrow;
             xb.d[cc] = d[bo];
-            if (TYPE == T_Q4_1 || TYPE == T_Q5_1) xb.s[cc] = s[bo];
-            if (TYPE == T_Q4_0 || TYPE == T_Q5_0) xb.isum[cc] = isum[bo];
+            if (HAS_S) xb.s[cc] = s[bo];
+            if (HAS_I) xb.isum[cc] = isum[bo];
         }
     }
 };
-
-// ---- optional timeline of CTA 0 (RWKV_B200_TRACE builds only; tools/decode_trace.py) -----------
-#ifdef RWKV_B200_TRACE
-__device__ unsigned long long g_trace[8192 * 12];
-__device__ unsigned int g_trace_n;
-__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-#define TRACE_DECL unsigned long long tr_[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}
-#define TRACE(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) tr_[i] = gtimer(); } while (0)
-#define TRACE_FLUSH(pro, grid) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { \
-    const unsigned int n_ = atomicAdd(&g_trace_n, 1u) & 8191u; \
-    for (int i_ = 0; i_ < 10; i_++) g_trace[n_ * 12 + i_] = tr_[i_]; g_trace[n_ * 12 + 10] = (pro); g_trace[n_ * 12 + 11] = (grid); } } while (0)
-#define TRACE_ARG , unsigned long long * tr_
-#define TRACE_PASS , tr_
-#else
-#define TRACE_DECL
-#define TRACE(i)
-#define TRACE_FLUSH(pro, grid)
-#define TRACE_ARG
-#define TRACE_PASS
-#endif
 
 // ---- decode prologues (kernels.h MatvecPrologue) ---------------------------------------------------
 // The input vector of the launch as q8 blocks in shared memory (what the chunk loop otherwise
@@ -169,18 +164,17 @@ __device__ __forceinline__ void pro_lnmix_pre(const MatvecPrologue & P, const fl
 }
 // part 2 (after pdl_wait): the row itself; same arithmetic as ln_mix_kernel<., ., 256> (elementwise.cu)
 template <int ITEMS, typename PX>
-__device__ __forceinline__ void pro_lnmix_post(const MatvecBatch & B, const float * __restrict__ mu, const ProLnRegs<ITEMS> & r, PX & px, double (*red)[32] TRACE_ARG) {
-    const MatvecPrologue & P = B.pro;
+__device__ __forceinline__ void pro_lnmix_post(const MatvecPrologue & P, const TpFused & tpf, const float * __restrict__ mu, const ProLnRegs<ITEMS> & r, PX & px, double (*red)[32] TRACE_ARG) {
     float x[1][ITEMS];
     if (P.wait.site >= 0) {                                  // fused tensor parallelism: the row is still in flight from the peers
-        const uint2 * inbox = tp_inbox(B.tp, P.wait.site);
-        const unsigned want = tp_flag(B.tp, P.wait.site);
+        const uint2 * inbox = tp_inbox(tpf, P.wait.site);
+        const unsigned want = tp_flag(tpf, P.wait.site);
 #pragma unroll
         for (int it = 0; it < ITEMS; it++) {
             const int e = it * PRO_NT + threadIdx.x;
             x[0][it] = 0.0f;
             if (e < P.D) {
-                x[0][it] = tp_gather_element(B.tp, P.wait, inbox, want, P.x[e], e);
+                x[0][it] = tp_gather_element(tpf, P.wait, inbox, want, P.x[e], e);
                 if (blockIdx.x == 0) P.wait.x_out[e] = x[0][it];
             }
         }
@@ -192,8 +186,7 @@ __device__ __forceinline__ void pro_lnmix_post(const MatvecBatch & B, const floa
         }
     }
     float scale[1];
-    ln_rows_stats<ITEMS, 1>(x, P.D, PRO_NT, red, scale, 1e-5f);
-    TRACE(7);
+    ln_rows_stats<ITEMS, 1>(x, P.D, PRO_NT, red, scale, 1e-5f TRACE_PASS);
     constexpr int G = 4;
 #pragma unroll
     for (int it0 = 0; it0 < ITEMS; it0 += G) {
@@ -214,7 +207,6 @@ __device__ __forceinline__ void pro_lnmix_post(const MatvecBatch & B, const floa
         }
         pro_store_group<G>(px, v, it0, P.D);
     }
-    TRACE(8);
 }
 
 template <int ITEMS> struct ProWkvRegs { float aa[ITEMS <= 8 ? ITEMS : 1], bb[ITEMS <= 8 ? ITEMS : 1], pp[ITEMS <= 8 ? ITEMS : 1], u[ITEMS <= 8 ? ITEMS : 1], w[ITEMS <= 8 ? ITEMS : 1]; };
@@ -273,27 +265,36 @@ __device__ __forceinline__ void pro_wkv4_post(const MatvecPrologue & P, const Pr
 static_assert(sizeof(MatvecBatch) <= 4096, "kernel parameter space");
 
 template <int TYPE, int NCOL, int S, int PRO = PRO_NONE, int PIT = 4>
-__global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? ((QFmt<TYPE>::QB == 32 || (PRO != PRO_NONE && PIT >= 16)) ? 2 : 3) : (NCOL == 2 ? 2 : 1))
+__global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? ((QFmt<TYPE>::QB == 32 || S >= 5 || (PRO != PRO_NONE && PIT >= 16)) ? 2 : 3) : (NCOL == 2 ? 2 : 1))
 matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     static_assert(PRO == PRO_NONE || NCOL == 1, "prologues are single-row");
     using F = QFmt<TYPE>;
     constexpr int BB = F::QB + F::HB + F::DB;              // bytes per block
     constexpr int STAGE = ga_stage_bytes<TYPE>();
     constexpr bool HAS_M = (TYPE == T_Q4_1 || TYPE == T_Q5_1);
+#ifdef RWKV_B200_MVQ_XNOW
+    constexpr bool PREFETCH_X = false;
+#else
     constexpr bool PREFETCH_X = (NCOL == 1);               // next chunk's activations one iteration ahead
+#endif
     extern __shared__ __align__(128) uint8_t ga_smem[];
     __shared__ float tile[NCOL][GA_WARPS * GA_R];
     __shared__ ProXT<PRO != PRO_NONE, PIT> pro_xs;
     __shared__ double pro_red[PRO == PRO_LNMIX ? 2 : 1][32];
+    // what the kernel reads after the dependency wait: this CTA's job and the prologue descriptor, copied out of the constant bank (launch.cuh)
+    __shared__ __align__(16) unsigned char j_raw[sizeof(MatvecJob)];
+    __shared__ __align__(16) unsigned char p_raw[PRO != PRO_NONE ? sizeof(MatvecPrologue) : 16];
 
     TRACE_DECL; TRACE(0);
     pdl_trigger();
     int j = 0;
 #pragma unroll 1
     while (j + 1 < B.n_jobs && (int) blockIdx.x >= B.cta_begin[j + 1]) j++;
-    const MatvecJob & J = B.job[j];
+    args_to_smem(j_raw, &B.job[j]);
+    if constexpr (PRO != PRO_NONE) args_to_smem(p_raw, &B.pro);
+    const MatvecJob & Jp = B.job[j];                     // the parameter itself: for everything ahead of the wait
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int M = J.W.M, nb = J.W.K >> 5, T = B.T;
+    const int M = Jp.W.M, nb = Jp.W.K >> 5, T = B.T;
     // K split: the `ks` CTAs of a cluster share one block of 32 rows, CTA kr takes a contiguous range
     // of the row's chunks; partial sums meet in the leader's shared memory (see the tail).
     const int ks = B.ks, local = (int) blockIdx.x - B.cta_begin[j];
@@ -309,8 +310,8 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     uint8_t * my = ga_smem + (size_t) warp * S * STAGE;
     const uint32_t my_s = smem_u32(my);
     const uint32_t bars = smem_u32(ga_smem + (size_t) GA_WARPS * S * STAGE) + warp * S * 8;
-    const uint8_t * src0 = reinterpret_cast<const uint8_t *>(J.W.qs) + (size_t) (row0 / GA_R) * J.W.rg_stride + (size_t) cbase * STAGE;
-    const uint32_t last_bytes = (uint32_t) ((GA_R * (nb - (nch_all - 1) * GA_KC) * BB + 15) & ~15);   // the row's final (possibly short) chunk
+    const uint8_t * src0 = reinterpret_cast<const uint8_t *>(Jp.W.qs) + (size_t) (row0 / GA_R) * Jp.W.rg_stride + (size_t) cbase * STAGE;
+    uint32_t last_bytes = (uint32_t) ((GA_R * (nb - (nch_all - 1) * GA_KC) * BB + 15) & ~15);   // the row's final (possibly short) chunk
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < S; s++) mbar_init(bars + s * 8, 1);
@@ -326,6 +327,16 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
             }
         }
     }
+    // Self-prefetch: the tiles of this warp's rows that do not fit the ring go to the L2 now, i.e. while the producer of the
+    // activations (a layer norm, the WKV step: latency-bound kernels that leave HBM idle) is still running; after the dependency
+    // wait the ring refills then come from the L2 instead of DRAM.
+    if (B.self_pf > 0 && lane == 0) {
+        const int c_hi = min(nch, S + B.self_pf);
+        for (int c = S; c < c_hi; c++) {
+            const uint32_t bytes = (cbase + c == nch_all - 1) ? last_bytes : (uint32_t) STAGE;
+            bulk_prefetch_l2(src0 + (size_t) c * STAGE, bytes);
+        }
+    }
     if (B.n_pf > 0 && lane == 0) {                       // this warp's slice of the next launch's weights -> L2 (see MatvecBatch)
         const unsigned nw = gridDim.x * gridDim.y * GA_WARPS, wid = (blockIdx.y * gridDim.x + blockIdx.x) * GA_WARPS + warp;
         for (int p = 0; p < B.n_pf; p++) {
@@ -337,17 +348,19 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
         }
     }
     XCursor<TYPE, NCOL> xc;
-    if (PRO == PRO_NONE) xc.init(J.x, J.x_off, col0, T, lane);
+    if (PRO == PRO_NONE) xc.init(Jp.x, Jp.x_off, col0, T, lane, cbase);
     ProLnRegs<PIT> pln; ProWkvRegs<PIT> pwk;
-    if (PRO == PRO_LNMIX) pro_lnmix_pre<PIT>(B.pro, J.pro_mu, pln);
+    if (PRO == PRO_LNMIX) pro_lnmix_pre<PIT>(B.pro, Jp.pro_mu, pln);
     if (PRO == PRO_WKV4)  pro_wkv4_pre<PIT>(B.pro, pwk);
-    __syncwarp();
+    __syncthreads();                                    // the argument copies are complete
+    const MatvecJob & J = *reinterpret_cast<const MatvecJob *>(j_raw);
+    const MatvecPrologue & P = *reinterpret_cast<const MatvecPrologue *>(p_raw);
     TRACE(1);
     pdl_wait();                                         // activations (and the residual) come from the preceding kernels
     TRACE(2);
     if constexpr (PRO != PRO_NONE) {
-        if (PRO == PRO_LNMIX) pro_lnmix_post<PIT>(B, J.pro_mu, pln, pro_xs, pro_red TRACE_PASS);
-        if (PRO == PRO_WKV4)  pro_wkv4_post<PIT>(B.pro, pwk, pro_xs);
+        if (PRO == PRO_LNMIX) pro_lnmix_post<PIT>(P, B.tp, J.pro_mu, pln, pro_xs, pro_red TRACE_PASS);
+        if (PRO == PRO_WKV4)  pro_wkv4_post<PIT>(P, pwk, pro_xs);
         __syncthreads();
         xc.q = pro_xs.q + lane * 32; xc.d = pro_xs.d + lane; xc.s = pro_xs.s + lane; xc.isum = pro_xs.isum + lane;
         xc.K = 0; xc.nbrow = 0; xc.tmax = 0;
@@ -367,16 +380,24 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     for (int r = 0; r < GA_R; r++) ra[r].clear();
 
     XBlock<NCOL> xb, xn;
-    if (PRO == PRO_NONE && NCOL <= 2 && nch > 2) xc.warm(cbase, cbase + nch, nb, lane);
-    if (PREFETCH_X && nch > 0 && lane < nb - cbase * GA_KC) xc.load(xb, cbase);
+    int left = nb - cbase * GA_KC;                       // blocks of the row from the current chunk on
+    if (PRO == PRO_NONE && NCOL <= 2 && nch > 2) xc.warm(nch, left, lane);
+    if (PREFETCH_X && nch > 0 && lane < left) xc.load(xb);
+    // the refill cursor: source of chunk c + S, and the iteration whose refill is the row's final (short) chunk
+    const uint8_t * src_next = src0 + (size_t) S * STAGE;
+    const int c_last = nch_all - 1 - cbase - S;
+#ifndef RWKV_B200_MVQ_NO_PIN
+    asm volatile("" : "+r"(last_bytes), "+l"(src_next));
+#endif
     int s = 0;
     uint32_t phase = 0;
 #pragma unroll 1
     for (int c = 0; c < nch; c++) {                      // c counts this CTA's chunks; cbase + c is the chunk of the row
-        const int cnt = min(GA_KC, nb - (cbase + c) * GA_KC);
+        const int cnt = min(GA_KC, left);
         const bool act = lane < cnt;
-        if (PREFETCH_X) { if (c + 1 < nch && lane < nb - (cbase + c + 1) * GA_KC) xc.load(xn, cbase + c + 1); }
-        else if (act) xc.load(xb, cbase + c);           // before the wait: independent of the tile
+        if (PREFETCH_X) { xc.next(); if (c + 1 < nch && lane < left - GA_KC) xc.load(xn); }
+        else { if (act) xc.load(xb); xc.next(); }       // before the wait: independent of the tile
+        left -= GA_KC;
         mbar_wait(bars + s * 8, phase);
 
         // the warp's 4 rows x (this lane's block) from the stage into registers, then hand the
@@ -410,10 +431,11 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
         }
         __syncwarp();                                   // every lane has read the stage
         if (lane == 0 && c + S < nch) {
-            const uint32_t bytes = (cbase + c + S == nch_all - 1) ? last_bytes : (uint32_t) STAGE;
+            const uint32_t bytes = c == c_last ? last_bytes : (uint32_t) STAGE;
             mbar_expect_tx(bars + s * 8, bytes);
-            bulk_g2s(my_s + s * STAGE, src0 + (size_t) (c + S) * STAGE, bytes, bars + s * 8);
+            bulk_g2s(my_s + s * STAGE, src_next, bytes, bars + s * 8);
         }
+        src_next += STAGE;
         if (act) {
 #pragma unroll
             for (int r = 0; r < GA_R; r++) {
@@ -462,7 +484,7 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
         const int m = row0 + (lane & (GA_R - 1)), peer = lane / GA_R;
         if (m < M && peer < B.tp.world) tp_push(B.tp, B.tp.site_push, tp_flag(B.tp, B.tp.site_push), peer, (size_t) J.tp_off + m, val);
         TRACE(5);
-        TRACE_FLUSH(PRO, gridDim.x);
+        TRACE_FLUSH(PRO | (nch_all << 8) | ((unsigned long long) M << 16), gridDim.x);
         return;
     }
     const bool want_q = (J.out_act.f != nullptr);
@@ -485,26 +507,24 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
         }
     }
     TRACE(5);
-    TRACE_FLUSH(PRO, gridDim.x);
+    TRACE_FLUSH(PRO | (nch_all << 8) | ((unsigned long long) M << 16), gridDim.x);
 }
 
-#ifdef RWKV_B200_TRACE
 } // namespace rb
-extern "C" __attribute__((visibility("default"))) int rwkv_b200_debug_trace(unsigned long long * out, int max_records) {
-    unsigned int n = 0;
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(&n, rb::g_trace_n, sizeof(n));
-    const int k = (int) (n < 8192u ? n : 8192u) < max_records ? (int) (n < 8192u ? n : 8192u) : max_records;
-    cudaMemcpyFromSymbol(out, rb::g_trace, (size_t) k * 12 * sizeof(unsigned long long));
-    const unsigned int zero = 0;
-    cudaMemcpyToSymbol(rb::g_trace_n, &zero, sizeof(zero));
-    return k;
-}
+TRACE_EXPORT(rwkv_b200_debug_trace)
 namespace rb {
-#endif
 
+#ifndef RWKV_B200_GA_DEEP_DEFAULT
+#define RWKV_B200_GA_DEEP_DEFAULT false
+#endif
 static int ga_stage_override() {
     static const int v = [] { const char * e = getenv("RWKV_B200_GA_STAGES"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
+// RWKV_B200_GA_DEEP=1: the 5-stage whole-row ring for single-row launches of the 4-bit formats (see launch_async_n)
+static bool ga_deep_ring() {
+    static const bool v = [] { const char * e = getenv("RWKV_B200_GA_DEEP"); return e ? e[0] == '1' : RWKV_B200_GA_DEEP_DEFAULT; }();
     return v;
 }
 
@@ -518,6 +538,16 @@ static cudaError_t launch_async_n(const MatvecBatch & b, int total_ctas, int ygr
     int S = (QFmt<TYPE>::QB == 32 || total_ctas * ygrid >= device_sm_count()) ? 3 : 4;
     if (ga_stage_override() == 3 || ga_stage_override() == 4) S = ga_stage_override();
     const int cl = b.ks > 1 ? b.ks : 0;
+    // Whole-row ring (single-row decode, 4-bit formats): with 5 stages a CTA of a K = 5120 matrix has every tile of its rows in
+    // flight at once -- one DRAM round trip per CTA instead of two (2 CTAs of 100 KB per SM hold the bytes 3 CTAs of 61 KB did)
+    if constexpr (NCOL == 1 && (TYPE == T_Q4_0 || TYPE == T_Q4_1)) {
+        if (ga_deep_ring() && ygrid == 1) {
+            int nch_max = 0;
+            for (int j = 0; j < b.n_jobs; j++) nch_max = std::max(nch_max, (int) ((b.job[j].W.K / 32 + GA_KC - 1) / GA_KC));
+            if (b.ks > 1) nch_max = (nch_max + b.ks - 1) / b.ks;
+            if (nch_max >= 5) return launch_pdl_cluster(matvec_q_kernel<TYPE, 1, 5>, dim3(total_ctas, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 5>(), st, cl, b);
+        }
+    }
     if (S == 3) return launch_pdl_cluster(matvec_q_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, cl, b);
     return launch_pdl_cluster(matvec_q_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, cl, b);
 }
@@ -576,6 +606,7 @@ static cudaError_t set_smem_attr() {
     if (e == cudaSuccess) e = set_smem_one<TYPE, 2, 4>();
     if (e == cudaSuccess) e = set_smem_one<TYPE, 4, 4>();
     if (e == cudaSuccess) e = set_smem_one<TYPE, 8, 4>();
+    if constexpr (TYPE == T_Q4_0 || TYPE == T_Q4_1) { if (e == cudaSuccess) e = set_smem_one<TYPE, 1, 5>(); }
     constexpr int SP = QFmt<TYPE>::QB == 32 ? 3 : 4;
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());

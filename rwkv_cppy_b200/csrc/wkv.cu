@@ -12,26 +12,34 @@
 // state held in registers) or B independent streams (one step each).
 #include "device_utils.cuh"
 #include "launch.cuh"
+#include "trace.cuh"
 
 namespace rb {
 
 // ----------------------------------------------------------------------------------------
 // v4: one thread per channel.
 // ----------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvArgs a) {
+__global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvArgs ga) {
+    __shared__ __align__(16) unsigned char a_raw[sizeof(WkvArgs)];
+    args_to_smem(a_raw, &ga);                   // read after the dependency wait from this copy, not from the constant bank (launch.cuh)
+    TRACE_DECL; TRACE(0);
     pdl_trigger();
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    const int D = a.D;                          // channels in the rows (a shard under tensor parallelism)
-    const int SD = a.state_D ? a.state_D : D;   // width of a state slot
+    const int D = ga.D;                         // channels in the rows (a shard under tensor parallelism)
+    const int SD = ga.state_D ? ga.state_D : D; // width of a state slot
     const bool valid = e < D;
-    const int stream = a.batch ? blockIdx.y : 0;
-    const size_t soff = (size_t) stream * a.state_stride + a.chan0;
+    const int stream = ga.batch ? blockIdx.y : 0;
+    const size_t soff = (size_t) stream * ga.state_stride + ga.chan0;
     float aa = 0, bb = 0, pp = 0, u = 0, w = 0;
     if (valid) {
-        aa = a.state_in[soff + e]; bb = a.state_in[soff + SD + e]; pp = a.state_in[soff + 2 * SD + e];
-        u = a.u[a.chan0 + e]; w = a.decay[a.chan0 + e];
+        aa = ga.state_in[soff + e]; bb = ga.state_in[soff + SD + e]; pp = ga.state_in[soff + 2 * SD + e];
+        u = ga.u[ga.chan0 + e]; w = ga.decay[ga.chan0 + e];
     }
+    __syncthreads();
+    const WkvArgs & a = *reinterpret_cast<const WkvArgs *>(a_raw);
+    TRACE(1);
     pdl_wait();                                 // r, k, v come from the preceding mat-vec; the input state is read-only
+    TRACE(2);
     const int steps = a.batch ? 1 : a.R;
     for (int s = 0; s < steps; s++) {
         const size_t row = a.batch ? stream : s;
@@ -54,6 +62,8 @@ __global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvAr
         act_store_block(a.y, row, e, valid, out);
     }
     if (valid) { a.state_out[soff + e] = aa; a.state_out[soff + SD + e] = bb; a.state_out[soff + 2 * SD + e] = pp; }
+    TRACE(5);
+    TRACE_FLUSH(200, gridDim.x * gridDim.y);
 }
 
 cudaError_t launch_wkv4(const WkvArgs & a, cudaStream_t st) {
@@ -641,3 +651,4 @@ cudaError_t launch_tp_ffn_combine(float * x, const float * recv, int R, int D, c
 }
 
 } // namespace rb
+TRACE_EXPORT(rwkv_b200_debug_trace_wkv)
