@@ -59,13 +59,11 @@ __device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, i
 // TPG (tensor-parallel decode, one row): the row is first gathered from the peers' partial sums (kernels.h TpWait); that variant
 // fetches its constants after the gather (it waits for the peers anyway) to stay within the register budget.
 template <int ITEMS, int NOUT, int NT, bool TPG = false>
-__global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMixArgs ga) {
+__global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMixArgs a) {
     __shared__ double red[4][32];
-    __shared__ __align__(16) unsigned char a_raw[sizeof(LnMixArgs)];
-    args_to_smem(a_raw, &ga);                  // everything read after the dependency wait comes from this copy (launch.cuh)
-    const int r = blockIdx.x, D = ga.D, nt = blockDim.x;
-    const bool from_state = ga.batch || r == 0;
-    const size_t soff = ga.batch ? (size_t) r * ga.state_stride : 0;
+    const int r = blockIdx.x, D = a.D, nt = blockDim.x;
+    const bool from_state = a.batch || r == 0;
+    const size_t soff = a.batch ? (size_t) r * a.state_stride : 0;
 
     TRACE_DECL_IF(true); TRACE(0);
     pdl_trigger();
@@ -73,7 +71,11 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
     // SPLIT (few wide rows, i.e. decode of a wide model): gridDim.y = ITEMS CTAs share a row; each computes the row statistics
     // (same reduction, same bits) but mixes / quantises only item blockIdx.y, so the serial q8 shuffle chains of a row run in parallel.
     const int my_it = gridDim.y > 1 ? (int) blockIdx.y : -1;
-    auto load_constants = [&](const LnMixArgs & a) {
+    // ... and gridDim.z = n_out CTAs per item, one output each (the kernel is then the NOUT = 1 instantiation and o0 selects the
+    // output): the q8 blocks of an item cost ~200 warp instructions per output and warp, issue-bound on the one SM that runs the CTA
+    // (tools/decode_trace.py: 1.7 us for two outputs, 3.1 us for three on the 14B shape).  Plane z = 0 stores the shift state.
+    const int o0 = (int) blockIdx.z;
+    auto load_constants = [&]() {
 #pragma unroll
         for (int it = 0; it < ITEMS; it++) {
             if (my_it >= 0 && it != my_it) continue;
@@ -82,12 +84,10 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
             xs[it] = (valid && from_state) ? a.state_in[soff + e] : 0.0f;
             w[it] = valid ? a.ln_w[e] : 0.0f; bia[it] = valid ? a.ln_b[e] : 0.0f;
 #pragma unroll
-            for (int o = 0; o < NOUT; o++) mu[o][it] = valid ? a.mu[o][e] : 0.0f;
+            for (int o = 0; o < NOUT; o++) mu[o][it] = valid ? a.mu[o0 + o][e] : 0.0f;
         }
     };
-    if constexpr (!TPG) load_constants(ga);    // constants and the (read-only) input state first, then wait for the producer of x
-    __syncthreads();                           // the argument copy is complete
-    const LnMixArgs & a = *reinterpret_cast<const LnMixArgs *>(a_raw);
+    if constexpr (!TPG) load_constants();      // constants and the (read-only) input state first, then wait for the producer of x
     TRACE(1);
     pdl_wait();
     TRACE(2);
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
                 if (my_it < 0 || it == my_it) a.wait.x_out[e] = x[0][it];
             }
         }
-        load_constants(a);
+        load_constants();
     }
     const int nrow = from_state ? 1 : 2;                     // rows to normalise (uniform per CTA)
     float scale[2];
@@ -131,9 +131,9 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
         float xp = xs[p];                                    // state value ...
         if (nrow == 2) xp = __fadd_rn(__fmul_rn(__fmul_rn(x[1][it], scale[1]), w[p]), bia[p]);   // ... or LN(x[r-1])
         const float sx = __fsub_rn(xp, x0);
-        if (valid && (a.batch || r == a.R - 1)) a.state_out[soff + e] = x0;
-        if (valid && a.x0) a.x0[(size_t) r * D + e] = x0;
-        if (valid && a.sx) a.sx[(size_t) r * D + e] = sx;
+        if (valid && o0 == 0 && (a.batch || r == a.R - 1)) a.state_out[soff + e] = x0;
+        if (valid && o0 == 0 && a.x0) a.x0[(size_t) r * D + e] = x0;
+        if (valid && o0 == 0 && a.sx) a.sx[(size_t) r * D + e] = sx;
         float v[NOUT];
 #pragma unroll
         for (int o = 0; o < NOUT; o++) {
@@ -141,10 +141,10 @@ __global__ void __launch_bounds__(NT) ln_mix_kernel(const __grid_constant__ LnMi
             else                    v[o] = __fadd_rn(__fmul_rn(sx, mu[o][p]), x0);
         }
         TRACE(4);
-        act_store_blocks<NOUT>(a.out, (size_t) r, e, valid, v);
+        act_store_blocks<NOUT>(a.out + o0, (size_t) r, e, valid, v);
     }
     TRACE(5);
-    TRACE_FLUSH(100 + NOUT, gridDim.x * gridDim.y);
+    TRACE_FLUSH(100 + NOUT * gridDim.z, gridDim.x * gridDim.y * gridDim.z);
 }
 
 // Sequence rows whose consumers are all tensor-core MATMULs (FP16 outputs only: the tolerance-mode path).
@@ -262,7 +262,12 @@ static cudaError_t launch_ln_mix_i(const LnMixArgs & a, int threads, cudaStream_
     // a handful of wide rows: split every row over ITEMS CTAs (see the kernel).  A TP gather must then not be in place: every CTA
     // reads the whole base row while its siblings write their items of the gathered row.
     const int items_used = (a.D + threads - 1) / threads;
-    const dim3 grid(a.R, (a.D > LN_SMALL_D && a.R <= 8 && (a.wait.site < 0 || a.wait.x_out != a.x)) ? items_used : 1);
+    const bool split = a.D > LN_SMALL_D && a.R <= 8 && (a.wait.site < 0 || a.wait.x_out != a.x);
+    dim3 grid(a.R, split ? items_used : 1);
+    if (split && a.wait.site < 0 && a.n_out > 1) {          // one CTA per (row, item, output): see the kernel
+        grid.z = a.n_out;
+        return launch_pdl(ln_mix_kernel<ITEMS, 1, NT>, grid, dim3(threads), 0, st, a);
+    }
     if (a.wait.site >= 0) {                                  // tensor-parallel decode (v4: 3 att mixes, 2 ffn mixes)
         if (a.n_out == 3) return launch_pdl(ln_mix_kernel<ITEMS, 3, NT, true>, grid, dim3(threads), 0, st, a);
         if (a.n_out == 2) return launch_pdl(ln_mix_kernel<ITEMS, 2, NT, true>, grid, dim3(threads), 0, st, a);

@@ -164,9 +164,21 @@ struct Pass {
             }
             pf_next.clear();
             if (tp_site >= 0) { b.tp = tpf; b.tp.site_push = tp_site; }
-            for (size_t k = i; k < jobs.size() && b.n_jobs < MATVEC_MAX_JOBS; k++)
-                if (!done[k] && jobs[k].W.type == jobs[i].W.type &&
-                    (!type_quantized(jobs[i].W.type) || matvec_ksplit(jobs[k].W.M, jobs[k].W.K) == matvec_ksplit(jobs[i].W.M, jobs[i].W.K))) {
+            // jobs of one launch share the K split, unless every split job of the launch can be split inside its CTAs (kernels.h
+            // MatvecBatch::ks_warps): then each job keeps the split of its own shape
+            auto flexible = [&](const MatvecJob & j) { return !pro && (matvec_ksplit(j.W.M, j.W.K) == 1 || matvec_split_in_cta(j)); };
+            const bool quant = type_quantized(jobs[i].W.type);
+            const int ks_i = quant ? matvec_ksplit(jobs[i].W.M, jobs[i].W.K) : 1;
+            bool grp_flex = quant && flexible(jobs[i]), grp_uniform = true;
+            for (size_t k = i; k < jobs.size() && b.n_jobs < MATVEC_MAX_JOBS; k++) {
+                if (done[k] || jobs[k].W.type != jobs[i].W.type) continue;
+                if (quant) {
+                    const int ks_k = matvec_ksplit(jobs[k].W.M, jobs[k].W.K);
+                    if (grp_flex && flexible(jobs[k])) { if (ks_k != ks_i) grp_uniform = false; }
+                    else if (grp_uniform && ks_k == ks_i) grp_flex = grp_flex && flexible(jobs[k]);
+                    else continue;
+                }
+                {
                     const MatvecJob & j = jobs[k];
                     if (type_quantized(j.W.type) && tc_written.count(j.x.f)) {   // produced by a MATMUL: q8 blocks are stale
                         Act a = j.x; a.h = nullptr; chk(launch_quantize_act(a, rows, st)); tc_written.erase(j.x.f);
@@ -174,6 +186,7 @@ struct Pass {
                     if (j.out_act.f) tc_written.erase(j.out_act.f);
                     b.job[b.n_jobs] = j; b.job[b.n_jobs].out_act.h = nullptr; b.n_jobs++; done[k] = true;
                 }
+            }
             chk(launch_matvec(b, st));
         }
     }

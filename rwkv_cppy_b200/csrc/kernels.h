@@ -52,6 +52,7 @@ struct MatvecJob {
     Act           out_act;            // optional quantised copy of `out` (out_act.q may be null)
     const float * pro_mu = nullptr;   // PRO_LNMIX launches: this job's token-shift mix vector [K]
     int           tp_off = 0;         // EPI_TP_PUSH*: entry offset inside this rank's inbox slot
+    int           ks = 1;             // K split of this job when the launch splits inside the CTA (MatvecBatch::ks_warps; filled by launch_matvec)
 };
 
 // Optional prologue of a single-row quantised mat-vec launch (decode of models up to LN_SMALL_D
@@ -104,6 +105,11 @@ struct MatvecBatch {
     int     n_jobs = 0;
     int     T = 1;
     int     ks = 1;                         // K split (cluster size along x) of the quantised kernel; all jobs of a batch share it
+    // K split inside the CTA instead (filled by launch_matvec): the 8 warps of a CTA cover 32 / ks rows, warp w takes K range w % ks of
+    // row group w / ks, and the partial sums meet in the CTA's own shared memory in the same rank order -- the same bits as the cluster
+    // form without a cluster launch or DSMEM, and every job of the launch may have its own split.  Used whenever no split job has to
+    // emit the q8 block of its 32 outputs (that needs 32 rows per CTA: the cluster form).
+    int     ks_warps = 0;
     // L2 prefetch of the weights of the NEXT dependent launch: a decode step is a chain of dependent launches, and between two of them
     // (tail of one, dependency wait + activation fetch of the next) HBM idles; every warp of this launch asks the L2 for its slice of the
     // next matrices before it waits, so the memory system keeps streaming through the hand-off.
@@ -118,13 +124,24 @@ constexpr unsigned MATVEC_PF_MAX_BYTES = 48u << 20;      // per matrix: the L2 a
 // of the same matrix adds its partial sums in the same order.  Splits while the row blocks alone
 // would leave most SMs idle and every CTA keeps at least five 1024-weight chunks (below that the
 // fixed cost of a CTA outweighs the extra parallelism: measured on 5120x5120 vs 5120x20480).
+inline bool matvec_ksplit_disabled() {
+    static const bool off = [] { const char * e = getenv("RWKV_B200_NO_KSPLIT"); return e && e[0] == '1'; }();
+    return off;
+}
 inline int matvec_ksplit(uint32_t M, uint32_t K) {
     static const int min_chunks = [] { const char * e = getenv("RWKV_B200_KSPLIT_MIN_CHUNKS"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 5; }();   // tuning switch
     const int row_blocks = (int) ((M + 31) / 32), nch = (int) ((K / 32 + TILE_BLOCKS - 1) / TILE_BLOCKS);
     int ks = 1;
+    if (matvec_ksplit_disabled()) return 1;
     while (row_blocks * ks < 3 * device_sm_count() && ks < 4 && nch / (ks * 2) >= min_chunks) ks *= 2;
     return ks;
 }
+// a split job can be split inside the CTA unless it emits the q8 block of its outputs (see MatvecBatch::ks_warps)
+inline bool matvec_split_in_cta_enabled() {           // RWKV_B200_KSPLIT_CLUSTER_ONLY=1: every split launch takes the cluster form (timing experiments)
+    static const bool on = [] { const char * e = getenv("RWKV_B200_KSPLIT_CLUSTER_ONLY"); return !(e && e[0] == '1'); }();
+    return on;
+}
+inline bool matvec_split_in_cta(const MatvecJob & j) { return matvec_split_in_cta_enabled() && j.out_act.f == nullptr; }
 
 // All jobs of a batch must have the same weight type.
 cudaError_t launch_matvec(const MatvecBatch & b, cudaStream_t st);

@@ -26,20 +26,6 @@ namespace rb {
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
-// Kernel arguments live in the constant bank, and the first touch of each of its 64-byte lines on an SM is a miss that costs close to a
-// microsecond (tools/decode_trace.py: a layer-norm kernel spent ~0.9 us per output descriptor it first read after its dependency wait).
-// In a chain of dependent launches every such miss after griddepcontrol.wait is on the critical path.  Kernels with large argument
-// structs therefore copy them to shared memory BEFORE the wait -- plain loads through the generic address of the __grid_constant__
-// parameter, issued by many threads at once: one round trip, hidden behind the predecessor -- and read the copy afterwards.
-// Usage: __shared__ __align__(16) unsigned char raw[sizeof(T)]; args_to_smem<T>(raw, &param); ... __syncthreads(); before the first use.
-template <typename T>
-__device__ __forceinline__ void args_to_smem(unsigned char * dst, const T * param) {
-    static_assert(sizeof(T) % 4 == 0, "argument structs are word-sized");
-    const uint32_t * s = reinterpret_cast<const uint32_t *>(param);
-    uint32_t * d = reinterpret_cast<uint32_t *>(dst);
-    for (unsigned i = threadIdx.x; i < sizeof(T) / 4; i += blockDim.x) d[i] = s[i];
-}
-
 // Debug aid: forward.cpp tags the launches of a pass with a site bit (1 att input, 2 wkv, 4 att output, 8 ffn key / receptance,
 // 16 ffn value, 32 ln_out, 64 head); RWKV_B200_PDL_OFF_SITES=<mask> launches those sites in plain stream order.
 inline int & pdl_site() { static thread_local int s = 0; return s; }

@@ -33,16 +33,14 @@ constexpr int MATVEC_ROWS  = MATVEC_WARPS * MATVEC_R;     // 32 rows per CTA = o
 template <int TYPE, int NCOL>
 __global__ void __launch_bounds__(MATVEC_WARPS * 32)
 matvec_kernel(const __grid_constant__ MatvecBatch B) {
-    __shared__ __align__(16) unsigned char j_raw[sizeof(MatvecJob)];     // this CTA's job, read from here after the dependency wait (launch.cuh)
     pdl_trigger();
     // which job / row block
     int j = 0;
 #pragma unroll 1
     while (j + 1 < B.n_jobs && (int) blockIdx.x >= B.cta_begin[j + 1]) j++;
-    args_to_smem(j_raw, &B.job[j]);
-    const MatvecJob & Jp = B.job[j];
+    const MatvecJob & J = B.job[j];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int M = Jp.W.M, K = Jp.W.K, T = B.T;
+    const int M = J.W.M, K = J.W.K, T = B.T;
     const int row0 = ((int) blockIdx.x - B.cta_begin[j]) * MATVEC_ROWS + warp * MATVEC_R;
     const int col0 = blockIdx.y * NCOL;
 
@@ -51,12 +49,10 @@ matvec_kernel(const __grid_constant__ MatvecBatch B) {
         const size_t esz = (TYPE == T_F32) ? 4 : 2;
 #pragma unroll
         for (int r = 0; r < MATVEC_R; r++) {
-            const char * p = reinterpret_cast<const char *>(Jp.W.qs) + (size_t) min(row0 + r, M - 1) * K * esz + (size_t) lane * 128;
+            const char * p = reinterpret_cast<const char *>(J.W.qs) + (size_t) min(row0 + r, M - 1) * K * esz + (size_t) lane * 128;
             if ((size_t) lane * 128 < (size_t) K * esz) asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
         }
     }
-    __syncthreads();
-    const MatvecJob & J = *reinterpret_cast<const MatvecJob *>(j_raw);
     pdl_wait();
 
     {
@@ -240,26 +236,31 @@ static cudaError_t launch_typed(const MatvecBatch & b, int total_ctas, cudaStrea
     else               return launch_pdl(matvec_kernel<TYPE, 8>, dim3(total_ctas, (b.T + 7) / 8), block, 0, st, b);
 }
 
-static bool matvec_ksplit_disabled() {
-    static const bool off = [] { const char * e = getenv("RWKV_B200_NO_KSPLIT"); return e && e[0] == '1'; }();
-    return off;
-}
 
 cudaError_t launch_matvec(const MatvecBatch & b_in, cudaStream_t st) {
     if (b_in.n_jobs == 0) return cudaSuccess;
     MatvecBatch b = b_in;
     const uint32_t type = b.job[0].W.type;
     int total = 0;
-    b.ks = 1;
+    b.ks = 1; b.ks_warps = 0;
     if (type_quantized(type)) {
-        b.ks = matvec_ksplit(b.job[0].W.M, b.job[0].W.K);
-        for (int j = 1; j < b.n_jobs; j++) if (matvec_ksplit(b.job[j].W.M, b.job[j].W.K) != b.ks) return cudaErrorInvalidValue;   // callers group by split
-        if (matvec_ksplit_disabled()) b.ks = 1;
+        // the split of a matrix is a function of its shape only (kernels.h); where it happens is a property of the launch
+        bool in_cta = matvec_split_in_cta_enabled() && b.pro.kind == PRO_NONE, any = false;
+        for (int j = 0; j < b.n_jobs; j++) {
+            b.job[j].ks = matvec_ksplit(b.job[j].W.M, b.job[j].W.K);
+            if (b.job[j].ks > 1) { any = true; in_cta = in_cta && matvec_split_in_cta(b.job[j]); }
+        }
+        if (any && in_cta) b.ks_warps = 1;
+        else if (any) {                                          // cluster form: one split for the whole launch (callers group by split)
+            b.ks = b.job[0].ks;
+            for (int j = 1; j < b.n_jobs; j++) if (b.job[j].ks != b.ks) return cudaErrorInvalidValue;
+        }
     }
     for (int j = 0; j < b.n_jobs; j++) {
         if (b.job[j].W.type != type) return cudaErrorInvalidValue;
         b.cta_begin[j] = total;
-        total += (((int) b.job[j].W.M + MATVEC_ROWS - 1) / MATVEC_ROWS) * b.ks;
+        const int rows_per_cta = b.ks_warps ? MATVEC_ROWS / b.job[j].ks : MATVEC_ROWS;
+        total += (((int) b.job[j].W.M + rows_per_cta - 1) / rows_per_cta) * b.ks;
     }
     b.cta_begin[b.n_jobs] = total;
     for (int j = 0; j < b.n_jobs; j++)

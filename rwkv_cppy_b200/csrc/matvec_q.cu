@@ -281,26 +281,24 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     __shared__ float tile[NCOL][GA_WARPS * GA_R];
     __shared__ ProXT<PRO != PRO_NONE, PIT> pro_xs;
     __shared__ double pro_red[PRO == PRO_LNMIX ? 2 : 1][32];
-    // what the kernel reads after the dependency wait: this CTA's job and the prologue descriptor, copied out of the constant bank (launch.cuh)
-    __shared__ __align__(16) unsigned char j_raw[sizeof(MatvecJob)];
-    __shared__ __align__(16) unsigned char p_raw[PRO != PRO_NONE ? sizeof(MatvecPrologue) : 16];
 
     TRACE_DECL; TRACE(0);
     pdl_trigger();
     int j = 0;
 #pragma unroll 1
     while (j + 1 < B.n_jobs && (int) blockIdx.x >= B.cta_begin[j + 1]) j++;
-    args_to_smem(j_raw, &B.job[j]);
-    if constexpr (PRO != PRO_NONE) args_to_smem(p_raw, &B.pro);
-    const MatvecJob & Jp = B.job[j];                     // the parameter itself: for everything ahead of the wait
+    const MatvecJob & J = B.job[j];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int M = Jp.W.M, nb = Jp.W.K >> 5, T = B.T;
+    const int M = J.W.M, nb = J.W.K >> 5, T = B.T;
     // K split: the `ks` CTAs of a cluster share one block of 32 rows, CTA kr takes a contiguous range
     // of the row's chunks; partial sums meet in the leader's shared memory (see the tail).
-    const int ks = B.ks, local = (int) blockIdx.x - B.cta_begin[j];
-    const int kr = ks > 1 ? local % ks : 0;
-    const int tile_row0 = (ks > 1 ? local / ks : local) * GA_WARPS * GA_R;
-    const int row0 = tile_row0 + warp * GA_R;
+    // ... or, B.ks_warps: the split happens inside the CTA -- its 8 warps cover 32 / ks rows, warp w takes K range w % ks of row
+    // group w / ks; the partial sums meet in this CTA's shared memory, in the same rank order.
+    const bool ksw = B.ks_warps != 0;
+    const int ks = ksw ? J.ks : B.ks, local = (int) blockIdx.x - B.cta_begin[j];
+    const int kr = ks > 1 ? (ksw ? warp % ks : local % ks) : 0;
+    const int tile_row0 = ksw ? local * (GA_WARPS * GA_R / ks) : (ks > 1 ? local / ks : local) * GA_WARPS * GA_R;
+    const int row0 = tile_row0 + (ksw ? warp / ks : warp) * GA_R;
     const int col0 = blockIdx.y * NCOL;
     const int nch_all = (nb + GA_KC - 1) / GA_KC;
     const int cbase = ks > 1 ? kr * nch_all / ks : 0;
@@ -310,7 +308,7 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     uint8_t * my = ga_smem + (size_t) warp * S * STAGE;
     const uint32_t my_s = smem_u32(my);
     const uint32_t bars = smem_u32(ga_smem + (size_t) GA_WARPS * S * STAGE) + warp * S * 8;
-    const uint8_t * src0 = reinterpret_cast<const uint8_t *>(Jp.W.qs) + (size_t) (row0 / GA_R) * Jp.W.rg_stride + (size_t) cbase * STAGE;
+    const uint8_t * src0 = reinterpret_cast<const uint8_t *>(J.W.qs) + (size_t) (row0 / GA_R) * J.W.rg_stride + (size_t) cbase * STAGE;
     uint32_t last_bytes = (uint32_t) ((GA_R * (nb - (nch_all - 1) * GA_KC) * BB + 15) & ~15);   // the row's final (possibly short) chunk
     if (lane == 0) {
 #pragma unroll
@@ -348,19 +346,17 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
         }
     }
     XCursor<TYPE, NCOL> xc;
-    if (PRO == PRO_NONE) xc.init(Jp.x, Jp.x_off, col0, T, lane, cbase);
+    if (PRO == PRO_NONE) xc.init(J.x, J.x_off, col0, T, lane, cbase);
     ProLnRegs<PIT> pln; ProWkvRegs<PIT> pwk;
-    if (PRO == PRO_LNMIX) pro_lnmix_pre<PIT>(B.pro, Jp.pro_mu, pln);
+    if (PRO == PRO_LNMIX) pro_lnmix_pre<PIT>(B.pro, J.pro_mu, pln);
     if (PRO == PRO_WKV4)  pro_wkv4_pre<PIT>(B.pro, pwk);
-    __syncthreads();                                    // the argument copies are complete
-    const MatvecJob & J = *reinterpret_cast<const MatvecJob *>(j_raw);
-    const MatvecPrologue & P = *reinterpret_cast<const MatvecPrologue *>(p_raw);
+    __syncwarp();
     TRACE(1);
     pdl_wait();                                         // activations (and the residual) come from the preceding kernels
     TRACE(2);
     if constexpr (PRO != PRO_NONE) {
-        if (PRO == PRO_LNMIX) pro_lnmix_post<PIT>(P, B.tp, J.pro_mu, pln, pro_xs, pro_red TRACE_PASS);
-        if (PRO == PRO_WKV4)  pro_wkv4_post<PIT>(P, pwk, pro_xs);
+        if (PRO == PRO_LNMIX) pro_lnmix_post<PIT>(B.pro, B.tp, J.pro_mu, pln, pro_xs, pro_red TRACE_PASS);
+        if (PRO == PRO_WKV4)  pro_wkv4_post<PIT>(B.pro, pwk, pro_xs);
         __syncthreads();
         xc.q = pro_xs.q + lane * 32; xc.d = pro_xs.d + lane; xc.s = pro_xs.s + lane; xc.isum = pro_xs.isum + lane;
         xc.K = 0; xc.nbrow = 0; xc.tmax = 0;
@@ -460,14 +456,31 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
             if (HAS_M) v = __fadd_rn(v, warp_sum(ra[r].summ[c]));
             if (lane == r * NCOL + c) mine = v;
         }
-    if (ks > 1) {
+    __shared__ float part[GA_KSPLIT_MAX][GA_WARPS * GA_R * NCOL];
+    if (ks > 1 && ksw) {
+        // partial sums of the ks warps of a row group -> its first warp, summed there in rank order (no q8 epilogue in this form:
+        // the other warps are done)
+        float * pw = &part[0][0];
+        if (lane < GA_R * NCOL) pw[warp * GA_R * NCOL + lane] = mine;
+        if (!EPI_EARLY && kr == 0 && lane < GA_R * NCOL && row0 + lane / NCOL < M && col0 + lane % NCOL < T)
+            epre = load_epilogue_operands(J, col0 + lane % NCOL, row0 + lane / NCOL);      // in flight across the barrier
+        __syncthreads();
+        if (kr != 0) return;
+        if (lane < GA_R * NCOL) {
+            float tsum = mine;
+            for (int k = 1; k < ks; k++) tsum = __fadd_rn(tsum, pw[(warp + k) * GA_R * NCOL + lane]);
+            mine = tsum;
+        }
+    } else if (ks > 1) {
         // partial sums of the cluster -> leader (DSMEM), summed there in rank order
-        __shared__ float part[GA_KSPLIT_MAX][GA_WARPS * GA_R * NCOL];
         const int slot = warp * GA_R * NCOL + min(lane, GA_R * NCOL - 1);
         uint32_t remote;
         asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(remote) : "r"(smem_u32(&part[kr][slot])));
         if (lane < GA_R * NCOL) asm volatile("st.shared::cluster.f32 [%0], %1;" :: "r"(remote), "f"(mine) : "memory");
         asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        // the leader's epilogue operands travel while the cluster gathers (they were an L2 round trip after the barrier)
+        if (!EPI_EARLY && kr == 0 && lane < GA_R * NCOL && row0 + lane / NCOL < M && col0 + lane % NCOL < T)
+            epre = load_epilogue_operands(J, col0 + lane % NCOL, row0 + lane / NCOL);
         asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
         if (kr != 0) return;
         if (lane < GA_R * NCOL) {
@@ -493,7 +506,7 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
         const int m = row0 + r, t = col0 + c;
         float v = 0.0f;
         if (m < M && t < T) {
-            if (!EPI_EARLY) epre = load_epilogue_operands(J, t, m);
+            if (!EPI_EARLY && ks == 1) epre = load_epilogue_operands(J, t, m);
             v = apply_epilogue_pre(J, mine, epre);
             if (J.out) J.out[(size_t) t * J.ldo + m] = v;
         }

@@ -10,8 +10,8 @@ constexpr unsigned TRACE_RECORDS = 8192;
 static __device__ unsigned long long g_trace[TRACE_RECORDS * 12];
 static __device__ unsigned int g_trace_n;
 __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-__device__ __forceinline__ bool trace_first() { return blockIdx.x == 0 && blockIdx.y == 0; }
-__device__ __forceinline__ bool trace_last()  { return blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1; }
+__device__ __forceinline__ bool trace_first() { return blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0; }
+__device__ __forceinline__ bool trace_last()  { return blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1 && blockIdx.z == gridDim.z - 1; }
 static inline int trace_read(unsigned long long * out, int max_records) {
     unsigned int n = 0;
     cudaDeviceSynchronize();
@@ -30,7 +30,7 @@ static inline int trace_read(unsigned long long * out, int max_records) {
 #define TRACE_FLUSH(kind, grid) do { if (tr_on_) { \
     const unsigned int n_ = atomicAdd(&rb::g_trace_n, 1u) & (rb::TRACE_RECORDS - 1); \
     for (int i_ = 0; i_ < 10; i_++) rb::g_trace[n_ * 12 + i_] = tr_[i_]; rb::g_trace[n_ * 12 + 10] = (unsigned long long) (kind); \
-    rb::g_trace[n_ * 12 + 11] = (unsigned long long) (grid) | ((unsigned long long) (blockIdx.y * gridDim.x + blockIdx.x) << 24); } } while (0)
+    rb::g_trace[n_ * 12 + 11] = (unsigned long long) (grid) | ((unsigned long long) ((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) << 24); } } while (0)
 #define TRACE_ARG , unsigned long long * tr_, bool tr_on_
 #define TRACE_PASS , tr_, tr_on_
 #define TRACE_EXPORT(name) extern "C" __attribute__((visibility("default"))) int name(unsigned long long * out, int max_records) { return rb::trace_read(out, max_records); }

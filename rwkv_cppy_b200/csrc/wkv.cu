@@ -19,24 +19,20 @@ namespace rb {
 // ----------------------------------------------------------------------------------------
 // v4: one thread per channel.
 // ----------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvArgs ga) {
-    __shared__ __align__(16) unsigned char a_raw[sizeof(WkvArgs)];
-    args_to_smem(a_raw, &ga);                   // read after the dependency wait from this copy, not from the constant bank (launch.cuh)
+__global__ void __launch_bounds__(256) wkv4_kernel(const __grid_constant__ WkvArgs a) {
     TRACE_DECL; TRACE(0);
     pdl_trigger();
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    const int D = ga.D;                         // channels in the rows (a shard under tensor parallelism)
-    const int SD = ga.state_D ? ga.state_D : D; // width of a state slot
+    const int D = a.D;                         // channels in the rows (a shard under tensor parallelism)
+    const int SD = a.state_D ? a.state_D : D; // width of a state slot
     const bool valid = e < D;
-    const int stream = ga.batch ? blockIdx.y : 0;
-    const size_t soff = (size_t) stream * ga.state_stride + ga.chan0;
+    const int stream = a.batch ? blockIdx.y : 0;
+    const size_t soff = (size_t) stream * a.state_stride + a.chan0;
     float aa = 0, bb = 0, pp = 0, u = 0, w = 0;
     if (valid) {
-        aa = ga.state_in[soff + e]; bb = ga.state_in[soff + SD + e]; pp = ga.state_in[soff + 2 * SD + e];
-        u = ga.u[ga.chan0 + e]; w = ga.decay[ga.chan0 + e];
+        aa = a.state_in[soff + e]; bb = a.state_in[soff + SD + e]; pp = a.state_in[soff + 2 * SD + e];
+        u = a.u[a.chan0 + e]; w = a.decay[a.chan0 + e];
     }
-    __syncthreads();
-    const WkvArgs & a = *reinterpret_cast<const WkvArgs *>(a_raw);
     TRACE(1);
     pdl_wait();                                 // r, k, v come from the preceding mat-vec; the input state is read-only
     TRACE(2);

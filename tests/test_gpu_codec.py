@@ -157,3 +157,59 @@ def test_matvec_at_full_size(raw_lib, t):
         ya, yb, yab = dm.mul(a)[0], dm.mul(b)[0], dm.mul(a + b)[0]
         assert np.allclose(yab, ya + yb, rtol=1e-5, atol=1e-4)
     dm.free()
+
+
+KSPLIT_SHAPES = [(256, 10240), (160, 20480), (96, 21600)]      # few row blocks, long rows: K split 2, 4 and 4 with a ragged last chunk
+_KSPLIT_CHILD = r"""
+import sys, hashlib, numpy as np
+sys.path.insert(0, {root!r}); sys.path.insert(0, {root!r} + "/tests")
+from oracle.refload import RwkvLib
+from test_gpu_codec import make_matrix, DevMatrix, KSPLIT_SHAPES
+from oracle import rwkv_oracle as O
+L = RwkvLib({lib!r})
+for t in (O.TYPE_Q4_0, O.TYPE_Q4_1, O.TYPE_Q5_0, O.TYPE_Q5_1, O.TYPE_Q8_0):
+    for M, K in KSPLIT_SHAPES:
+        rng = np.random.default_rng(M + K + t)
+        mat, raw = make_matrix(rng, t, M, K)
+        dm = DevMatrix(L.lib, t, raw, M, K)
+        x = rng.standard_normal((8, K)).astype(np.float32)
+        h = hashlib.sha256()
+        for n in (1, 3, 8):
+            h.update(dm.mul(x[:n]).tobytes())
+        print(t, M, K, h.hexdigest())
+        dm.free()
+"""
+
+
+@pytest.mark.gpu
+def test_matvec_k_split_inside_cta_and_cluster_agree(raw_lib, lib_path):
+    """Long rows with few row blocks are split along K (kernels.h matvec_ksplit): inside the CTA (8 warps = 32 / ks rows x ks ranges)
+    or, when the q8 block of the outputs is wanted, over a thread-block cluster.  Both add the partial sums in rank order: the
+    results must agree with the oracle and with each other bit for bit (the cluster form is forced in a child process)."""
+    import hashlib, subprocess, sys
+    mine = {}
+    for t in (O.TYPE_Q4_0, O.TYPE_Q4_1, O.TYPE_Q5_0, O.TYPE_Q5_1, O.TYPE_Q8_0):
+        for M, K in KSPLIT_SHAPES:
+            rng = np.random.default_rng(M + K + t)
+            mat, raw = make_matrix(rng, t, M, K)
+            dm = DevMatrix(raw_lib.lib, t, raw, M, K)
+            x = rng.standard_normal((8, K)).astype(np.float32)
+            h = hashlib.sha256()
+            for n in (1, 3, 8):
+                y = dm.mul(x[:n])
+                h.update(y.tobytes())
+                if n == 3:
+                    ref = np.stack([mat.matvec(x[i], "ref") for i in range(n)])
+                    assert np.abs(y - ref).max() <= 2e-5 * (np.abs(ref).max() + 1e-6) * np.sqrt(K / 32), (t, M, K)
+            mine[(t, M, K)] = h.hexdigest()
+            dm.free()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, RWKV_B200_KSPLIT_CLUSTER_ONLY="1")
+    r = subprocess.run([sys.executable, "-c", _KSPLIT_CHILD.format(root=root, lib=lib_path)], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    theirs = {}
+    for line in r.stdout.split("\n"):
+        if line.strip():
+            t, M, K, d = line.split()
+            theirs[(int(t), int(M), int(K))] = d
+    assert theirs == mine
