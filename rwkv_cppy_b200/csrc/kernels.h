@@ -116,9 +116,7 @@ struct MatvecBatch {
     const void * pf_ptr[3] = {};
     unsigned     pf_bytes[3] = {};
     int          n_pf = 0;
-    int          self_pf = 0;               // quantised kernel: tiles per warp beyond the ring that are prefetched into the L2 before the dependency wait
 };
-constexpr int MATVEC_SELF_PF_DEFAULT = 0;
 constexpr unsigned MATVEC_PF_MAX_BYTES = 48u << 20;      // per matrix: the L2 also holds the stream of the running launch
 // K split of a quantised (M x K) mat-vec: a function of the shape only, so that every evaluation
 // of the same matrix adds its partial sums in the same order.  Splits while the row blocks alone

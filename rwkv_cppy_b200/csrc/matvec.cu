@@ -265,12 +265,7 @@ cudaError_t launch_matvec(const MatvecBatch & b_in, cudaStream_t st) {
     b.cta_begin[b.n_jobs] = total;
     for (int j = 0; j < b.n_jobs; j++)
         if ((b.job[j].epi == EPI_TP_PUSH || b.job[j].epi == EPI_TP_PUSH_SIGMOID) && (b.T != 1 || !b.tp.ll[0] || b.tp.site_push < 0)) return cudaErrorInvalidValue;
-    if (type_quantized(type)) {
-        // single-row decode: tiles beyond the ring are prefetched into the L2 ahead of the dependency wait (matvec_q.cu); RWKV_B200_SELF_PF=<tiles per warp>
-        static const int self_pf = [] { const char * e = getenv("RWKV_B200_SELF_PF"); return e ? atoi(e) : MATVEC_SELF_PF_DEFAULT; }();
-        b.self_pf = b.T == 1 ? self_pf : 0;
-        return launch_matvec_async(b, total, st);
-    }
+    if (type_quantized(type)) return launch_matvec_async(b, total, st);
     if (b.pro.kind != PRO_NONE) return cudaErrorInvalidValue;      // prologues exist in the quantised kernel only
     if (type == T_F32 && smallk_ok(b)) return launch_smallk(b, st);
     if (type == T_F32) return launch_typed<T_F32>(b, total, st);

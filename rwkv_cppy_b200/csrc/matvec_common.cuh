@@ -77,11 +77,7 @@ template <int TYPE, int NCOL>
 __device__ __forceinline__ void dot_block(RowAcc<TYPE, NCOL> & ra, const XBlock<NCOL> & xb,
                                           const uint4 q0, const uint4 q1, const uint32_t qh, const float dw, const float mw) {
     int wv[8];
-#ifndef RWKV_B200_MVQ_NO_HI16
     constexpr bool HI16 = (TYPE == T_Q4_0 || TYPE == T_Q4_1);
-#else
-    constexpr bool HI16 = false;
-#endif
     // 4-bit formats: the high nibbles stay where they are (16 x their value, as unsigned bytes) and are summed in a chain of
     // their own; the chain total is an exact multiple of 16, so `>> 4` gives the same integer the shifted nibbles would --
     // four shifts fewer per block and two 4-deep dp4a chains instead of one 8-deep

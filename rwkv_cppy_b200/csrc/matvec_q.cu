@@ -55,11 +55,9 @@ struct XCursor {
     }
     // keeps the pointers in registers (the compiler otherwise rebuilds them from constant memory every iteration)
     __device__ __forceinline__ void pin() {
-#ifndef RWKV_B200_MVQ_NO_PIN
         asm volatile("" : "+l"(q), "+l"(d));
         if (HAS_S) asm volatile("" : "+l"(s));
         if (HAS_I) asm volatile("" : "+l"(isum));
-#endif
     }
     __device__ __forceinline__ void next() { q += GA_KC * 32; d += GA_KC; s += GA_KC; isum += GA_KC; pin(); }
     // Fire-and-forget loads of this lane's share of the next `n` chunks: pulls the whole activation
@@ -265,18 +263,14 @@ __device__ __forceinline__ void pro_wkv4_post(const MatvecPrologue & P, const Pr
 static_assert(sizeof(MatvecBatch) <= 4096, "kernel parameter space");
 
 template <int TYPE, int NCOL, int S, int PRO = PRO_NONE, int PIT = 4>
-__global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? ((QFmt<TYPE>::QB == 32 || S >= 5 || (PRO != PRO_NONE && PIT >= 16)) ? 2 : 3) : (NCOL == 2 ? 2 : 1))
+__global__ void __launch_bounds__(GA_WARPS * 32, NCOL == 1 ? ((QFmt<TYPE>::QB == 32 || (PRO != PRO_NONE && PIT >= 16)) ? 2 : 3) : (NCOL == 2 ? 2 : 1))
 matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     static_assert(PRO == PRO_NONE || NCOL == 1, "prologues are single-row");
     using F = QFmt<TYPE>;
     constexpr int BB = F::QB + F::HB + F::DB;              // bytes per block
     constexpr int STAGE = ga_stage_bytes<TYPE>();
     constexpr bool HAS_M = (TYPE == T_Q4_1 || TYPE == T_Q5_1);
-#ifdef RWKV_B200_MVQ_XNOW
-    constexpr bool PREFETCH_X = false;
-#else
     constexpr bool PREFETCH_X = (NCOL == 1);               // next chunk's activations one iteration ahead
-#endif
     extern __shared__ __align__(128) uint8_t ga_smem[];
     __shared__ float tile[NCOL][GA_WARPS * GA_R];
     __shared__ ProXT<PRO != PRO_NONE, PIT> pro_xs;
@@ -323,16 +317,6 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
                 mbar_expect_tx(bars + s * 8, bytes);
                 bulk_g2s(my_s + s * STAGE, src0 + (size_t) s * STAGE, bytes, bars + s * 8);
             }
-        }
-    }
-    // Self-prefetch: the tiles of this warp's rows that do not fit the ring go to the L2 now, i.e. while the producer of the
-    // activations (a layer norm, the WKV step: latency-bound kernels that leave HBM idle) is still running; after the dependency
-    // wait the ring refills then come from the L2 instead of DRAM.
-    if (B.self_pf > 0 && lane == 0) {
-        const int c_hi = min(nch, S + B.self_pf);
-        for (int c = S; c < c_hi; c++) {
-            const uint32_t bytes = (cbase + c == nch_all - 1) ? last_bytes : (uint32_t) STAGE;
-            bulk_prefetch_l2(src0 + (size_t) c * STAGE, bytes);
         }
     }
     if (B.n_pf > 0 && lane == 0) {                       // this warp's slice of the next launch's weights -> L2 (see MatvecBatch)
@@ -382,9 +366,7 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
     // the refill cursor: source of chunk c + S, and the iteration whose refill is the row's final (short) chunk
     const uint8_t * src_next = src0 + (size_t) S * STAGE;
     const int c_last = nch_all - 1 - cbase - S;
-#ifndef RWKV_B200_MVQ_NO_PIN
     asm volatile("" : "+r"(last_bytes), "+l"(src_next));
-#endif
     int s = 0;
     uint32_t phase = 0;
 #pragma unroll 1
@@ -527,17 +509,8 @@ matvec_q_kernel(const __grid_constant__ MatvecBatch B) {
 TRACE_EXPORT(rwkv_b200_debug_trace)
 namespace rb {
 
-#ifndef RWKV_B200_GA_DEEP_DEFAULT
-#define RWKV_B200_GA_DEEP_DEFAULT false
-#endif
 static int ga_stage_override() {
     static const int v = [] { const char * e = getenv("RWKV_B200_GA_STAGES"); return e ? atoi(e) : 0; }();
-    return v;
-}
-
-// RWKV_B200_GA_DEEP=1: the 5-stage whole-row ring for single-row launches of the 4-bit formats (see launch_async_n)
-static bool ga_deep_ring() {
-    static const bool v = [] { const char * e = getenv("RWKV_B200_GA_DEEP"); return e ? e[0] == '1' : RWKV_B200_GA_DEEP_DEFAULT; }();
     return v;
 }
 
@@ -551,16 +524,9 @@ static cudaError_t launch_async_n(const MatvecBatch & b, int total_ctas, int ygr
     int S = (QFmt<TYPE>::QB == 32 || total_ctas * ygrid >= device_sm_count()) ? 3 : 4;
     if (ga_stage_override() == 3 || ga_stage_override() == 4) S = ga_stage_override();
     const int cl = b.ks > 1 ? b.ks : 0;
-    // Whole-row ring (single-row decode, 4-bit formats): with 5 stages a CTA of a K = 5120 matrix has every tile of its rows in
-    // flight at once -- one DRAM round trip per CTA instead of two (2 CTAs of 100 KB per SM hold the bytes 3 CTAs of 61 KB did)
-    if constexpr (NCOL == 1 && (TYPE == T_Q4_0 || TYPE == T_Q4_1)) {
-        if (ga_deep_ring() && ygrid == 1) {
-            int nch_max = 0;
-            for (int j = 0; j < b.n_jobs; j++) nch_max = std::max(nch_max, (int) ((b.job[j].W.K / 32 + GA_KC - 1) / GA_KC));
-            if (b.ks > 1) nch_max = (nch_max + b.ks - 1) / b.ks;
-            if (nch_max >= 5) return launch_pdl_cluster(matvec_q_kernel<TYPE, 1, 5>, dim3(total_ctas, 1), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 5>(), st, cl, b);
-        }
-    }
+    // Measured and not kept (14B Q4_1 decode, 2.32 ms per token with the rule above): a 5-stage whole-row ring at 2 CTAs per SM
+    // 3.02 ms; a 2-stage ring with 64 registers at 4 CTAs per SM (the 480-CTA att k / v / r launch then fits in one wave) 2.57 ms
+    // -- the layer-norm CTAs that share the SMs with the waiting mat-vec CTAs slow down, and two tiles per warp are too few.
     if (S == 3) return launch_pdl_cluster(matvec_q_kernel<TYPE, NCOL, 3>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 3>(), st, cl, b);
     return launch_pdl_cluster(matvec_q_kernel<TYPE, NCOL, 4>, dim3(total_ctas, ygrid), dim3(GA_WARPS * 32), ga_smem_bytes<TYPE, 4>(), st, cl, b);
 }
@@ -619,7 +585,6 @@ static cudaError_t set_smem_attr() {
     if (e == cudaSuccess) e = set_smem_one<TYPE, 2, 4>();
     if (e == cudaSuccess) e = set_smem_one<TYPE, 4, 4>();
     if (e == cudaSuccess) e = set_smem_one<TYPE, 8, 4>();
-    if constexpr (TYPE == T_Q4_0 || TYPE == T_Q4_1) { if (e == cudaSuccess) e = set_smem_one<TYPE, 1, 5>(); }
     constexpr int SP = QFmt<TYPE>::QB == 32 ? 3 : 4;
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_LNMIX, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
     if (e == cudaSuccess) e = cudaFuncSetAttribute(matvec_q_kernel<TYPE, 1, SP, PRO_WKV4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ga_smem_bytes<TYPE, SP>());
