@@ -281,6 +281,10 @@ struct Pass {
     // ---- tensor parallel (v4): column-parallel k / v / r and ffn key / receptance, row-parallel
     // att output and ffn value, one all-reduce per block -------------------------------
     void tp_all_reduce(const float * send, float * recv, size_t n) { chk(tp_allreduce(m.tp, send, recv, n, st)); }
+    static bool tp_nccl_only() {
+        static const bool v = [] { const char * e = getenv("RWKV_B200_TP_NCCL_ONLY"); return e && e[0] == '1'; }();
+        return v;
+    }
 
     // Fused form (single-row decode, peer memory connected): no collective launches.  The row-split mat-vecs push their partial
     // sums into every peer's low-latency inbox from their epilogue (site 2*layer: att, 2*layer + 1: ffn), and the layer norm that
@@ -347,8 +351,13 @@ struct Pass {
         matvec({k, r}, R);
         Act kin = ws.ffn_k; kin.K = Fl;
         matvec({job(l.ffn_value, kin, ws.tp_send, 2 * (int) D, EPI_STORE)}, R);
-        tp_all_reduce(ws.tp_send, ws.tp_recv, (size_t) R * 2 * D);
-        chk(launch_tp_ffn_combine(ws.x, ws.tp_recv, R, (int) D, st));
+        if (R == 1 && tp_ll_allreduce_usable(m.tp, 2 * D) && !tp_nccl_only()) {
+            // one row: the low-latency all-reduce finishes the channel mix itself (x += sum(r shards) * sum(partial Wv k)): no combine launch
+            chk(tp_ll_allreduce(m.tp, ws.tp_send, nullptr, 2 * D, ws.x, st));
+        } else {
+            tp_all_reduce(ws.tp_send, ws.tp_recv, (size_t) R * 2 * D);
+            chk(launch_tp_ffn_combine(ws.x, ws.tp_recv, R, (int) D, st));
+        }
     }
 
     void ffn(uint32_t layer) {

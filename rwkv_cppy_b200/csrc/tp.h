@@ -33,8 +33,12 @@ inline size_t tp_region_flags_bytes() { return 4096; }
 constexpr size_t TP_LL_MAX_D = 8192;
 constexpr size_t TP_LL_SLOT = TP_LL_MAX_D + TP_LL_MAX_D / 2;
 inline size_t tp_region_ll_offset(int world) { return tp_region_flags_bytes() + (size_t) 2 * world * TP_NMAX * sizeof(float); }
-inline size_t tp_region_bytes(int world) { return tp_region_ll_offset(world) + (size_t) 2 * world * TP_LL_SLOT * 8; }
+// A second area of the same shape serves the stand-alone low-latency all-reduce kernel (tp_p2p.cu tp_ll_allreduce_kernel): entries
+// {value, call counter} instead of a separate flag word, so a collective costs one NVLink store latency and no system-wide fence.
+inline size_t tp_region_ll2_offset(int world) { return tp_region_ll_offset(world) + (size_t) 2 * world * TP_LL_SLOT * 8; }
+inline size_t tp_region_bytes(int world) { return tp_region_ll2_offset(world) + (size_t) 2 * world * TP_LL_SLOT * 8; }
 constexpr int TP_STEP_WORD = 1000;           // u32 index of the pass counter inside the flags page (local use only)
+constexpr int TP_LL2_COUNTER_WORD = 512;     // u32 index of the per-CTA call counters of the low-latency all-reduce (TP_LL_SLOT / 256 of them)
 
 struct TpInfo {
     int rank = 0, world = 1;
@@ -61,6 +65,11 @@ bool tp_p2p_alloc(TpInfo & tp, void * handle_out_64);
 bool tp_p2p_connect(TpInfo & tp, const void * handles /* world x 64 bytes, rank order */);
 void tp_p2p_destroy(TpInfo & tp);
 cudaError_t tp_p2p_collective(const TpInfo & tp, const float * send, float * recv, size_t n, bool gather, cudaStream_t st);
+// Low-latency form for vectors of up to TP_LL_SLOT floats: recv[i] = sum over ranks (rank order) of send[i].  With combine_x the
+// vector is [n / 2 partial sums | n / 2 gate values] and the kernel finishes the v4 channel mix in place of a separate launch:
+// combine_x[i] += sum(send[n / 2 + i]) * sum(send[i])   (recv is not written).
+bool tp_ll_allreduce_usable(const TpInfo & tp, size_t n);
+cudaError_t tp_ll_allreduce(const TpInfo & tp, const float * send, float * recv, size_t n, float * combine_x, cudaStream_t st);
 struct TpFused;
 TpFused tp_fused_desc(const TpInfo & tp);                          // launch descriptor of the fused collectives (ll[0] == nullptr: peer memory not connected)
 bool tp_error_pending(const TpInfo & tp);                          // true (and the word cleared) when a collective kernel timed out since the last call

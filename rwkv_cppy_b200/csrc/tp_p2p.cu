@@ -9,6 +9,7 @@
 // Two inbox generations alternate by epoch parity: a peer can be at most one call ahead.
 #include "tp.h"
 #include "launch.cuh"
+#include "trace.cuh"
 #include "tp_ll.cuh"
 #include <cstdio>
 #include <cstring>
@@ -32,14 +33,17 @@ __device__ __forceinline__ float * region_inbox(uint8_t * base, int world, int p
 }
 
 __global__ void __launch_bounds__(256) tp_p2p_kernel(const __grid_constant__ P2pArgs a) {
+    TRACE_DECL; TRACE(0);
     pdl_trigger();
     const int cta = blockIdx.x, tid = threadIdx.x;
     uint8_t * mine = a.peer[a.rank];
     // this CTA's slice, in float4 units
     const unsigned n4 = (a.n + 3) / 4, per = (n4 + TP_CTAS - 1) / TP_CTAS;
     const unsigned lo = min(n4, per * cta), hi = min(n4, lo + per);
+    TRACE(1);
     pdl_wait();                                              // `send` comes from the preceding kernel; the previous collective
                                                              // (a few launches back, possibly still running under PDL) owns the epoch until it exits
+    TRACE(2);
     const uint32_t e = region_epoch(mine)[cta] + 1;          // this CTA's call counter (only this CTA writes it)
     const int par = e & 1;
     for (unsigned i = lo + tid; i < hi; i += 256) {
@@ -49,6 +53,7 @@ __global__ void __launch_bounds__(256) tp_p2p_kernel(const __grid_constant__ P2p
         for (int p = 0; p < a.world; p++) reinterpret_cast<float4 *>(region_inbox(a.peer[p], a.world, par, a.rank))[i] = v;
     }
     __syncthreads();
+    TRACE(3);
     if (tid < a.world) {
         __threadfence_system();
         // publish: flags[src = me][cta] on peer `tid`
@@ -65,6 +70,7 @@ __global__ void __launch_bounds__(256) tp_p2p_kernel(const __grid_constant__ P2p
         }
     }
     __syncthreads();
+    TRACE(4);
     for (unsigned i = lo + tid; i < hi; i += 256) {
         if (a.gather) {
             for (int r = 0; r < a.world; r++) {
@@ -84,6 +90,84 @@ __global__ void __launch_bounds__(256) tp_p2p_kernel(const __grid_constant__ P2p
         }
     }
     if (tid == 0) region_epoch(mine)[cta] = e;
+    TRACE(5);
+    TRACE_FLUSH(300 + a.gather, gridDim.x);
+}
+
+// Low-latency all-reduce: every entry travels as one 8-byte {value, call counter} store, so the receiver that sees the counter of
+// this call also holds the value -- no __threadfence_system(), no flag word, no second round trip (the flag protocol above measured
+// 9.5 us per call on 2 GPUs, 7.8 us of it between a rank's own stores and the peers' flags: tools/decode_trace.py).  One thread per
+// element: it stores its value into slot `rank` of every peer (a warp writes 256 contiguous bytes per peer), then polls the world
+// slots of its own inbox and adds them in rank order.  Counters are per CTA (a CTA always owns the same elements, whatever the
+// vector length of the call), generations alternate with the counter's parity: a peer can be at most one call ahead per element.
+struct LlArArgs {
+    uint8_t * peer[TP_MAX_WORLD];      // regions of all ranks
+    int rank, world;
+    const float * send; float * recv; float * combine_x;
+    unsigned n, half;                  // elements of the vector; half = n / 2 when combine_x is set
+    size_t ll2_off;                    // byte offset of the area inside a region
+    unsigned int * err;
+};
+
+__global__ void __launch_bounds__(256) tp_ll_allreduce_kernel(const __grid_constant__ LlArArgs a) {
+    TRACE_DECL; TRACE(0);
+    pdl_trigger();
+    const unsigned e = blockIdx.x * 256 + threadIdx.x;
+    const unsigned n_thr = a.combine_x ? a.half : a.n;             // a thread owns element e (and e + half under combine)
+    uint32_t * counter = reinterpret_cast<uint32_t *>(a.peer[a.rank]) + TP_LL2_COUNTER_WORD + blockIdx.x;
+    TRACE(1);
+    pdl_wait();                                                      // `send` comes from the preceding kernel; the previous call of this kernel has completed
+    TRACE(2);
+    const uint32_t call = *reinterpret_cast<volatile uint32_t *>(counter) + 1;
+    const size_t gen = (size_t) (call & 1) * a.world * TP_LL_SLOT;
+    if (e < n_thr) {
+        const float v0 = a.send[e], v1 = a.combine_x ? a.send[a.half + e] : 0.0f;
+        for (int p = 0; p < a.world; p++) {
+            uint2 * slot = reinterpret_cast<uint2 *>(a.peer[p] + a.ll2_off) + gen + (size_t) a.rank * TP_LL_SLOT;
+            asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(slot + e), "r"(__float_as_uint(v0)), "r"(call) : "memory");
+            if (a.combine_x) asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(slot + a.half + e), "r"(__float_as_uint(v1)), "r"(call) : "memory");
+        }
+        TRACE(3);
+        const uint2 * inbox = reinterpret_cast<const uint2 *>(a.peer[a.rank] + a.ll2_off) + gen;
+        uint2 w0[TP_MAX_WORLD], w1[TP_MAX_WORLD];
+#pragma unroll
+        for (int r = 0; r < TP_MAX_WORLD; r++) if (r < a.world) {
+            w0[r] = ll_load(inbox + (size_t) r * TP_LL_SLOT + e);
+            if (a.combine_x) w1[r] = ll_load(inbox + (size_t) r * TP_LL_SLOT + a.half + e);
+        }
+        float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+        for (int r = 0; r < TP_MAX_WORLD; r++) if (r < a.world) {
+            const float p0 = ll_wait(inbox + (size_t) r * TP_LL_SLOT + e, w0[r], call, a.err);
+            s0 = r == 0 ? p0 : __fadd_rn(s0, p0);
+            if (a.combine_x) {
+                const float p1 = ll_wait(inbox + (size_t) r * TP_LL_SLOT + a.half + e, w1[r], call, a.err);
+                s1 = r == 0 ? p1 : __fadd_rn(s1, p1);
+            }
+        }
+        TRACE(4);
+        if (a.combine_x) a.combine_x[e] = __fadd_rn(a.combine_x[e], __fmul_rn(s1, s0));
+        else a.recv[e] = s0;
+    }
+    __syncthreads();                                                 // every thread of the CTA has read the counter
+    if (threadIdx.x == 0) *counter = call;
+    TRACE(5);
+    TRACE_FLUSH(310 + (a.combine_x ? 1 : 0), gridDim.x);
+}
+
+bool tp_ll_allreduce_usable(const TpInfo & tp, size_t n) {
+    static const bool off = [] { const char * e = getenv("RWKV_B200_TP_NO_LL"); return e && e[0] == '1'; }();     // back to the flag protocol (timing comparisons)
+    return !off && tp.p2p.connected && n > 0 && n <= TP_LL_SLOT && tp.world <= TP_MAX_WORLD;
+}
+
+cudaError_t tp_ll_allreduce(const TpInfo & tp, const float * send, float * recv, size_t n, float * combine_x, cudaStream_t st) {
+    if (!tp_ll_allreduce_usable(tp, n) || (combine_x && (n & 1))) return cudaErrorInvalidValue;
+    LlArArgs a;
+    for (int r = 0; r < TP_MAX_WORLD; r++) a.peer[r] = r < tp.world ? tp.p2p.peer[r] : nullptr;
+    a.rank = tp.rank; a.world = tp.world; a.send = send; a.recv = recv; a.combine_x = combine_x;
+    a.n = (unsigned) n; a.half = (unsigned) (n / 2); a.ll2_off = tp_region_ll2_offset(tp.world); a.err = tp.p2p.d_err;
+    const unsigned n_thr = combine_x ? a.half : a.n;
+    return launch_pdl(tp_ll_allreduce_kernel, dim3((n_thr + 255) / 256), dim3(256), 0, st, a);
 }
 
 // Fused tensor parallelism: the residual row of a site materialised outside a mat-vec prologue (the last
@@ -169,3 +253,4 @@ cudaError_t tp_p2p_collective(const TpInfo & tp, const float * send, float * rec
 }
 
 } // namespace rb
+TRACE_EXPORT(rwkv_b200_debug_trace_tp)

@@ -635,11 +635,16 @@ cudaError_t launch_wkv7(const WkvArgs & a, cudaStream_t st) {
 
 // ---- tensor parallel: x += r * (Wv k) after the all-reduce of [partial Wv k | r shards] ----
 __global__ void __launch_bounds__(256) tp_ffn_combine_kernel(float * x, const float * recv /* written by the preceding kernel: NOT __restrict__ (invariant loads may be hoisted above griddepcontrol.wait) */, int D) {
+    TRACE_DECL; TRACE(0);
     pdl_trigger();
+    TRACE(1);
     pdl_wait();
+    TRACE(2);
     const int e = blockIdx.x * 256 + threadIdx.x;
     const size_t row = blockIdx.y;
     if (e < D) x[row * D + e] = __fadd_rn(x[row * D + e], __fmul_rn(recv[row * 2 * D + D + e], recv[row * 2 * D + e]));
+    TRACE(5);
+    TRACE_FLUSH(400, gridDim.x * gridDim.y);
 }
 
 cudaError_t launch_tp_ffn_combine(float * x, const float * recv, int R, int D, cudaStream_t st) {

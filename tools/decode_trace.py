@@ -13,13 +13,31 @@ from rwkv_cppy_b200.rwkv_cpp_shared_library import RWKVSharedLibrary
 shape = sys.argv[1] if len(sys.argv) > 1 else "v4-169m"
 fmt = sys.argv[2] if len(sys.argv) > 2 else "FP16-to-Q4_0"
 lib = RWKVSharedLibrary(os.path.abspath(os.environ["RWKV_B200_LIB"])) if os.environ.get("RWKV_B200_LIB") else rwkv_cppy_b200.load_rwkv_shared_library()
+world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+if world > 1:                                   # tensor parallel: run under torchrun, rank 0 reports its own timeline
+    import torch, torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib.library.rwkv_b200_set_device(local)
+    if rank == 0: synth.ensure_model(None if shape == "v4-14b" else lib, shape, fmt)
+    dist.barrier()
 path = synth.ensure_model(None if shape == "v4-14b" else lib, shape, fmt)
-model = rwkv_cppy_b200.RWKVModel(lib, path)
+if world > 1:
+    ids = [lib.rwkv_b200_tp_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(ids, src=0)
+    model = rwkv_cppy_b200.RWKVModel(lib, path, tensor_parallel=(rank, world, ids[0]))
+    if os.environ.get("RWKV_B200_TP_NCCL_ONLY") != "1":
+        handles = [None] * world
+        dist.all_gather_object(handles, lib.rwkv_b200_tp_ipc_handle(model._ctx))
+        lib.rwkv_b200_tp_connect(model._ctx, handles)
+else:
+    model = rwkv_cppy_b200.RWKVModel(lib, path)
 batch = model.create_batch(1)
 toks = np.random.default_rng(0).integers(0, model.n_vocab, size=(16, 1)).astype(np.uint32)
 batch.run_timed(toks, True)
 readers = []
-for name in ("rwkv_b200_debug_trace", "rwkv_b200_debug_trace_ew", "rwkv_b200_debug_trace_wkv"):
+for name in ("rwkv_b200_debug_trace", "rwkv_b200_debug_trace_ew", "rwkv_b200_debug_trace_wkv", "rwkv_b200_debug_trace_tp"):
     fn = getattr(lib.library, name)
     fn.restype = ctypes.c_int
     readers.append(fn)
@@ -36,8 +54,20 @@ rec = rec[np.argsort(rec[:, 0], kind="stable")]
 print(f"{len(rec)} records, {ms / STEPS * 1e3:.1f} us/step, {model.n_layer} layers")
 
 
+if world > 1:
+    dist.barrier()
+    if rank != 0:
+        dist.destroy_process_group()
+        sys.exit(0)
+
+
 def kind_name(k):
     if k == 200: return "wkv4"
+    if k == 300: return "tp all-reduce"
+    if k == 310: return "tp ll all-reduce"
+    if k == 311: return "tp ll all-reduce+mix"
+    if k == 301: return "tp all-gather"
+    if k == 400: return "tp ffn combine"
     if 100 <= k < 200: return f"ln_mix{k - 100}"
     return f"mv pro{k & 255} nch{(k >> 8) & 255} M{k >> 16}"
 
@@ -48,6 +78,7 @@ rec[:, 11] = gridsz
 first = rec[cta == 0]
 last = rec[(cta == gridsz - 1) & (gridsz > 1)]
 ln_all = rec[(rec[:, 10] >= 100) & (rec[:, 10] < 200)]
+p2p_all = rec[(rec[:, 10] == 300) | (rec[:, 10] == 310) | (rec[:, 10] == 311)]
 # pair first / last CTA records of the same launch: same kind, entry stamps within the launch
 per_step = len(first) // STEPS
 step = first[per_step * 2: per_step * 3]
@@ -115,3 +146,10 @@ for k in np.unique(ln_all[:, 10]):
     al = np.array([[r[i] - r[2] for i in (6, 7, 8, 9, 3, 4, 5)] for r in g])
     print("   median over all CTAs: " + " ".join(f"{np.median(al[:, i]):6.0f}" for i in range(7)) + "   max end: %.0f  (per launch median of max end: %.0f)" % (
         al[:, 6].max(), np.median([int((l[:, 5] - l[:, 2].min()).max()) for l in launches])))
+
+if len(p2p_all):
+    d = p2p_all
+    print("\ntp all-reduce kernel, first / last CTA (ns after wait_out): own stores done | peers' flags seen | end   -- medians: %.0f | %.0f | %.0f  (waited for the predecessor %.0f)" % (
+        np.median(d[:, 3] - d[:, 2]), np.median(d[:, 4] - d[:, 2]), np.median(d[:, 5] - d[:, 2]), np.median(d[:, 2] - d[:, 0])))
+if world > 1:
+    dist.destroy_process_group()
