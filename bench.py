@@ -499,7 +499,7 @@ def run_main(args):
                        "model_load_s": round(load_s, 2), "file_bytes": os.path.getsize(path),
                        "collective": None if d.world == 1 else ("NCCL" if os.environ.get("RWKV_B200_TP_NCCL_ONLY") == "1" else
                                      ("fused: push from the mat-vec epilogue + gather in the next layer norm" if os.environ.get("RWKV_B200_TP_FUSE") == "1"
-                                      else "one-shot all-reduce kernel over NVLink peer memory (csrc/tp_p2p.cu)"))},
+                                      else "low-latency all-reduce kernel over NVLink peer memory: {value, call counter} entries pushed into every peer's inbox, summed in rank order (csrc/tp_p2p.cu)"))},
         }
         if d.world == 1 and not args.no_cpu:
             try:
