@@ -122,6 +122,10 @@ RWKV_API bool   rwkv_b200_matrix_mul_no_alloc(struct rwkv_b200_matrix * m, const
 RWKV_API size_t rwkv_b200_no_alloc_max_elements(void);
 /* Algorithmic bytes of one copy (the file bytes of the matrix). */
 RWKV_API size_t rwkv_b200_matrix_bytes(const struct rwkv_b200_matrix * m);
+/* Test hook: the K split (1, 2 or 4) the quantised mat-vec applies to an n_rows x n_cols matrix on the current device -- a function of
+ * the shape and the SM count only (148 assumed without a device), so every evaluation of a matrix adds its partial sums in one order
+ * (csrc/kernels.h matvec_ksplit; replaces nothing in the reference, whose ggml_compute_forward_mul_mat ggml-cpu.c:7377 splits rows over threads). */
+RWKV_API int    rwkv_b200_matvec_k_split(size_t n_rows, size_t n_cols);
 
 #ifdef __cplusplus
 }

@@ -451,6 +451,8 @@ void rwkv_b200_matrix_free(struct rwkv_b200_matrix * m) {
 
 size_t rwkv_b200_matrix_bytes(const struct rwkv_b200_matrix * m) { return m && !m->copies.empty() ? m->copies[0].bytes : 0; }
 
+int rwkv_b200_matvec_k_split(size_t n_rows, size_t n_cols) { return matvec_ksplit((uint32_t) n_rows, (uint32_t) n_cols); }
+
 static bool matrix_prepare(rwkv_b200_matrix * m, size_t n_vec) {
     const DevMat & W = m->copies[0];
     if (!m->scratch.buf && matmul_tc_enabled()) {

@@ -74,3 +74,20 @@ def test_no_cpu_fallback_without_a_gpu(raw_lib):
     raw = np.zeros(18, np.uint8)
     assert not raw_lib.lib.rwkv_b200_dequantize(2, raw.ctypes.data, 1, 32, out.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
     raw_lib.lib.rwkv_set_print_errors(None, True)
+
+
+def test_k_split_rule_is_a_function_of_the_shape(lib_path):
+    """csrc/kernels.h matvec_ksplit through its C-ABI hook (no device needed: 148 SMs assumed): long rows with few row blocks are
+    split 2 or 4 ways down to five 1024-weight chunks per warp, tiny grids with short rows two ways, everything else not at all."""
+    import ctypes
+    lib = ctypes.CDLL(lib_path)
+    f = lib.rwkv_b200_matvec_k_split
+    f.restype = ctypes.c_int
+    f.argtypes = [ctypes.c_size_t, ctypes.c_size_t]
+    expect = {(5120, 20480): 4, (5120, 5120): 1, (20480, 5120): 1, (5120, 10240): 2,     # 14B shape and its 2-way shards
+              (768, 3072): 2, (3072, 768): 1, (768, 768): 1,                               # 169M shape: the tiny-grid rule
+              (2560, 2560): 1, (2560, 10240): 2, (2048, 7168): 1,                          # v7 2.9B / v6 1.6B shapes
+              (256, 10240): 2, (160, 20480): 4, (96, 21600): 4, (67, 2048): 2, (32, 32): 1}
+    got = {k: f(*k) for k in expect}
+    assert got == expect
+    assert all(f(*k) == v for k, v in expect.items())      # and again: no hidden state
