@@ -1,8 +1,10 @@
 """Timeline of one decode step from a -DRWKV_B200_TRACE build (csrc/trace.cuh):
     RWKV_B200_BUILD_NAME=trace RWKV_B200_NVCC_FLAGS=-DRWKV_B200_TRACE python -m rwkv_cppy_b200.build
     RWKV_B200_LIB=rwkv_cppy_b200/build/variants/librwkv_trace.so python tools/decode_trace.py [shape] [format]
-The first and the last CTA of every quantised mat-vec, layer-norm / mix and WKV4 launch stamp %globaltimer (ns):
-0 kernel entry, 1 before griddepcontrol.wait, 2 after it, 3 after the prologue / statistics, 4 after the chunk loop, 5 kernel end."""
+The first and the last CTA of every quantised mat-vec, WKV4 and tensor-parallel collective launch and every CTA of the layer-norm / mix
+launches stamp %globaltimer (ns): 0 kernel entry, 1 before griddepcontrol.wait, 2 after it, 3 after the prologue / statistics, 4 after the
+chunk loop / mixes, 5 kernel end (6 - 9: phases of the layer-norm statistics).  Under torchrun (WORLD_SIZE > 1) the model is loaded
+tensor-parallel and rank 0 reports its own timeline."""
 import ctypes, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -108,17 +110,12 @@ for k in np.unique(first[:, 10]):
     lw = np.median(l[:, 2] - l[:, 0]) if len(l) else -1
     print(f"{kind_name(int(k)):28s} n={len(f):5d} first: dur {d:7.0f} ({parts}) waited {w:7.0f} | last CTA: dur {ld:7.0f} waited {lw:7.0f}")
 
-# how the step divides: for consecutive launches (ordered by wait_out), time from the previous launch's last end to this launch's end
-allr = rec[np.argsort(rec[:, 2], kind="stable")]
+# how the step divides: time from the previous launch's latest recorded end to this launch's latest recorded end (a launch whose last
+# CTA leaves no record -- the cluster form of the K split -- passes its tail on to the next launch)
 print("\nstep time by kernel kind: sum over launches of (this launch's latest end - previous launch's latest end), one step")
-ends = {}
-order = []
-for r in step:
-    key = (int(r[10]), int(r[2]))
-    order.append((r, key))
 tot = {}
 prev = None
-for r, key in order:
+for r in step:
     grid = r[11]
     sel = (last[:, 10] == r[10]) & (last[:, 11] == grid) & (np.abs(last[:, 2] - r[2]) < 20000)
     end = max(int(r[5]), int(last[sel][:, 5].max())) if sel.any() else int(r[5])
