@@ -17,6 +17,20 @@ namespace rb {
 // N activation blocks at once (one per output), shuffle chains interleaved for ILP.
 template <int N>
 __device__ __forceinline__ void act_store_blocks(const Act * outs, size_t row, int e, bool valid, const float (&v)[N]) {
+    // rows whose consumers all run on the tensor cores carry no q8 planes: the two shuffle chains and the divisions of every block
+    // would be computed for nothing (256-stream v7 step: the layer norm was issue-bound on exactly this code)
+    bool need_q = false;
+#pragma unroll
+    for (int o = 0; o < N; o++) need_q = need_q || outs[o].q != nullptr;                   // uniform
+    if (!need_q) {
+#pragma unroll
+        for (int o = 0; o < N; o++) {
+            const Act & a = outs[o];
+            if (valid && a.f) a.f[row * a.K + e] = v[o];
+            if (valid && a.h) a.h[row * a.K + e] = __half_as_ushort(__float2half_rn(v[o]));
+        }
+        return;
+    }
     float amax[N]; int q[N], sum[N];
 #pragma unroll
     for (int o = 0; o < N; o++) amax[o] = valid ? fabsf(v[o]) : 0.0f;
