@@ -280,7 +280,7 @@ struct Pass {
 
     // ---- tensor parallel (v4): column-parallel k / v / r and ffn key / receptance, row-parallel
     // att output and ffn value, one all-reduce per block -------------------------------
-    void tp_all_reduce(const float * send, float * recv, size_t n) { chk(tp_allreduce(m.tp, send, recv, n, st)); }
+    void tp_all_reduce(const float * send, float * recv, size_t n) { chk(tp_allreduce(m.tp, send, recv, n, st, /* low_latency = */ R == 1)); }
     static bool tp_nccl_only() {
         static const bool v = [] { const char * e = getenv("RWKV_B200_TP_NCCL_ONLY"); return e && e[0] == '1'; }();
         return v;

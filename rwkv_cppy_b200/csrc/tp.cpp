@@ -68,8 +68,8 @@ static bool use_p2p(const TpInfo & tp, size_t n) {
     return !off && tp.p2p.connected && n <= TP_NMAX;
 }
 
-cudaError_t tp_allreduce(const TpInfo & tp, const float * send, float * recv, size_t n, cudaStream_t st) {
-    if (use_p2p(tp, n) && tp_ll_allreduce_usable(tp, n)) return tp_ll_allreduce(tp, send, recv, n, nullptr, st);
+cudaError_t tp_allreduce(const TpInfo & tp, const float * send, float * recv, size_t n, cudaStream_t st, bool low_latency) {
+    if (low_latency && use_p2p(tp, n) && tp_ll_allreduce_usable(tp, n)) return tp_ll_allreduce(tp, send, recv, n, nullptr, st);
     if (use_p2p(tp, n)) return tp_p2p_collective(tp, send, recv, n, false, st);
     if (!tp.comm) return cudaErrorInvalidValue;
     return api().AllReduce(send, recv, n, NCCL_FLOAT32, NCCL_SUM, tp.comm, st) == 0 ? cudaSuccess : cudaErrorUnknown;

@@ -50,8 +50,11 @@ bool tp_available();                                               // libnccl fo
 bool tp_unique_id(void * out128);                                  // ncclGetUniqueId
 bool tp_comm_init(TpInfo & tp, const void * id128);                // ncclCommInitRank (device = current)
 void tp_comm_destroy(TpInfo & tp);
-// sum of `n` floats over the ranks, result on every rank (send may equal recv)
-cudaError_t tp_allreduce(const TpInfo & tp, const float * send, float * recv, size_t n, cudaStream_t st);
+// sum of `n` floats over the ranks, result on every rank (send may equal recv).  low_latency: the vector is ONE row of the model
+// (single-token decode): it may take the {value, call counter} kernel.  Longer vectors (several rows) must not: an inbox entry of that
+// kernel is always validated against the call counter of the CTA that owns it, and only with one row per call do the plain form
+// (entries [0, D)) and the channel-mix form (entries [0, 2D), two per thread) agree on the owner of every entry.
+cudaError_t tp_allreduce(const TpInfo & tp, const float * send, float * recv, size_t n, cudaStream_t st, bool low_latency = false);
 // every rank contributes `n` floats; recv holds world * n floats in rank order
 cudaError_t tp_allgather(const TpInfo & tp, const float * send, float * recv, size_t n, cudaStream_t st);
 

@@ -100,6 +100,8 @@ __global__ void __launch_bounds__(256) tp_p2p_kernel(const __grid_constant__ P2p
 // element: it stores its value into slot `rank` of every peer (a warp writes 256 contiguous bytes per peer), then polls the world
 // slots of its own inbox and adds them in rank order.  Counters are per CTA (a CTA always owns the same elements, whatever the
 // vector length of the call), generations alternate with the counter's parity: a peer can be at most one call ahead per element.
+// Only single-row vectors take this kernel (tp.h tp_allreduce): then the plain form (entries [0, D), thread e) and the channel-mix form
+// (entries e and D + e, thread e) agree on which CTA's counter validates every entry.
 struct LlArArgs {
     uint8_t * peer[TP_MAX_WORLD];      // regions of all ranks
     int rank, world;
