@@ -227,7 +227,7 @@ struct Pass {
         // mixes: 5 x 4 D bytes from L2) rival its share of the weights -- measured on the 14B shape (D = 5120): 7.18 ms per token
         // fused against 3.44 ms with the stand-alone layer-norm launch.  Fusion pays where the launch chain dominates, not bytes.
         if (!fusion_enabled() || R != 1 || D > (size_t) LN_SMALL_D || D % 32 != 0 || m.tp.world > 1) return false;
-        for (const DevMat * W : mats) if (!type_quantized(W->type) || W->K != D) return false;
+        for (const DevMat * W : mats) if (!type_quantized(W->type) || W->K != D || matvec_ksplit(W->M, W->K) != 1) return false;   // (prologue launches do not split K)
         return true;
     }
     MatvecPrologue ln_prologue(uint32_t layer, bool att, int kind) const {
